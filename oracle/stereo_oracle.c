@@ -1,0 +1,475 @@
+/*
+ * stereo_oracle.c -- CPU ORACLE (test infrastructure, NOT product code).
+ *
+ * Plain-C restatement of the arithmetic that the reference
+ * (ocean1100/stereo_match) hands to OpenCV on its hot path:
+ *   stereo_vision/stereo_vision.py:153-166,178   cv2.StereoSGBM / cv2.StereoBM compute
+ *   stereo_vision/stereo_vision.py:209, disparity_calculation.py:302   cv2.reprojectImageTo3D
+ *   rectified_img_cal.py:253-254, disparity_calculation.py:207-208     cv2.remap
+ *   disparity_calculation.py:286-287                                   cv2.cvtColor(BGR2GRAY)
+ *
+ * The arithmetic lives in a third-party dependency that is NOT under
+ * /root/reference: OpenCV (calib3d / imgproc).  The reference pins no version;
+ * the version in this image is opencv-python-headless 4.13.0.92.  This file
+ * follows the behavioural specification in SURVEY.md Appendix A and is PINNED
+ * by tests/test_oracle_vs_cv2.py (live cv2 4.13.0, bit-exact) and by the
+ * committed fixtures under tests/golden/ (generated from cv2 by
+ * tests/golden/make_golden.py).
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * --impl reference legs may load this library.  The product
+ * (stereo_match_b200/) never does.
+ *
+ * Written for clarity, one loop nest per stage, direction-decomposed path
+ * aggregation (legal because S = sat16(sum_r L_r) is order independent).
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+
+#define ORC_API __attribute__((visibility("default")))
+
+static inline int imin(int a, int b) { return a < b ? a : b; }
+static inline int imax(int a, int b) { return a > b ? a : b; }
+static inline int iclamp(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+static inline int16_t wrap16(int v) { return (int16_t)(uint16_t)(v & 0xffff); }
+static inline int16_t sat16(int v) { return (int16_t)iclamp(v, -32768, 32767); }
+
+typedef struct {
+    int minDisparity, numDisparities, blockSize, P1, P2, disp12MaxDiff;
+    int preFilterCap, uniquenessRatio, speckleWindowSize, speckleRange, mode;
+} orc_sgbm_params;
+
+/* ------------------------------------------------------------------ */
+/* per-row descriptors (clipped x-Sobel g, raw r) and   */
+/* their half-pixel intervals.  Planes are H x W uint8.                */
+/* ------------------------------------------------------------------ */
+static void descriptors(const uint8_t* I, int H, int W, int ftzero,
+                        uint8_t* g, uint8_t* r)
+{
+    for (int y = 0; y < H; y++) {
+        int yn = y > 0 ? y - 1 : y, ys = y < H - 1 ? y + 1 : y;
+        const uint8_t *c = I + (size_t)y * W, *n = I + (size_t)yn * W, *s = I + (size_t)ys * W;
+        uint8_t *gy = g + (size_t)y * W, *ry = r + (size_t)y * W;
+        for (int x = 1; x < W - 1; x++) {
+            int v = 2 * (c[x + 1] - c[x - 1]) + (n[x + 1] - n[x - 1]) + (s[x + 1] - s[x - 1]);
+            gy[x] = (uint8_t)(iclamp(v, -ftzero, ftzero) + ftzero);
+            ry[x] = c[x];
+        }
+        gy[0] = gy[W - 1] = (uint8_t)ftzero;
+        ry[0] = ry[W - 1] = (uint8_t)ftzero;
+    }
+}
+
+static void halfpix(const uint8_t* p, int W, uint8_t* lo, uint8_t* hi)
+{
+    for (int x = 0; x < W; x++) {
+        int v = p[x];
+        int pl = x > 0 ? (v + p[x - 1]) / 2 : v;
+        int pr = x < W - 1 ? (v + p[x + 1]) / 2 : v;
+        lo[x] = (uint8_t)imin(imin(pl, pr), v);
+        hi[x] = (uint8_t)imax(imax(pl, pr), v);
+    }
+}
+
+static inline int bt(int u, int v, int lo1, int hi1, int lo2, int hi2)
+{
+    int c0 = imax(0, imax(u - hi2, lo2 - u));
+    int c1 = imax(0, imax(v - hi1, lo1 - v));
+    return imin(c0, c1);
+}
+
+/* effective parameters, SURVEY.md A.0 */
+typedef struct {
+    int minD, D, maxD, SW2, SH2, P1, P2, uniq, lrmax, ftzero, minX1, maxX1, width1, INVALID;
+} eff_t;
+
+static eff_t effective(const orc_sgbm_params* p, int W)
+{
+    eff_t e;
+    e.minD = p->minDisparity; e.D = p->numDisparities; e.maxD = e.minD + e.D;
+    int bs = p->blockSize > 0 ? p->blockSize : 5;
+    e.SW2 = e.SH2 = bs / 2;
+    e.P1 = p->P1 > 0 ? p->P1 : 2;
+    e.P2 = imax(p->P2 > 0 ? p->P2 : 5, e.P1 + 1);
+    e.uniq = p->uniquenessRatio >= 0 ? p->uniquenessRatio : 10;
+    e.lrmax = p->disp12MaxDiff > 0 ? p->disp12MaxDiff : 1;
+    e.ftzero = imax(p->preFilterCap, 15) | 1;
+    e.minX1 = imax(e.maxD, 0);
+    e.maxX1 = W + imin(e.minD, 0);
+    e.width1 = e.maxX1 - e.minX1;
+    e.INVALID = (e.minD - 1) * 16;
+    return e;
+}
+
+/* ------------------------------------------------------------------ */
+/* SURVEY.md A.1 + A.2: C[y][x][d] = i16(P2 + block sum of BT cost).   */
+/* Cvol must hold H*width1*D int16.                                    */
+/* ------------------------------------------------------------------ */
+static void cost_volume(const uint8_t* L, const uint8_t* R, int H, int W,
+                        const eff_t* e, int16_t* Cvol)
+{
+    const int D = e->D, w1 = e->width1;
+    size_t plane = (size_t)H * W;
+    uint8_t* buf = (uint8_t*)malloc(plane * 12);
+    uint8_t *g1 = buf, *r1 = buf + plane, *g2 = buf + 2 * plane, *r2 = buf + 3 * plane;
+    uint8_t *lo[4], *hi[4];
+    for (int k = 0; k < 4; k++) { lo[k] = buf + (4 + 2 * k) * plane; hi[k] = buf + (5 + 2 * k) * plane; }
+    descriptors(L, H, W, e->ftzero, g1, r1);
+    descriptors(R, H, W, e->ftzero, g2, r2);
+    uint8_t* pl[4] = { g1, r1, g2, r2 };
+    for (int k = 0; k < 4; k++)
+        for (int y = 0; y < H; y++)
+            halfpix(pl[k] + (size_t)y * W, W, lo[k] + (size_t)y * W, hi[k] + (size_t)y * W);
+
+    /* pix[y][x][d], then horizontal sums hs[y][x][d] (clamp on cropped axis) */
+    size_t rowsz = (size_t)w1 * D;
+    uint16_t* pix = (uint16_t*)malloc(rowsz * sizeof(uint16_t));
+    int32_t* hs = (int32_t*)malloc((size_t)H * rowsz * sizeof(int32_t));
+    for (int y = 0; y < H; y++) {
+        size_t o = (size_t)y * W;
+        for (int x = 0; x < w1; x++) {
+            int xi = x + e->minX1;
+            for (int d = 0; d < D; d++) {
+                int xr = xi - (d + e->minD);
+                int cg = bt(g1[o + xi], g2[o + xr], lo[0][o + xi], hi[0][o + xi], lo[2][o + xr], hi[2][o + xr]);
+                int cr = bt(r1[o + xi], r2[o + xr], lo[1][o + xi], hi[1][o + xi], lo[3][o + xr], hi[3][o + xr]);
+                pix[(size_t)x * D + d] = (uint16_t)(cg + (cr >> 2));
+            }
+        }
+        int32_t* hrow = hs + (size_t)y * rowsz;
+        for (int x = 0; x < w1; x++)
+            for (int d = 0; d < D; d++) {
+                int s = 0;
+                for (int k = -e->SW2; k <= e->SW2; k++)
+                    s += pix[(size_t)iclamp(x + k, 0, w1 - 1) * D + d];
+                hrow[(size_t)x * D + d] = s;
+            }
+    }
+    for (int y = 0; y < H; y++) {
+        int16_t* crow = Cvol + (size_t)y * rowsz;
+        for (size_t i = 0; i < rowsz; i++) {
+            int s = e->P2;
+            for (int k = -e->SH2; k <= e->SH2; k++)
+                s += hs[(size_t)iclamp(y + k, 0, H - 1) * rowsz + i];
+            crow[i] = wrap16(s);
+        }
+    }
+    free(hs); free(pix); free(buf);
+}
+
+/* ------------------------------------------------------------------ */
+/* one path direction (dx,dy) = step from predecessor   */
+/* to pixel, i.e. q = p - (dx,dy).  Adds L_r into Ssum (int32).        */
+/* Lout (optional) receives L_r as int16, same layout as C.            */
+/* ------------------------------------------------------------------ */
+static void aggregate_dir(const int16_t* Cvol, int H, int w1, int D, int P1, int P2,
+                          int dx, int dy, int32_t* Ssum, int16_t* Lout)
+{
+    size_t rowsz = (size_t)w1 * D;
+    int16_t* Lbuf = (int16_t*)malloc((size_t)H * rowsz * sizeof(int16_t));
+    int* minL = (int*)malloc((size_t)H * w1 * sizeof(int));
+    int y0 = dy >= 0 ? 0 : H - 1, y1 = dy >= 0 ? H : -1, ys = dy >= 0 ? 1 : -1;
+    /* traversal order: rows so that predecessor row is done; inside a row,
+       x in the order that makes the (dx, dy=0) predecessor available */
+    int x0 = dx >= 0 ? 0 : w1 - 1, x1 = dx >= 0 ? w1 : -1, xs = dx >= 0 ? 1 : -1;
+    for (int y = y0; y != y1; y += ys)
+        for (int x = x0; x != x1; x += xs) {
+            int qx = x - dx, qy = y - dy;
+            const int16_t* Cp = Cvol + (size_t)y * rowsz + (size_t)x * D;
+            int16_t* Lp = Lbuf + (size_t)y * rowsz + (size_t)x * D;
+            int inside = qx >= 0 && qx < w1 && qy >= 0 && qy < H;
+            const int16_t* Lq = inside ? Lbuf + (size_t)qy * rowsz + (size_t)qx * D : NULL;
+            int mq = inside ? minL[(size_t)qy * w1 + qx] : 0;
+            int delta = P2 + mq, mn = 32767;
+            for (int d = 0; d < D; d++) {
+                int a = inside ? Lq[d] : 0;
+                int b = inside ? (d > 0 ? Lq[d - 1] : 32767) + P1 : 0 + P1;
+                int c = inside ? (d < D - 1 ? Lq[d + 1] : 32767) + P1 : 0 + P1;
+                /* outside: L_r(q,.)=0, minL=0 -> min(0, P1, P1, P2) = 0 */
+                int v = Cp[d] + imin(imin(a, b), imin(c, delta)) - delta;
+                int16_t l = wrap16(v);
+                Lp[d] = l;
+                if (l < mn) mn = l;
+                Ssum[(size_t)y * rowsz + (size_t)x * D + d] += l;
+            }
+            minL[(size_t)y * w1 + x] = mn;
+        }
+    if (Lout) memcpy(Lout, Lbuf, (size_t)H * rowsz * sizeof(int16_t));
+    free(minL); free(Lbuf);
+}
+
+static const int DIRS[8][2] = {
+    /* pass 1 */ { 1, 0 }, { 1, 1 }, { 0, 1 }, { -1, 1 },
+    /* 5th path of MODE_SGBM and first of pass 2 */ { -1, 0 },
+    /* rest of pass 2 (MODE_HH) */ { 1, -1 }, { 0, -1 }, { -1, -1 }
+};
+
+/* ------------------------------------------------------------------ */
+/* WTA + uniqueness + disp2 + sub-pixel + LR check.     */
+/* ------------------------------------------------------------------ */
+static void wta_rows(const int16_t* S, int H, int W, const eff_t* e, int16_t* disp)
+{
+    const int D = e->D, w1 = e->width1, INV = e->INVALID;
+    int16_t* disp2 = (int16_t*)malloc(W * sizeof(int16_t));
+    int* disp2cost = (int*)malloc(W * sizeof(int));
+    for (int y = 0; y < H; y++) {
+        int16_t* d1 = disp + (size_t)y * W;
+        for (int x = 0; x < W; x++) { d1[x] = (int16_t)INV; disp2[x] = (int16_t)INV; disp2cost[x] = 32767; }
+        for (int x = w1 - 1; x >= 0; x--) {
+            const int16_t* Sp = S + ((size_t)y * w1 + x) * D;
+            int best = 0, minS = Sp[0];
+            for (int d = 1; d < D; d++) if (Sp[d] < minS) { minS = Sp[d]; best = d; }
+            int d;
+            for (d = 0; d < D; d++)
+                if (Sp[d] * (100 - e->uniq) < minS * 100 && abs(best - d) > 1) break;
+            if (d < D) continue;
+            int x2 = x + e->minX1 - best - e->minD;
+            if (disp2cost[x2] > minS) { disp2cost[x2] = minS; disp2[x2] = (int16_t)(best + e->minD); }
+            int dq;
+            if (best > 0 && best < D - 1) {
+                int denom2 = imax(Sp[best - 1] + Sp[best + 1] - 2 * Sp[best], 1);
+                dq = best * 16 + ((Sp[best - 1] - Sp[best + 1]) * 16 + denom2) / (denom2 * 2);
+            } else dq = best * 16;
+            d1[x + e->minX1] = (int16_t)(dq + e->minD * 16);
+        }
+        for (int x = e->minX1; x < e->maxX1; x++) {
+            int v = d1[x];
+            if (v == INV) continue;
+            int _d = v >> 4, d_ = (v + 15) >> 4, _x = x - _d, x_ = x - d_;
+            if (0 <= _x && _x < W && disp2[_x] >= e->minD && abs(disp2[_x] - _d) > e->lrmax &&
+                0 <= x_ && x_ < W && disp2[x_] >= e->minD && abs(disp2[x_] - d_) > e->lrmax)
+                d1[x] = (int16_t)INV;
+        }
+    }
+    free(disp2cost); free(disp2);
+}
+
+/* 3x3 median, int16, replicate border, out of place */
+ORC_API void orc_median3_i16(const int16_t* src, int H, int W, int16_t* dst)
+{
+    for (int y = 0; y < H; y++)
+        for (int x = 0; x < W; x++) {
+            int16_t v[9]; int n = 0;
+            for (int dy = -1; dy <= 1; dy++)
+                for (int dx = -1; dx <= 1; dx++)
+                    v[n++] = src[(size_t)iclamp(y + dy, 0, H - 1) * W + iclamp(x + dx, 0, W - 1)];
+            for (int i = 1; i < 9; i++) {           /* insertion sort */
+                int16_t k = v[i]; int j = i - 1;
+                while (j >= 0 && v[j] > k) { v[j + 1] = v[j]; j--; }
+                v[j + 1] = k;
+            }
+            dst[(size_t)y * W + x] = v[4];
+        }
+}
+
+/* filterSpeckles as union-find connected components */
+static int uf_find(int* p, int i) { while (p[i] != i) { p[i] = p[p[i]]; i = p[i]; } return i; }
+static void uf_union(int* p, int a, int b)
+{
+    a = uf_find(p, a); b = uf_find(p, b);
+    if (a == b) return;
+    if (a < b) p[b] = a; else p[a] = b;
+}
+
+ORC_API void orc_filter_speckles(int16_t* img, int H, int W, int newVal, int maxSize, int maxDiff)
+{
+    size_t n = (size_t)H * W;
+    int* parent = (int*)malloc(n * sizeof(int));
+    int* count = (int*)calloc(n, sizeof(int));
+    for (size_t i = 0; i < n; i++) parent[i] = (int)i;
+    for (int y = 0; y < H; y++)
+        for (int x = 0; x < W; x++) {
+            int i = y * W + x, v = img[i];
+            if (v == newVal) continue;
+            if (x + 1 < W && img[i + 1] != newVal && abs(v - img[i + 1]) <= maxDiff) uf_union(parent, i, i + 1);
+            if (y + 1 < H && img[i + W] != newVal && abs(v - img[i + W]) <= maxDiff) uf_union(parent, i, i + W);
+        }
+    for (size_t i = 0; i < n; i++) if (img[i] != newVal) count[uf_find(parent, (int)i)]++;
+    for (size_t i = 0; i < n; i++)
+        if (img[i] != newVal && count[uf_find(parent, (int)i)] <= maxSize) img[i] = (int16_t)newVal;
+    free(count); free(parent);
+}
+
+/* ------------------------------------------------------------------ */
+/* StereoSGBM.compute (single-channel).  Optional outputs (may be NULL) */
+/*   Cout, Sout : H*width1*D int16 ; raw : H*W int16 (before median)   */
+/* returns 0, or -1 for unsupported mode.                              */
+/* ------------------------------------------------------------------ */
+ORC_API int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, int W,
+                             const orc_sgbm_params* p, int16_t* disp,
+                             int16_t* Cout, int16_t* Sout, int16_t* raw)
+{
+    if (p->mode != 0 && p->mode != 1) return -1;
+    eff_t e = effective(p, W);
+    size_t n = (size_t)H * W;
+    if (e.width1 <= 0) { for (size_t i = 0; i < n; i++) disp[i] = (int16_t)e.INVALID; return 0; }
+    size_t vol = (size_t)H * e.width1 * e.D;
+    int16_t* Cvol = (int16_t*)malloc(vol * sizeof(int16_t));
+    int32_t* Ssum = (int32_t*)calloc(vol, sizeof(int32_t));
+    cost_volume(left, right, H, W, &e, Cvol);
+    int ndirs = p->mode == 1 ? 8 : 5;
+    for (int k = 0; k < ndirs; k++)
+        aggregate_dir(Cvol, H, e.width1, e.D, e.P1, e.P2, DIRS[k][0], DIRS[k][1], Ssum, NULL);
+    int16_t* S = (int16_t*)malloc(vol * sizeof(int16_t));
+    for (size_t i = 0; i < vol; i++) S[i] = sat16(Ssum[i]);
+    int16_t* tmp = (int16_t*)malloc(n * sizeof(int16_t));
+    wta_rows(S, H, W, &e, tmp);
+    if (raw) memcpy(raw, tmp, n * sizeof(int16_t));
+    orc_median3_i16(tmp, H, W, disp);
+    if (p->speckleWindowSize > 0)
+        orc_filter_speckles(disp, H, W, e.INVALID, p->speckleWindowSize, 16 * p->speckleRange);
+    if (Cout) memcpy(Cout, Cvol, vol * sizeof(int16_t));
+    if (Sout) memcpy(Sout, S, vol * sizeof(int16_t));
+    free(tmp); free(S); free(Ssum); free(Cvol);
+    return 0;
+}
+
+/* one direction's L_r for kernel-level tests; k indexes DIRS */
+ORC_API int orc_sgbm_path(const int16_t* Cvol, int H, int w1, int D, int P1, int P2, int k, int16_t* Lout)
+{
+    if (k < 0 || k >= 8) return -1;
+    int32_t* Ssum = (int32_t*)calloc((size_t)H * w1 * D, sizeof(int32_t));
+    aggregate_dir(Cvol, H, w1, D, P1, P2, DIRS[k][0], DIRS[k][1], Ssum, Lout);
+    free(Ssum);
+    return 0;
+}
+
+ORC_API void orc_sgbm_geometry(const orc_sgbm_params* p, int W, int* out8)
+{
+    eff_t e = effective(p, W);
+    out8[0] = e.minX1; out8[1] = e.maxX1; out8[2] = e.width1; out8[3] = e.INVALID;
+    out8[4] = e.P1; out8[5] = e.P2; out8[6] = e.ftzero; out8[7] = e.uniq;
+}
+
+/* ------------------------------------------------------------------ */
+/* StereoBM.compute, minDisparity = 0, XSOBEL prefilter */
+/* ------------------------------------------------------------------ */
+static void bm_prefilter(const uint8_t* I, int H, int W, int ftzero, uint8_t* P)
+{
+    for (int y = 0; y + 1 < H; y += 2) {
+        int r0 = y > 0 ? y - 1 : y + 1, r1 = y, r2 = y + 1, r3 = y < H - 2 ? y + 2 : y;
+        const uint8_t *a = I + (size_t)r0 * W, *b = I + (size_t)r1 * W, *c = I + (size_t)r2 * W, *d = I + (size_t)r3 * W;
+        uint8_t *p0 = P + (size_t)y * W, *p1 = P + (size_t)(y + 1) * W;
+        p0[0] = p0[W - 1] = p1[0] = p1[W - 1] = (uint8_t)ftzero;
+        for (int x = 1; x < W - 1; x++) {
+            int d0 = a[x + 1] - a[x - 1], d1 = b[x + 1] - b[x - 1];
+            int d2 = c[x + 1] - c[x - 1], d3 = d[x + 1] - d[x - 1];
+            p0[x] = (uint8_t)(iclamp(d0 + 2 * d1 + d2, -ftzero, ftzero) + ftzero);
+            p1[x] = (uint8_t)(iclamp(d1 + 2 * d2 + d3, -ftzero, ftzero) + ftzero);
+        }
+    }
+    if (H & 1) memset(P + (size_t)(H - 1) * W, ftzero, W);
+}
+
+typedef struct {
+    int numDisparities, blockSize, preFilterCap, textureThreshold, uniquenessRatio;
+} orc_bm_params;
+
+ORC_API int orc_bm_compute(const uint8_t* left, const uint8_t* right, int H, int W,
+                           const orc_bm_params* p, int16_t* disp)
+{
+    const int D = p->numDisparities, r = p->blockSize / 2, ftzero = p->preFilterCap;
+    const int FILTERED = -16;
+    size_t n = (size_t)H * W;
+    for (size_t i = 0; i < n; i++) disp[i] = (int16_t)FILTERED;
+    if (D <= 0 || (D % 16) || !(p->blockSize & 1)) return -1;
+    uint8_t* PL = (uint8_t*)malloc(n), *PR = (uint8_t*)malloc(n);
+    bm_prefilter(left, H, W, ftzero, PL);
+    bm_prefilter(right, H, W, ftzero, PR);
+    int x0 = D - 1 + r, x1 = W - r, y0 = r, y1 = H - r;
+    if (x0 < x1 && y0 < y1) {
+        /* column sums of |PL - PR(d)| over the vertical window, per (x', d), rolling in y */
+        int* sad = (int*)malloc(D * sizeof(int));
+        /* colsad[x'][d] for current y window; recomputed per row for clarity (oracle) */
+        int32_t* col = (int32_t*)malloc((size_t)W * D * sizeof(int32_t));
+        int32_t* tcol = (int32_t*)malloc((size_t)W * sizeof(int32_t));
+        for (int y = y0; y < y1; y++) {
+            for (int xx = x0 - r; xx < x1 + r; xx++) {
+                int t = 0;
+                for (int yy = y - r; yy <= y + r; yy++) t += abs(PL[(size_t)yy * W + xx] - ftzero);
+                tcol[xx] = t;
+                for (int d = 0; d < D; d++) {
+                    int s = 0;
+                    for (int yy = y - r; yy <= y + r; yy++)
+                        s += abs(PL[(size_t)yy * W + xx] - PR[(size_t)yy * W + xx - d]);
+                    col[(size_t)xx * D + d] = s;
+                }
+            }
+            for (int x = x0; x < x1; x++) {
+                int tsum = 0;
+                for (int d = 0; d < D; d++) sad[d] = 0;
+                for (int xx = x - r; xx <= x + r; xx++) {
+                    tsum += tcol[xx];
+                    for (int d = 0; d < D; d++) sad[d] += col[(size_t)xx * D + d];
+                }
+                int best = D - 1, minsad = sad[D - 1];
+                for (int d = D - 2; d >= 0; d--) if (sad[d] < minsad) { minsad = sad[d]; best = d; }
+                if (tsum < p->textureThreshold) continue;
+                if (p->uniquenessRatio > 0) {
+                    int thresh = minsad + minsad * p->uniquenessRatio / 100, d;
+                    for (d = 0; d < D; d++) if (abs(d - best) > 1 && sad[d] <= thresh) break;
+                    if (d < D) continue;
+                }
+                int pp = best > 0 ? sad[best - 1] : sad[best + 1];
+                int nn = best < D - 1 ? sad[best + 1] : sad[best - 1];
+                int dd = pp + nn - 2 * sad[best] + abs(pp - nn);
+                disp[(size_t)y * W + x] = (int16_t)((best * 256 + (dd ? (pp - nn) * 256 / dd : 0) + 15) >> 4);
+            }
+        }
+        free(tcol); free(col); free(sad);
+    }
+    free(PR); free(PL);
+    return 0;
+}
+
+/* ------------------------------------------------------------------ */
+/* reprojectImageTo3D.  disp already converted to f32   */
+/* by the caller with NO scaling (that is what cv2 does for u8/i16/i32).*/
+/* ------------------------------------------------------------------ */
+ORC_API void orc_reproject(const float* disp, int H, int W, const double* Q, int handleMissing, float* xyz)
+{
+    float minv = INFINITY;
+    if (handleMissing)
+        for (size_t i = 0; i < (size_t)H * W; i++) if (disp[i] < minv) minv = disp[i];
+    for (int y = 0; y < H; y++)
+        for (int x = 0; x < W; x++) {
+            double d = (double)disp[(size_t)y * W + x];
+            double P[4];
+            for (int k = 0; k < 4; k++)
+                P[k] = Q[4 * k + 0] * x + Q[4 * k + 1] * y + Q[4 * k + 2] * d + Q[4 * k + 3];
+            double iw = 1.0 / P[3];
+            float* o = xyz + ((size_t)y * W + x) * 3;
+            for (int k = 0; k < 3; k++) o[k] = (float)((double)(float)P[k] * iw);
+            if (handleMissing && disp[(size_t)y * W + x] == minv) o[2] = 10000.f;
+        }
+}
+
+/* remap INTER_LINEAR, BORDER_CONSTANT 0, cn interleaved channels */
+ORC_API void orc_remap_u8(const uint8_t* src, int sH, int sW, int cn, const float* mapx, const float* mapy,
+                          int H, int W, uint8_t* dst)
+{
+    for (int y = 0; y < H; y++)
+        for (int x = 0; x < W; x++) {
+            size_t i = (size_t)y * W + x;
+            int sx = (int)lrintf(mapx[i] * 32.f), sy = (int)lrintf(mapy[i] * 32.f);
+            int ix = iclamp(sx >> 5, -32768, 32767), fx = sx & 31;
+            int iy = iclamp(sy >> 5, -32768, 32767), fy = sy & 31;
+            int w00 = imin(32767, (32 - fx) * (32 - fy) * 32), w01 = fx * (32 - fy) * 32;
+            int w10 = (32 - fx) * fy * 32, w11 = fx * fy * 32;
+            for (int c = 0; c < cn; c++) {
+#define TAP(yy, xx) (((yy) >= 0 && (yy) < sH && (xx) >= 0 && (xx) < sW) ? src[((size_t)(yy) * sW + (xx)) * cn + c] : 0)
+                int v = w00 * TAP(iy, ix) + w01 * TAP(iy, ix + 1) + w10 * TAP(iy + 1, ix) + w11 * TAP(iy + 1, ix + 1);
+#undef TAP
+                dst[i * cn + c] = (uint8_t)((v + 16384) >> 15);
+            }
+        }
+}
+
+/* cvtColor BGR2GRAY */
+ORC_API void orc_bgr2gray(const uint8_t* bgr, size_t npix, uint8_t* gray)
+{
+    for (size_t i = 0; i < npix; i++)
+        gray[i] = (uint8_t)((3735 * bgr[3 * i] + 19235 * bgr[3 * i + 1] + 9798 * bgr[3 * i + 2] + 16384) >> 15);
+}
