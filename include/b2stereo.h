@@ -1,0 +1,158 @@
+/*
+ * b2stereo.h -- C ABI of libb2stereo.so: the B200 (sm_100a) stereo disparity engine.
+ *
+ * Drop-in boundary for the ONE hot path of ocean1100/stereo_match: what the
+ * reference hands to OpenCV.  Each entry point names the reference call site it
+ * replaces (paths under the reference repository):
+ *
+ *   b2s_sgbm_*      cv2.StereoSGBM_create(...).compute(l, r)
+ *                       stereo_vision/stereo_vision.py:153-163,178
+ *                       disparity_test.py:165-177, try_try.py:69-81
+ *   b2s_bm_*        cv2.StereoBM_create(numDisparities, blockSize).compute(l, r)
+ *                       stereo_vision/stereo_vision.py:165-166,178
+ *   b2s_reproject   cv2.reprojectImageTo3D(disp, Q)
+ *                       stereo_vision/stereo_vision.py:209, disparity_calculation.py:302
+ *   b2s_remap_u8    cv2.remap(img, mapx, mapy, cv2.INTER_LINEAR)
+ *                       rectified_img_cal.py:253-254, disparity_calculation.py:207-208
+ *   b2s_bgr2gray    cv2.cvtColor(img, cv2.COLOR_BGR2GRAY)
+ *                       disparity_calculation.py:286-287
+ *   b2s_median3_i16, b2s_filter_speckles
+ *                   the cv2.medianBlur / cv2.filterSpeckles that StereoSGBM.compute
+ *                   runs internally, exposed for stage-level parity
+ *
+ * Conventions
+ *   - every data pointer is a DEVICE pointer on the current CUDA device unless the
+ *     name ends in _host; images are dense row-major, batch-major ([batch][H][W]).
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *     Calls are asynchronous on that stream.
+ *   - return value: 0 = ok, otherwise a B2S_E_* code; b2s_last_error() returns a
+ *     thread-local message that names the violated condition.
+ *   - no CPU fallback exists: without a usable CUDA device every compute entry
+ *     point fails with B2S_E_CUDA.
+ */
+#ifndef B2STEREO_H
+#define B2STEREO_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B2S_API __attribute__((visibility("default")))
+#else
+#define B2S_API
+#endif
+
+#define B2S_OK 0
+#define B2S_E_INVALID 1      /* bad argument (message mirrors the cv2 assertion) */
+#define B2S_E_UNSUPPORTED 2  /* valid for cv2 but outside this engine's contract */
+#define B2S_E_CUDA 3         /* CUDA runtime error */
+#define B2S_E_NOMEM 4
+
+/* cv2.STEREO_SGBM_MODE_* */
+#define B2S_MODE_SGBM 0
+#define B2S_MODE_HH 1
+#define B2S_MODE_SGBM_3WAY 2 /* unsupported */
+#define B2S_MODE_HH4 3       /* unsupported */
+
+/* matcher parameters exactly as cv2.StereoSGBM_create receives them (raw, before
+   cv2's silent fallbacks -- those are applied inside) */
+typedef struct b2s_sgbm_params {
+    int32_t minDisparity;
+    int32_t numDisparities;
+    int32_t blockSize;
+    int32_t P1;
+    int32_t P2;
+    int32_t disp12MaxDiff;
+    int32_t preFilterCap;
+    int32_t uniquenessRatio;
+    int32_t speckleWindowSize;
+    int32_t speckleRange;
+    int32_t mode;
+} b2s_sgbm_params;
+
+/* cv2.StereoBM parameters that the reference path can reach (minDisparity is 0,
+   prefilter is XSOBEL, no LR check: SURVEY.md A.9) */
+typedef struct b2s_bm_params {
+    int32_t numDisparities;   /* >0, multiple of 16 */
+    int32_t blockSize;        /* odd, 5..255 */
+    int32_t preFilterCap;     /* 1..63, cv2 default 31 */
+    int32_t textureThreshold; /* cv2 default 10 */
+    int32_t uniquenessRatio;  /* cv2 default 15 */
+    int32_t speckleWindowSize;/* cv2 default 0 */
+    int32_t speckleRange;     /* cv2 default 0 */
+} b2s_bm_params;
+
+typedef struct b2s_matcher* b2s_handle;
+
+/* derived geometry of an SGBM call, for callers that want to inspect volumes */
+typedef struct b2s_sgbm_geometry {
+    int32_t minX1, maxX1, width1; /* computed columns [minX1, maxX1) */
+    int32_t Dp;                   /* padded disparity stride of the cost volumes */
+    int32_t invalid;              /* (minDisparity-1)*16 */
+    int32_t P1, P2, ftzero, uniquenessRatio, disp12MaxDiff; /* effective values */
+    int32_t ndirs;                /* 5 (MODE_SGBM) or 8 (MODE_HH) */
+} b2s_sgbm_geometry;
+
+B2S_API const char* b2s_last_error(void);
+B2S_API const char* b2s_version(void);
+/* number of this library's kernels launched by the calling thread so far */
+B2S_API uint64_t b2s_launch_count(void);
+
+/* ---- StereoSGBM ---------------------------------------------------------- */
+B2S_API int b2s_sgbm_create(const b2s_sgbm_params* params, b2s_handle* out);
+B2S_API int b2s_sgbm_set_params(b2s_handle h, const b2s_sgbm_params* params);
+B2S_API int b2s_sgbm_get_geometry(b2s_handle h, int W, b2s_sgbm_geometry* out);
+/* bytes of workspace the handle will hold for (H, W, batch); allocated lazily */
+B2S_API size_t b2s_sgbm_workspace_bytes(b2s_handle h, int H, int W, int batch);
+/* left/right: [batch][H][W] uint8 ; disp: [batch][H][W] int16 (Q4 fixed point) */
+B2S_API int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t* right,
+                     int H, int W, int batch, int16_t* disp, void* stream);
+/* stage taps for parity tests: copies the last compute's volumes (device to device, on
+   `stream`) into caller buffers of `elems` uint16 each (either may be NULL); layout
+   [batch][H][width1][Dp].  cost = raw block cost (cv2's C minus P2, padded cells 0);
+   S = min(32767, sum of path costs) (padded cells 32767). */
+B2S_API int b2s_sgbm_debug_volumes(b2s_handle h, uint16_t* cost_out, uint16_t* S_out,
+                                   size_t elems, void* stream);
+/* 1 if the last compute left the domain in which bit-exact parity with cv2 is
+   guaranteed: 2*max(raw block cost) + 3*P2 > 32767.  Beyond it cv2's saturating SIMD
+   lanes and its scalar tail disagree with each other, so results there
+   are unpinned (they may still match).  Synchronises the stream. */
+B2S_API int b2s_sgbm_overflow_flag(b2s_handle h, int* flag_host);
+
+/* ---- StereoBM ------------------------------------------------------------ */
+B2S_API int b2s_bm_create(const b2s_bm_params* params, b2s_handle* out);
+B2S_API int b2s_bm_compute(b2s_handle h, const uint8_t* left, const uint8_t* right,
+                   int H, int W, int batch, int16_t* disp, void* stream);
+
+B2S_API void b2s_destroy(b2s_handle h);
+
+/* ---- stand-alone stages -------------------------------------------------- */
+#define B2S_DT_U8 0
+#define B2S_DT_I16 1
+#define B2S_DT_I32 2
+#define B2S_DT_F32 3
+/* xyz: [batch][H][W][3] float32.  Q_host: 16 doubles, row-major, HOST pointer.
+   disp_scale multiplies the disparity after conversion to float32 (1.0 = cv2's
+   behaviour; 1/16 fuses project_points_3D's "/16.0", stereo_vision.py:204).
+   handle_missing needs `scratch` = device buffer of >= batch floats. */
+B2S_API int b2s_reproject(const void* disp, int dtype, int H, int W, int batch,
+                  const double* Q_host, float disp_scale, int handle_missing,
+                  float* scratch, float* xyz, void* stream);
+/* src: [batch][sH][sW][cn] uint8 ; maps: [H][W] float32 shared by the batch */
+B2S_API int b2s_remap_u8(const uint8_t* src, int sH, int sW, int cn, const float* mapx,
+                 const float* mapy, int H, int W, int batch, uint8_t* dst, void* stream);
+B2S_API int b2s_bgr2gray(const uint8_t* bgr, size_t npixels, uint8_t* gray, void* stream);
+B2S_API int b2s_median3_i16(const int16_t* src, int H, int W, int batch, int16_t* dst, void* stream);
+/* in place; labels: device scratch of batch*H*W int32, counts likewise */
+B2S_API int b2s_filter_speckles(int16_t* img, int H, int W, int batch, int newVal,
+                        int maxSpeckleSize, int maxDiff, int32_t* labels,
+                        int32_t* counts, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2STEREO_H */

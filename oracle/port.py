@@ -72,6 +72,8 @@ def sgbm_compute(left, right, want_volumes=False, **kw):
         Sv = np.zeros_like(Cv)
         raw = np.empty((H, W), np.int16)
     rc = lib().orc_sgbm_compute(_p(left), _p(right), H, W, C.byref(p), _p(disp), _p(Cv), _p(Sv), _p(raw))
+    if rc == -2:
+        raise ValueError("oracle: cv2.error -- width - (minDisparity + numDisparities) > SADWindowSize/2")
     if rc != 0:
         raise ValueError("oracle: unsupported SGBM mode")
     return (disp, Cv, Sv, raw) if want_volumes else disp

@@ -295,7 +295,7 @@ ORC_API void orc_filter_speckles(int16_t* img, int H, int W, int newVal, int max
 /* ------------------------------------------------------------------ */
 /* StereoSGBM.compute (single-channel).  Optional outputs (may be NULL) */
 /*   Cout, Sout : H*width1*D int16 ; raw : H*W int16 (before median)   */
-/* returns 0, or -1 for unsupported mode.                              */
+/* returns 0, -1 for unsupported mode, -2 where cv2 raises cv2.error.   */
 /* ------------------------------------------------------------------ */
 ORC_API int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, int W,
                              const orc_sgbm_params* p, int16_t* disp,
@@ -304,6 +304,9 @@ ORC_API int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, i
     if (p->mode != 0 && p->mode != 1) return -1;
     eff_t e = effective(p, W);
     size_t n = (size_t)H * W;
+    /* cv2 4.13.0 (stereosgbm.cpp:511) raises cv2.error unless
+       width - (minDisparity + numDisparities) > SADWindowSize/2 */
+    if (!(W - e.maxD > e.SW2)) return -2;
     if (e.width1 <= 0) { for (size_t i = 0; i < n; i++) disp[i] = (int16_t)e.INVALID; return 0; }
     size_t vol = (size_t)H * e.width1 * e.D;
     int16_t* Cvol = (int16_t*)malloc(vol * sizeof(int16_t));

@@ -1,0 +1,323 @@
+// api.cu -- C ABI of libb2stereo.so (see include/b2stereo.h): handles, parameter rules,
+// workspace, and the per-call kernel pipeline.  No CPU fallback anywhere.
+#include "common.cuh"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+static thread_local char g_err[512] = "";
+static thread_local uint64_t g_launches = 0;
+
+void b2s_set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+void b2s_count_launch(int n) { g_launches += (uint64_t)n; }
+
+extern "C" const char* b2s_last_error(void) { return g_err; }
+extern "C" const char* b2s_version(void) { return "b2stereo 0.1 (sm_100a)"; }
+extern "C" uint64_t b2s_launch_count(void) { return g_launches; }
+
+int b2s_bm_run(const uint8_t* left, const uint8_t* right, int H, int W, int batch, const b2s_bm_params& p,
+               uint8_t* PL, uint8_t* PR, int16_t* disp, cudaStream_t st);
+
+struct b2s_matcher {
+    int kind;                 // 0 = SGBM, 1 = BM
+    b2s_sgbm_params sp;
+    b2s_bm_params bp;
+    // workspace (device), grown on demand
+    void* ws = nullptr;
+    size_t ws_bytes = 0;
+    int* flag = nullptr;      // overflow flag (device)
+    const uint16_t* last_cost = nullptr;
+    const uint16_t* last_S = nullptr;
+    size_t last_elems = 0;
+    cudaStream_t last_stream = nullptr;
+};
+
+static size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
+
+// ---- SGBM parameter rules -----------------------------------
+static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, SgbmEff& e)
+{
+    if (p.numDisparities <= 0) { b2s_set_error("StereoSGBM: numDisparities must be positive"); return B2S_E_INVALID; }
+    if (p.mode != B2S_MODE_SGBM && p.mode != B2S_MODE_HH) {
+        b2s_set_error("StereoSGBM: mode %d (MODE_SGBM_3WAY / MODE_HH4) is not supported by this engine", p.mode);
+        return B2S_E_UNSUPPORTED;
+    }
+    e.H = H; e.W = W; e.batch = batch;
+    e.minD = p.minDisparity; e.D = p.numDisparities;
+    const int bs = p.blockSize > 0 ? p.blockSize : 5;
+    e.SW2 = bs / 2;
+    e.P1 = p.P1 > 0 ? p.P1 : 2;
+    const int p2 = p.P2 > 0 ? p.P2 : 5;
+    e.P2 = p2 > e.P1 + 1 ? p2 : e.P1 + 1;
+    e.uniq = p.uniquenessRatio >= 0 ? p.uniquenessRatio : 10;
+    e.lrmax = p.disp12MaxDiff > 0 ? p.disp12MaxDiff : 1;
+    e.ftzero = (p.preFilterCap > 15 ? p.preFilterCap : 15) | 1;
+    const int maxD = e.minD + e.D;
+    e.minX1 = maxD > 0 ? maxD : 0;
+    e.maxX1 = W + (e.minD < 0 ? e.minD : 0);
+    e.width1 = e.maxX1 - e.minX1;
+    e.invalid = (e.minD - 1) * 16;
+    e.ndirs = p.mode == B2S_MODE_HH ? 8 : 5;
+    // cv2 4.13.0 stereosgbm.cpp:511 raises cv2.error on this condition
+    if (!(W - maxD > e.SW2)) {
+        b2s_set_error("StereoSGBM: Your input images are too small for your window size and max disparity "
+                      "(expected: 'width - (params.minDisparity + params.numDisparities) > "
+                      "params.calcSADWindowSize().width/2'), where %d must be greater than %d", W - maxD, e.SW2);
+        return B2S_E_INVALID;
+    }
+    if (e.ftzero > 127) { b2s_set_error("StereoSGBM: preFilterCap must be <= 127"); return B2S_E_UNSUPPORTED; }
+    if (e.P2 > 32767) { b2s_set_error("StereoSGBM: P2 must be <= 32767 (int16 cost domain)"); return B2S_E_UNSUPPORTED; }
+    // lanes per pixel / registers per lane
+    static const int R8[] = { 1, 2, 3, 4, 6, 8, 12, 16 };
+    static const int R32[] = { 6, 8, 12, 16 };
+    e.G = 0;
+    for (int r : R8) if (16 * r >= e.D) { e.G = 8; e.R = r; break; }
+    if (!e.G) for (int r : R32) if (64 * r >= e.D) { e.G = 32; e.R = r; break; }
+    if (!e.G) { b2s_set_error("StereoSGBM: numDisparities > 1024 is not supported"); return B2S_E_UNSUPPORTED; }
+    e.Dp = 2 * e.R * e.G;
+    return B2S_OK;
+}
+
+struct SgbmLayout { size_t descL, descR, cost, S, raw, key, labels, counts, total; };
+
+static SgbmLayout sgbm_layout(const SgbmEff& e, bool speckle)
+{
+    SgbmLayout l;
+    const size_t npix = (size_t)e.batch * e.H * e.W;
+    const size_t vol = e.width1 > 0 ? (size_t)e.batch * e.H * e.width1 * e.Dp * sizeof(uint16_t) : 0;
+    size_t o = 0;
+    l.descL = o; o += align_up(npix * sizeof(uint2));
+    l.descR = o; o += align_up(npix * sizeof(uint2));
+    l.cost = o; o += align_up(vol);
+    l.S = o; o += align_up(vol);
+    l.raw = o; o += align_up(npix * sizeof(int16_t));
+    l.key = o; o += align_up(npix * sizeof(uint32_t));
+    l.labels = o; o += speckle ? align_up(npix * sizeof(int32_t)) : 0;
+    l.counts = o; o += speckle ? align_up(npix * sizeof(int32_t)) : 0;
+    l.total = o;
+    return l;
+}
+
+static int ensure_ws(b2s_matcher* h, size_t bytes, cudaStream_t st)
+{
+    if (!h->flag) B2S_CUDA_CHECK(cudaMalloc(&h->flag, sizeof(int)));
+    if (bytes <= h->ws_bytes) return B2S_OK;
+    if (h->ws) {
+        B2S_CUDA_CHECK(cudaStreamSynchronize(st));
+        if (h->last_stream && h->last_stream != st) B2S_CUDA_CHECK(cudaStreamSynchronize(h->last_stream));
+        cudaFree(h->ws);
+        h->ws = nullptr; h->ws_bytes = 0;
+    }
+    cudaError_t err = cudaMalloc(&h->ws, bytes);
+    if (err != cudaSuccess) {
+        cudaGetLastError();
+        b2s_set_error("workspace allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(err));
+        return B2S_E_NOMEM;
+    }
+    h->ws_bytes = bytes;
+    return B2S_OK;
+}
+
+static int check_images(const char* who, const void* l, const void* r, const void* d, int H, int W, int batch)
+{
+    if (!l || !r || !d) { b2s_set_error("%s: null image pointer", who); return B2S_E_INVALID; }
+    if (H <= 0 || W <= 0 || batch <= 0) { b2s_set_error("%s: empty image (H=%d W=%d batch=%d)", who, H, W, batch); return B2S_E_INVALID; }
+    if (W > 32768 || H > 65535 || batch > 65535) { b2s_set_error("%s: image or batch too large", who); return B2S_E_UNSUPPORTED; }
+    return B2S_OK;
+}
+
+extern "C" int b2s_sgbm_create(const b2s_sgbm_params* params, b2s_handle* out)
+{
+    if (!params || !out) { b2s_set_error("sgbm_create: null argument"); return B2S_E_INVALID; }
+    b2s_matcher* h = new (std::nothrow) b2s_matcher();
+    if (!h) { b2s_set_error("out of host memory"); return B2S_E_NOMEM; }
+    h->kind = 0; h->sp = *params;
+    *out = h;
+    return B2S_OK;
+}
+
+extern "C" int b2s_sgbm_set_params(b2s_handle h, const b2s_sgbm_params* params)
+{
+    if (!h || h->kind != 0 || !params) { b2s_set_error("sgbm_set_params: bad handle"); return B2S_E_INVALID; }
+    h->sp = *params;
+    return B2S_OK;
+}
+
+extern "C" int b2s_sgbm_get_geometry(b2s_handle h, int W, b2s_sgbm_geometry* out)
+{
+    if (!h || h->kind != 0 || !out) { b2s_set_error("sgbm_get_geometry: bad handle"); return B2S_E_INVALID; }
+    SgbmEff e;
+    int rc = sgbm_effective(h->sp, 1, W, 1, e);
+    if (rc) return rc;
+    out->minX1 = e.minX1; out->maxX1 = e.maxX1; out->width1 = e.width1; out->Dp = e.Dp;
+    out->invalid = e.invalid; out->P1 = e.P1; out->P2 = e.P2; out->ftzero = e.ftzero;
+    out->uniquenessRatio = e.uniq; out->disp12MaxDiff = e.lrmax; out->ndirs = e.ndirs;
+    return B2S_OK;
+}
+
+extern "C" size_t b2s_sgbm_workspace_bytes(b2s_handle h, int H, int W, int batch)
+{
+    if (!h || h->kind != 0) return 0;
+    SgbmEff e;
+    if (sgbm_effective(h->sp, H, W, batch, e)) return 0;
+    return sgbm_layout(e, h->sp.speckleWindowSize > 0).total;
+}
+
+__global__ void k_fill16(int16_t* p, size_t n, int16_t v)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t* right, int H, int W, int batch,
+                                int16_t* disp, void* stream)
+{
+    if (!h || h->kind != 0) { b2s_set_error("sgbm_compute: bad handle"); return B2S_E_INVALID; }
+    int rc = check_images("StereoSGBM", left, right, disp, H, W, batch);
+    if (rc) return rc;
+    SgbmEff e;
+    rc = sgbm_effective(h->sp, H, W, batch, e);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t npix = (size_t)batch * H * W;
+    h->last_cost = h->last_S = nullptr;
+    if (e.width1 <= 0) {                       // nothing computable: whole map INVALID (A.0)
+        k_fill16<<<b2s_cdiv((long long)npix, 256), 256, 0, st>>>(disp, npix, (int16_t)e.invalid);
+        B2S_LAUNCH_CHECK();
+        return B2S_OK;
+    }
+    const bool speckle = h->sp.speckleWindowSize > 0;
+    const SgbmLayout l = sgbm_layout(e, speckle);
+    rc = ensure_ws(h, l.total, st);
+    if (rc) return rc;
+    char* ws = (char*)h->ws;
+    uint2* descL = (uint2*)(ws + l.descL);
+    uint2* descR = (uint2*)(ws + l.descR);
+    uint16_t* cost = (uint16_t*)(ws + l.cost);
+    uint16_t* S = (uint16_t*)(ws + l.S);
+    int16_t* raw = (int16_t*)(ws + l.raw);
+    uint32_t* key = (uint32_t*)(ws + l.key);
+
+    B2S_CUDA_CHECK(cudaMemsetAsync(h->flag, 0, sizeof(int), st));
+    if ((rc = b2s_launch_descriptors(left, e, descL, st))) return rc;
+    if ((rc = b2s_launch_descriptors(right, e, descR, st))) return rc;
+    if ((rc = b2s_launch_cost(descL, descR, e, cost, h->flag, st))) return rc;
+    for (int k = 0; k < e.ndirs; k++)
+        if ((rc = b2s_launch_aggregate(cost, S, e, k, k == 0, st))) return rc;
+    if ((rc = b2s_launch_wta(S, e, raw, key, st))) return rc;
+    if ((rc = b2s_launch_median3(raw, H, W, batch, disp, st))) return rc;
+    if (speckle) {
+        rc = b2s_launch_speckles(disp, H, W, batch, e.invalid, h->sp.speckleWindowSize, 16 * h->sp.speckleRange,
+                                 (int32_t*)(ws + l.labels), (int32_t*)(ws + l.counts), st);
+        if (rc) return rc;
+    }
+    h->last_cost = cost; h->last_S = S; h->last_stream = st;
+    h->last_elems = (size_t)batch * H * e.width1 * e.Dp;
+    return B2S_OK;
+}
+
+extern "C" int b2s_sgbm_debug_volumes(b2s_handle h, uint16_t* cost_out, uint16_t* S_out, size_t elems, void* stream)
+{
+    if (!h || h->kind != 0 || !h->last_cost) { b2s_set_error("debug_volumes: no completed compute on this handle"); return B2S_E_INVALID; }
+    if (elems > h->last_elems) { b2s_set_error("debug_volumes: %zu elements requested, volume has %zu", elems, h->last_elems); return B2S_E_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cost_out) B2S_CUDA_CHECK(cudaMemcpyAsync(cost_out, h->last_cost, elems * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
+    if (S_out) B2S_CUDA_CHECK(cudaMemcpyAsync(S_out, h->last_S, elems * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
+    return B2S_OK;
+}
+
+extern "C" int b2s_sgbm_overflow_flag(b2s_handle h, int* flag_host)
+{
+    if (!h || h->kind != 0 || !flag_host) { b2s_set_error("overflow_flag: bad argument"); return B2S_E_INVALID; }
+    *flag_host = 0;
+    if (!h->flag) return B2S_OK;
+    B2S_CUDA_CHECK(cudaStreamSynchronize(h->last_stream));
+    B2S_CUDA_CHECK(cudaMemcpy(flag_host, h->flag, sizeof(int), cudaMemcpyDeviceToHost));
+    return B2S_OK;
+}
+
+// ---- BM -------------------------------------------------------------------
+static int bm_validate(const b2s_bm_params& p)
+{
+    if (p.numDisparities <= 0 || p.numDisparities % 16 != 0) {
+        b2s_set_error("StereoBM: numDisparities must be positive and divisible by 16");
+        return B2S_E_INVALID;
+    }
+    if (p.blockSize % 2 == 0 || p.blockSize < 5 || p.blockSize > 255) {
+        b2s_set_error("StereoBM: SADWindowSize must be odd, be within 5..255 and be not larger than image width or height");
+        return B2S_E_INVALID;
+    }
+    if (p.preFilterCap < 1 || p.preFilterCap > 63) { b2s_set_error("StereoBM: preFilterCap must be within 1..63"); return B2S_E_INVALID; }
+    if (p.textureThreshold < 0) { b2s_set_error("StereoBM: texture threshold must be non-negative"); return B2S_E_INVALID; }
+    if (p.uniquenessRatio < 0) { b2s_set_error("StereoBM: uniqueness ratio must be non-negative"); return B2S_E_INVALID; }
+    return B2S_OK;
+}
+
+extern "C" int b2s_bm_create(const b2s_bm_params* params, b2s_handle* out)
+{
+    if (!params || !out) { b2s_set_error("bm_create: null argument"); return B2S_E_INVALID; }
+    b2s_matcher* h = new (std::nothrow) b2s_matcher();
+    if (!h) { b2s_set_error("out of host memory"); return B2S_E_NOMEM; }
+    h->kind = 1; h->bp = *params;
+    *out = h;
+    return B2S_OK;
+}
+
+extern "C" int b2s_bm_compute(b2s_handle h, const uint8_t* left, const uint8_t* right, int H, int W, int batch,
+                              int16_t* disp, void* stream)
+{
+    if (!h || h->kind != 1) { b2s_set_error("bm_compute: bad handle"); return B2S_E_INVALID; }
+    int rc = check_images("StereoBM", left, right, disp, H, W, batch);
+    if (rc) return rc;
+    if ((rc = bm_validate(h->bp))) return rc;
+    if (h->bp.blockSize > W || h->bp.blockSize > H) {
+        b2s_set_error("StereoBM: SADWindowSize must be odd, be within 5..255 and be not larger than image width or height");
+        return B2S_E_INVALID;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t npix = (size_t)batch * H * W;
+    const bool speckle = h->bp.speckleWindowSize > 0;
+    size_t need = 2 * align_up(npix) + (speckle ? 2 * align_up(npix * sizeof(int32_t)) : 0);
+    if ((rc = ensure_ws(h, need, st))) return rc;
+    uint8_t* PL = (uint8_t*)h->ws;
+    uint8_t* PR = PL + align_up(npix);
+    if ((rc = b2s_bm_run(left, right, H, W, batch, h->bp, PL, PR, disp, st))) return rc;
+    if (speckle) {
+        int32_t* labels = (int32_t*)(PR + align_up(npix));
+        int32_t* counts = (int32_t*)((char*)labels + align_up(npix * sizeof(int32_t)));
+        rc = b2s_launch_speckles(disp, H, W, batch, -16, h->bp.speckleWindowSize, 16 * h->bp.speckleRange, labels, counts, st);
+        if (rc) return rc;
+    }
+    h->last_stream = st;
+    return B2S_OK;
+}
+
+extern "C" void b2s_destroy(b2s_handle h)
+{
+    if (!h) return;
+    if (h->ws) cudaFree(h->ws);
+    if (h->flag) cudaFree(h->flag);
+    delete h;
+}
+
+// ---- stand-alone stages -----------------------------------------------------
+extern "C" int b2s_median3_i16(const int16_t* src, int H, int W, int batch, int16_t* dst, void* stream)
+{
+    if (!src || !dst || H <= 0 || W <= 0 || batch <= 0) { b2s_set_error("median3: bad argument"); return B2S_E_INVALID; }
+    if (src == dst) { b2s_set_error("median3: in-place operation is not supported"); return B2S_E_INVALID; }
+    return b2s_launch_median3(src, H, W, batch, dst, (cudaStream_t)stream);
+}
+
+extern "C" int b2s_filter_speckles(int16_t* img, int H, int W, int batch, int newVal, int maxSpeckleSize, int maxDiff,
+                                   int32_t* labels, int32_t* counts, void* stream)
+{
+    if (!img || !labels || !counts || H <= 0 || W <= 0 || batch <= 0) { b2s_set_error("filterSpeckles: bad argument"); return B2S_E_INVALID; }
+    return b2s_launch_speckles(img, H, W, batch, newVal, maxSpeckleSize, maxDiff, labels, counts, (cudaStream_t)stream);
+}

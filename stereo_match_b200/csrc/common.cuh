@@ -1,0 +1,60 @@
+// common.cuh -- shared declarations of libb2stereo (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/b2stereo.h"
+
+// Effective SGBM parameters after cv2's silent fallbacks plus the
+// volume geometry.  Passed by value to kernels.
+struct SgbmEff {
+    int H, W, batch;
+    int minD, D, Dp;          // Dp: padded disparity stride (u16 cells) of cost/S volumes
+    int SW2;                  // block half size
+    int P1, P2, uniq, lrmax, ftzero;
+    int minX1, maxX1, width1;
+    int invalid;              // (minD-1)*16
+    int ndirs;                // 5 or 8
+    int G;                    // lanes per pixel in the aggregation/WTA kernels (8 or 32)
+    int R;                    // packed u16x2 registers per lane: Dp = 2*R*G
+};
+
+// aggregation direction table (step from predecessor to pixel), same order as the
+// oracle's DIRS: -> , down-right, down, down-left, <- , up-right, up, up-left
+__host__ __device__ inline void b2s_dir(int k, int& dx, int& dy)
+{
+    const int DX[8] = { 1, 1, 0, -1, -1, 1, 0, -1 };
+    const int DY[8] = { 0, 1, 1, 1, 0, -1, -1, -1 };
+    dx = DX[k]; dy = DY[k];
+}
+
+void b2s_set_error(const char* fmt, ...);
+void b2s_count_launch(int n = 1);
+
+#define B2S_CUDA_CHECK(expr)                                                          \
+    do {                                                                              \
+        cudaError_t _e = (expr);                                                      \
+        if (_e != cudaSuccess) {                                                      \
+            b2s_set_error("CUDA error %s at %s:%d: %s", cudaGetErrorName(_e),        \
+                          __FILE__, __LINE__, cudaGetErrorString(_e));                \
+            return B2S_E_CUDA;                                                        \
+        }                                                                             \
+    } while (0)
+
+#define B2S_LAUNCH_CHECK() do { b2s_count_launch(); B2S_CUDA_CHECK(cudaGetLastError()); } while (0)
+
+static inline int b2s_cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// ---- stage launchers (each in its own .cu) ---------------------------------
+// descriptors: per image pixel 2 words: (u, lo, hi, 0) for the Sobel channel and the raw channel
+int b2s_launch_descriptors(const uint8_t* img, const SgbmEff& e, uint2* desc, cudaStream_t st);
+int b2s_launch_cost(const uint2* descL, const uint2* descR, const SgbmEff& e, uint16_t* cost,
+                    int* overflow_flag, cudaStream_t st);
+// first!=0: S = L_r (plain store); otherwise S = min(32767, S + L_r)
+int b2s_launch_aggregate(const uint16_t* cost, uint16_t* S, const SgbmEff& e, int dir, int first,
+                         cudaStream_t st);
+int b2s_launch_wta(const uint16_t* S, const SgbmEff& e, int16_t* disp_raw, uint32_t* disp2key,
+                   cudaStream_t st);
+int b2s_launch_median3(const int16_t* src, int H, int W, int batch, int16_t* dst, cudaStream_t st);
+int b2s_launch_speckles(int16_t* img, int H, int W, int batch, int newVal, int maxSize, int maxDiff,
+                        int32_t* labels, int32_t* counts, cudaStream_t st);

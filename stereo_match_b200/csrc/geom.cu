@@ -1,0 +1,164 @@
+// geom.cu -- reprojectImageTo3D, remap(INTER_LINEAR) and BGR2GRAY.
+// Reference call sites: stereo_vision/stereo_vision.py:209, disparity_calculation.py:302
+// (reproject); rectified_img_cal.py:253-254, disparity_calculation.py:207-208 (remap);
+// disparity_calculation.py:286-287 (gray).
+#include "common.cuh"
+
+struct QMat { double q[16]; };
+
+template <typename T> __device__ __forceinline__ float to_f32(T v) { return (float)v; }
+
+// A.6:  P = Q * [x, y, d, 1]^T in fp64 ; out = float( double(float(P_c)) * (1.0 / P_w) )
+// fp contraction must stay off for bitwise parity with the CPU evaluation order.
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_reproject(const T* __restrict__ disp, int H, int W, QMat Q, float scale, int handle_missing,
+            const float* __restrict__ minv, float* __restrict__ xyz)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    if (x >= W) return;
+    const size_t i = ((size_t)blockIdx.z * H + y) * W + x;
+    float df = to_f32(disp[i]);
+    if (scale != 1.0f) df = __fmul_rn(df, scale);
+    const double d = (double)df;
+    double P[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        double a = __dmul_rn(Q.q[4 * k + 0], (double)x);
+        a = __dadd_rn(a, __dmul_rn(Q.q[4 * k + 1], (double)y));
+        a = __dadd_rn(a, __dmul_rn(Q.q[4 * k + 2], d));
+        P[k] = __dadd_rn(a, Q.q[4 * k + 3]);
+    }
+    const double iw = __ddiv_rn(1.0, P[3]);
+    float o0 = (float)__dmul_rn((double)(float)P[0], iw);
+    float o1 = (float)__dmul_rn((double)(float)P[1], iw);
+    float o2 = (float)__dmul_rn((double)(float)P[2], iw);
+    if (handle_missing && df == minv[blockIdx.z]) o2 = 10000.f;
+    float* o = xyz + i * 3;
+    o[0] = o0; o[1] = o1; o[2] = o2;
+}
+
+// per-image minimum of the (scaled) disparity for handleMissingValues
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_min_f32(const T* __restrict__ disp, size_t n, float scale, float* __restrict__ minv)
+{
+    const T* p = disp + (size_t)blockIdx.y * n;
+    float m = INFINITY;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        float v = to_f32(p[i]);
+        if (scale != 1.0f) v = __fmul_rn(v, scale);
+        m = fminf(m, v);
+    }
+    for (int o = 16; o > 0; o >>= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) {
+        // float atomic min through the monotone int mapping (values may be negative)
+        int bits = __float_as_int(m);
+        if (bits >= 0) atomicMin((int*)&minv[blockIdx.y], bits);
+        else atomicMax((unsigned int*)&minv[blockIdx.y], (unsigned int)bits);
+    }
+}
+
+template <typename T>
+static int reproject_t(const T* disp, int H, int W, int batch, const QMat& Q, float scale, int hm,
+                       float* scratch, float* xyz, cudaStream_t st)
+{
+    if (hm) {
+        if (!scratch) { b2s_set_error("reproject: handle_missing needs a scratch buffer of batch floats"); return B2S_E_INVALID; }
+        // +inf bit pattern as the neutral element
+        B2S_CUDA_CHECK(cudaMemsetAsync(scratch, 0x7f, (size_t)batch * sizeof(float), st));  // 0x7f7f7f7f = 3.39e38
+        dim3 g(64, batch);
+        k_min_f32<T><<<g, 256, 0, st>>>(disp, (size_t)H * W, scale, scratch);
+        B2S_LAUNCH_CHECK();
+    }
+    dim3 grid(b2s_cdiv(W, 256), H, batch);
+    k_reproject<T><<<grid, 256, 0, st>>>(disp, H, W, Q, scale, hm, scratch, xyz);
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}
+
+extern "C" int b2s_reproject(const void* disp, int dtype, int H, int W, int batch, const double* Q_host,
+                             float disp_scale, int handle_missing, float* scratch, float* xyz, void* stream)
+{
+    if (!disp || !xyz || !Q_host || H <= 0 || W <= 0 || batch <= 0) {
+        b2s_set_error("reproject: null pointer or empty image");
+        return B2S_E_INVALID;
+    }
+    QMat Q;
+    for (int i = 0; i < 16; i++) Q.q[i] = Q_host[i];
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (dtype) {
+    case B2S_DT_U8:  return reproject_t((const uint8_t*)disp, H, W, batch, Q, disp_scale, handle_missing, scratch, xyz, st);
+    case B2S_DT_I16: return reproject_t((const int16_t*)disp, H, W, batch, Q, disp_scale, handle_missing, scratch, xyz, st);
+    case B2S_DT_I32: return reproject_t((const int32_t*)disp, H, W, batch, Q, disp_scale, handle_missing, scratch, xyz, st);
+    case B2S_DT_F32: return reproject_t((const float*)disp, H, W, batch, Q, disp_scale, handle_missing, scratch, xyz, st);
+    }
+    b2s_set_error("reproject: disparity type must be CV_8U, CV_16S, CV_32S or CV_32F");
+    return B2S_E_INVALID;
+}
+
+// A.7: fixed-point bilinear gather, 5 fractional bits, 15-bit weights, constant-0 border
+template <int CN>
+__global__ void __launch_bounds__(256)
+k_remap(const uint8_t* __restrict__ src, int sH, int sW, const float* __restrict__ mapx,
+        const float* __restrict__ mapy, int H, int W, uint8_t* __restrict__ dst)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    if (x >= W) return;
+    const size_t m = (size_t)y * W + x;
+    const int sx = __float2int_rn(__fmul_rn(__ldg(mapx + m), 32.f));
+    const int sy = __float2int_rn(__fmul_rn(__ldg(mapy + m), 32.f));
+    const int ix = min(max(sx >> 5, -32768), 32767), fx = sx & 31;
+    const int iy = min(max(sy >> 5, -32768), 32767), fy = sy & 31;
+    const int w00 = min(32767, (32 - fx) * (32 - fy) * 32), w01 = fx * (32 - fy) * 32;
+    const int w10 = (32 - fx) * fy * 32, w11 = fx * fy * 32;
+    const uint8_t* s = src + (size_t)blockIdx.z * sH * sW * CN;
+    const bool x0 = ix >= 0 && ix < sW, x1 = ix + 1 >= 0 && ix + 1 < sW;
+    const bool y0 = iy >= 0 && iy < sH, y1 = iy + 1 >= 0 && iy + 1 < sH;
+    uint8_t* o = dst + ((size_t)blockIdx.z * H * W + m) * CN;
+#pragma unroll
+    for (int c = 0; c < CN; c++) {
+        int t00 = (y0 && x0) ? s[((size_t)iy * sW + ix) * CN + c] : 0;
+        int t01 = (y0 && x1) ? s[((size_t)iy * sW + ix + 1) * CN + c] : 0;
+        int t10 = (y1 && x0) ? s[((size_t)(iy + 1) * sW + ix) * CN + c] : 0;
+        int t11 = (y1 && x1) ? s[((size_t)(iy + 1) * sW + ix + 1) * CN + c] : 0;
+        o[c] = (uint8_t)((w00 * t00 + w01 * t01 + w10 * t10 + w11 * t11 + 16384) >> 15);
+    }
+}
+
+extern "C" int b2s_remap_u8(const uint8_t* src, int sH, int sW, int cn, const float* mapx, const float* mapy,
+                            int H, int W, int batch, uint8_t* dst, void* stream)
+{
+    if (!src || !mapx || !mapy || !dst || sH <= 0 || sW <= 0 || H <= 0 || W <= 0 || batch <= 0) {
+        b2s_set_error("remap: null pointer or empty image");
+        return B2S_E_INVALID;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    dim3 grid(b2s_cdiv(W, 256), H, batch);
+    if (cn == 1) k_remap<1><<<grid, 256, 0, st>>>(src, sH, sW, mapx, mapy, H, W, dst);
+    else if (cn == 3) k_remap<3><<<grid, 256, 0, st>>>(src, sH, sW, mapx, mapy, H, W, dst);
+    else { b2s_set_error("remap: 1 or 3 channels supported, got %d", cn); return B2S_E_UNSUPPORTED; }
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}
+
+// A.8
+__global__ void __launch_bounds__(256)
+k_bgr2gray(const uint8_t* __restrict__ bgr, size_t n, uint8_t* __restrict__ gray)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint8_t* p = bgr + 3 * i;
+    gray[i] = (uint8_t)((3735 * p[0] + 19235 * p[1] + 9798 * p[2] + 16384) >> 15);
+}
+
+extern "C" int b2s_bgr2gray(const uint8_t* bgr, size_t npixels, uint8_t* gray, void* stream)
+{
+    if (!bgr || !gray) { b2s_set_error("bgr2gray: null pointer"); return B2S_E_INVALID; }
+    if (npixels == 0) return B2S_OK;
+    k_bgr2gray<<<b2s_cdiv((long long)npixels, 256), 256, 0, (cudaStream_t)stream>>>(bgr, npixels, gray);
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}

@@ -1,0 +1,280 @@
+// sgbm_post.cu -- winner-take-all, uniqueness, sub-pixel, LR check,
+// 3x3 median (A.4) and speckle filter (A.5): the tail of cv2.StereoSGBM.compute
+// (reference call site stereo_vision/stereo_vision.py:178).
+#include "common.cuh"
+
+template <int R>
+__device__ __forceinline__ void load_regs_s(const uint16_t* p, uint32_t (&r)[R])
+{
+    if constexpr (R % 4 == 0) {
+#pragma unroll
+        for (int i = 0; i < R / 4; i++) {
+            uint4 v = __ldg(reinterpret_cast<const uint4*>(p) + i);
+            r[4 * i] = v.x; r[4 * i + 1] = v.y; r[4 * i + 2] = v.z; r[4 * i + 3] = v.w;
+        }
+    } else if constexpr (R % 2 == 0) {
+#pragma unroll
+        for (int i = 0; i < R / 2; i++) {
+            uint2 v = __ldg(reinterpret_cast<const uint2*>(p) + i);
+            r[2 * i] = v.x; r[2 * i + 1] = v.y;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < R; i++) r[i] = __ldg(reinterpret_cast<const uint32_t*>(p) + i);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// WTA: one G-lane group per computed pixel.  Writes the pre-LR-check disparity and
+// scatters (cost, x) into the per-row disp2 key array with atomicMin:
+//   key = minS << 16 | (0xffff - x)   ->  lowest cost wins, ties go to the largest x,
+// which is cv2's "strict > while x runs downward" rule, independent of thread order.
+// ---------------------------------------------------------------------------
+#define WTA_NT 256
+template <int R, int G>
+__global__ void __launch_bounds__(WTA_NT)
+k_wta(const uint16_t* __restrict__ S, SgbmEff e, int16_t* __restrict__ disp, uint32_t* __restrict__ disp2key)
+{
+    const int lane = threadIdx.x % G;
+    const long long gid = ((long long)blockIdx.x * WTA_NT + threadIdx.x) / G;
+    const long long total = (long long)e.batch * e.H * e.width1;
+    const bool active = gid < total;
+    const long long pid = active ? gid : 0;
+    const int x = (int)(pid % e.width1);
+    const long long by = pid / e.width1;               // b*H + y
+
+    uint32_t v[R];
+    load_regs_s<R>(S + (size_t)pid * e.Dp + (size_t)lane * 2 * R, v);
+
+    const int dbase = lane * 2 * R;
+    uint32_t key = 0xffffffffu;
+#pragma unroll
+    for (int i = 0; i < R; i++) {
+        int d0 = dbase + 2 * i;
+        uint32_t k0 = ((v[i] & 0xffffu) << 16) | (uint32_t)d0;
+        uint32_t k1 = (v[i] & 0xffff0000u) | (uint32_t)(d0 + 1);
+        if (d0 < e.D) key = min(key, k0);
+        if (d0 + 1 < e.D) key = min(key, k1);
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, o));
+    const int best = (int)(key & 0xffffu);
+    const int minS = (int)(key >> 16);
+
+    // uniqueness + neighbours of the winner
+    const int thr = minS * 100;
+    const int mul = 100 - e.uniq;
+    uint32_t bad = 0, sm1 = 0, sp1 = 0;
+#pragma unroll
+    for (int i = 0; i < R; i++) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            int d = dbase + 2 * i + h;
+            int val = h ? (int)(v[i] >> 16) : (int)(v[i] & 0xffffu);
+            if (d < e.D) {
+                int ad = d - best;
+                if ((ad > 1 || ad < -1) && val * mul < thr) bad = 1;
+                if (ad == -1) sm1 = (uint32_t)val;
+                if (ad == 1) sp1 = (uint32_t)val;
+            }
+        }
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) {
+        bad |= __shfl_xor_sync(0xffffffffu, bad, o);
+        sm1 |= __shfl_xor_sync(0xffffffffu, sm1, o);
+        sp1 |= __shfl_xor_sync(0xffffffffu, sp1, o);
+    }
+    if (!active || lane != 0) return;
+    int16_t* drow = disp + (size_t)by * e.W;
+    if (bad) { drow[x + e.minX1] = (int16_t)e.invalid; return; }
+    int x2 = x + e.minX1 - best - e.minD;
+    atomicMin(disp2key + (size_t)by * e.W + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
+    int dq = best * 16;
+    if (best > 0 && best < e.D - 1) {
+        int denom2 = max((int)sm1 + (int)sp1 - 2 * minS, 1);
+        dq += (((int)sm1 - (int)sp1) * 16 + denom2) / (denom2 * 2);
+    }
+    drow[x + e.minX1] = (int16_t)(dq + e.minD * 16);
+}
+
+// LR consistency check, in place; also fills the never-computed columns with INVALID.
+__global__ void __launch_bounds__(256)
+k_lrcheck(SgbmEff e, int16_t* __restrict__ disp, const uint32_t* __restrict__ disp2key)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= e.W) return;
+    const size_t row = ((size_t)blockIdx.z * e.H + blockIdx.y) * e.W;
+    if (x < e.minX1 || x >= e.maxX1) { disp[row + x] = (int16_t)e.invalid; return; }
+    const int d1 = disp[row + x];
+    if (d1 == e.invalid) return;
+    const int _d = d1 >> 4, d_ = (d1 + 15) >> 4;
+    const int _x = x - _d, x_ = x - d_;
+    bool fail = true;
+    {
+        if (!(0 <= _x && _x < e.W)) fail = false;
+        else {
+            uint32_t k = disp2key[row + _x];
+            // disp2 = best + minD of the winning x;  empty slots read as the scaled INVALID (cv2 quirk)
+            int v = (k == 0xffffffffu) ? e.invalid : ((0xffff - (int)(k & 0xffffu)) + e.minX1 - _x);
+            if (!(v >= e.minD && abs(v - _d) > e.lrmax)) fail = false;
+        }
+    }
+    if (fail) {
+        if (!(0 <= x_ && x_ < e.W)) fail = false;
+        else {
+            uint32_t k = disp2key[row + x_];
+            int v = (k == 0xffffffffu) ? e.invalid : ((0xffff - (int)(k & 0xffffu)) + e.minX1 - x_);
+            if (!(v >= e.minD && abs(v - d_) > e.lrmax)) fail = false;
+        }
+    }
+    if (fail) disp[row + x] = (int16_t)e.invalid;
+}
+
+template <int R, int G>
+static int launch_wta_rg(const uint16_t* S, const SgbmEff& e, int16_t* disp, uint32_t* disp2key, cudaStream_t st)
+{
+    long long groups = (long long)e.batch * e.H * e.width1;
+    k_wta<R, G><<<b2s_cdiv(groups * G, WTA_NT), WTA_NT, 0, st>>>(S, e, disp, disp2key);
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}
+
+int b2s_launch_wta(const uint16_t* S, const SgbmEff& e, int16_t* disp_raw, uint32_t* disp2key, cudaStream_t st)
+{
+    B2S_CUDA_CHECK(cudaMemsetAsync(disp2key, 0xff, (size_t)e.batch * e.H * e.W * sizeof(uint32_t), st));
+    int rc = B2S_E_UNSUPPORTED;
+#define WTA_CASE(RR, GG) if (e.R == RR && e.G == GG) rc = launch_wta_rg<RR, GG>(S, e, disp_raw, disp2key, st);
+    WTA_CASE(1, 8) WTA_CASE(2, 8) WTA_CASE(3, 8) WTA_CASE(4, 8) WTA_CASE(6, 8) WTA_CASE(8, 8)
+    WTA_CASE(12, 8) WTA_CASE(16, 8)
+    WTA_CASE(6, 32) WTA_CASE(8, 32) WTA_CASE(12, 32) WTA_CASE(16, 32)
+#undef WTA_CASE
+    if (rc != B2S_OK) {
+        if (rc == B2S_E_UNSUPPORTED) b2s_set_error("no WTA kernel for R=%d G=%d", e.R, e.G);
+        return rc;
+    }
+    dim3 grid(b2s_cdiv(e.W, 256), e.H, e.batch);
+    k_lrcheck<<<grid, 256, 0, st>>>(e, disp_raw, disp2key);
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}
+
+// ---------------------------------------------------------------------------
+// 3x3 median on int16, replicate border, out of place (cv2.medianBlur(disp, 3)).
+// 19-exchange median-of-9 network.
+// ---------------------------------------------------------------------------
+#define MSORT(a, b) { int _t = min(a, b); b = max(a, b); a = _t; }
+__global__ void __launch_bounds__(256)
+k_median3(const int16_t* __restrict__ src, int H, int W, int16_t* __restrict__ dst)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    if (x >= W) return;
+    const size_t base = (size_t)blockIdx.z * H * W;
+    const int xm = max(x - 1, 0), xp = min(x + 1, W - 1);
+    const int16_t* r0 = src + base + (size_t)max(y - 1, 0) * W;
+    const int16_t* r1 = src + base + (size_t)y * W;
+    const int16_t* r2 = src + base + (size_t)min(y + 1, H - 1) * W;
+    int p0 = r0[xm], p1 = r0[x], p2 = r0[xp];
+    int p3 = r1[xm], p4 = r1[x], p5 = r1[xp];
+    int p6 = r2[xm], p7 = r2[x], p8 = r2[xp];
+    MSORT(p1, p2) MSORT(p4, p5) MSORT(p7, p8) MSORT(p0, p1) MSORT(p3, p4) MSORT(p6, p7)
+    MSORT(p1, p2) MSORT(p4, p5) MSORT(p7, p8) MSORT(p0, p3) MSORT(p5, p8) MSORT(p4, p7)
+    MSORT(p3, p6) MSORT(p1, p4) MSORT(p2, p5) MSORT(p4, p7) MSORT(p4, p2) MSORT(p6, p4)
+    MSORT(p4, p2)
+    dst[base + (size_t)y * W + x] = (int16_t)p4;
+}
+
+int b2s_launch_median3(const int16_t* src, int H, int W, int batch, int16_t* dst, cudaStream_t st)
+{
+    dim3 grid(b2s_cdiv(W, 256), H, batch);
+    k_median3<<<grid, 256, 0, st>>>(src, H, W, dst);
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}
+
+// ---------------------------------------------------------------------------
+// filterSpeckles as parallel connected components (union-find with atomicMin roots).
+// cv2's sequential flood fill is order independent, so any exact
+// component labelling gives the same pixels removed.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ int uf_find(const int32_t* L, int i)
+{
+    int p = ((volatile const int32_t*)L)[i];
+    while (p != i) { i = p; p = ((volatile const int32_t*)L)[i]; }
+    return i;
+}
+
+__device__ __forceinline__ void uf_union(int32_t* L, int a, int b)
+{
+    bool done;
+    do {
+        a = uf_find(L, a);
+        b = uf_find(L, b);
+        if (a < b) { int old = atomicMin(&L[b], a); done = (old == b); b = old; }
+        else if (b < a) { int old = atomicMin(&L[a], b); done = (old == a); a = old; }
+        else done = true;
+    } while (!done);
+}
+
+__global__ void __launch_bounds__(256)
+k_speckle_init(const int16_t* __restrict__ img, size_t n, int newVal, int32_t* __restrict__ labels,
+               int32_t* __restrict__ counts)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    labels[i] = (img[i] != newVal) ? (int32_t)i : -1;
+    counts[i] = 0;
+}
+
+__global__ void __launch_bounds__(256)
+k_speckle_merge(const int16_t* __restrict__ img, int H, int W, int newVal, int maxDiff, int32_t* labels)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    if (x >= W) return;
+    const size_t i = ((size_t)blockIdx.z * H + y) * W + x;
+    const int v = img[i];
+    if (v == newVal) return;
+    if (x + 1 < W) { int w = img[i + 1]; if (w != newVal && abs(v - w) <= maxDiff) uf_union(labels, (int)i, (int)i + 1); }
+    if (y + 1 < H) { int w = img[i + W]; if (w != newVal && abs(v - w) <= maxDiff) uf_union(labels, (int)i, (int)i + W); }
+}
+
+__global__ void __launch_bounds__(256)
+k_speckle_count(size_t n, int32_t* labels, int32_t* counts)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int root = -1;
+    if (i < n && labels[i] >= 0) { root = uf_find(labels, (int)i); labels[i] = root; }
+    // one atomic per distinct root per warp
+    unsigned peers = __match_any_sync(0xffffffffu, root);
+    if (root >= 0 && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&counts[root], __popc(peers));
+}
+
+__global__ void __launch_bounds__(256)
+k_speckle_apply(int16_t* img, size_t n, int newVal, int maxSize, const int32_t* __restrict__ labels,
+                const int32_t* __restrict__ counts)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int r = labels[i];
+    if (r >= 0 && counts[r] <= maxSize) img[i] = (int16_t)newVal;
+}
+
+int b2s_launch_speckles(int16_t* img, int H, int W, int batch, int newVal, int maxSize, int maxDiff,
+                        int32_t* labels, int32_t* counts, cudaStream_t st)
+{
+    const size_t n = (size_t)batch * H * W;
+    if (n >= (size_t)1 << 31) { b2s_set_error("filterSpeckles: batch*H*W must be < 2^31"); return B2S_E_INVALID; }
+    const int nb = b2s_cdiv((long long)n, 256);
+    dim3 grid(b2s_cdiv(W, 256), H, batch);
+    k_speckle_init<<<nb, 256, 0, st>>>(img, n, newVal, labels, counts);
+    B2S_LAUNCH_CHECK();
+    k_speckle_merge<<<grid, 256, 0, st>>>(img, H, W, newVal, maxDiff, labels);
+    B2S_LAUNCH_CHECK();
+    k_speckle_count<<<nb, 256, 0, st>>>(n, labels, counts);
+    B2S_LAUNCH_CHECK();
+    k_speckle_apply<<<nb, 256, 0, st>>>(img, n, newVal, maxSize, labels, counts);
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}

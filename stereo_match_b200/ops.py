@@ -1,0 +1,142 @@
+"""Stand-alone stages with cv2 signatures: reprojectImageTo3D, remap, cvtColor(BGR2GRAY),
+medianBlur(ksize=3, int16) and filterSpeckles.  See engine.py for the array conventions."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import error
+from .engine import _to_device, _from_device, _ptr, _stream, INTER_LINEAR, COLOR_BGR2GRAY, CV_32F
+
+_DT = {torch.uint8: _lib.DT_U8, torch.int16: _lib.DT_I16, torch.int32: _lib.DT_I32, torch.float32: _lib.DT_F32}
+
+
+def reprojectImageTo3D(disparity, Q, _3dImage=None, handleMissingValues=False, ddepth=-1, *, disp_scale=1.0):
+    """cv2.reprojectImageTo3D (stereo_vision.py:209, disparity_calculation.py:302).
+
+    u8/int16/int32/float32 disparity is converted to float32 WITHOUT scaling, like cv2.
+    `disp_scale` (keyword only, extension) multiplies it on the device first, which fuses
+    project_points_3D's "/16.0".  Returns (H, W, 3) float32 ([B,H,W,3] for batched input).
+    """
+    if ddepth not in (-1, CV_32F):
+        raise error("reprojectImageTo3D: only ddepth=-1/CV_32F is supported", _lib.E_UNSUPPORTED)
+    d, kind = _to_device(disparity, "disparity")
+    if d.dtype not in _DT:
+        raise error("reprojectImageTo3D: stype == CV_8UC1 || stype == CV_16SC1 || stype == CV_32SC1 || stype == CV_32FC1")
+    Qh = np.ascontiguousarray(Q.detach().cpu().numpy() if isinstance(Q, torch.Tensor) else Q, dtype=np.float64)
+    if Qh.shape != (4, 4):
+        raise error("reprojectImageTo3D: Q.size() == Size(4,4)")
+    squeeze = d.dim() == 2
+    if squeeze:
+        d = d[None]
+    if d.dim() != 3:
+        raise error("reprojectImageTo3D: disparity must be (H, W) or (B, H, W)")
+    B, H, W = d.shape
+    out = torch.empty((B, H, W, 3), dtype=torch.float32, device=d.device)
+    scratch = torch.empty(B, dtype=torch.float32, device=d.device) if handleMissingValues else None
+    with torch.cuda.device(d.device):
+        _lib.check(_lib.load().b2s_reproject(
+            _ptr(d), _DT[d.dtype], H, W, B, Qh.ctypes.data_as(C.POINTER(C.c_double)), C.c_float(disp_scale),
+            int(bool(handleMissingValues)), _ptr(scratch) if scratch is not None else None, _ptr(out), _stream()))
+    if squeeze:
+        out = out[0]
+    res = _from_device(out, kind)
+    if _3dImage is not None:
+        if isinstance(_3dImage, np.ndarray):
+            _3dImage[...] = res
+        else:
+            _3dImage.copy_(out)
+        return _3dImage
+    return res
+
+
+def remap(src, map1, map2, interpolation=INTER_LINEAR, dst=None, borderMode=0, borderValue=0):
+    """cv2.remap(src, mapx, mapy, cv2.INTER_LINEAR), BORDER_CONSTANT 0 (rectified_img_cal.py:253-254;
+    SURVEY.md A.7).  src (H,W) / (H,W,3) uint8, or batched (B,H,W) is NOT inferred: pass
+    batched colour as (B,H,W,3) and batched gray as (B,H,W,1)."""
+    if interpolation != INTER_LINEAR:
+        raise error("remap: only INTER_LINEAR is supported", _lib.E_UNSUPPORTED)
+    if borderMode != 0 or (np.asarray(borderValue) != 0).any():
+        raise error("remap: only BORDER_CONSTANT with value 0 is supported", _lib.E_UNSUPPORTED)
+    s, kind = _to_device(src, "src")
+    mx, _ = _to_device(map1, "map1")
+    my, _ = _to_device(map2, "map2")
+    if s.dtype != torch.uint8:
+        raise error("remap: only uint8 images are supported", _lib.E_UNSUPPORTED)
+    if mx.dtype != torch.float32 or my.dtype != torch.float32 or mx.shape != my.shape or mx.dim() != 2:
+        raise error("remap: map1/map2 must be CV_32FC1 maps of the same size")
+    if s.dim() == 2:
+        B, sH, sW, cn, oshape = 1, s.shape[0], s.shape[1], 1, lambda H, W: (H, W)
+    elif s.dim() == 3:
+        B, sH, sW, cn, oshape = 1, s.shape[0], s.shape[1], s.shape[2], lambda H, W: (H, W, s.shape[2])
+    elif s.dim() == 4:
+        B, sH, sW, cn, oshape = s.shape[0], s.shape[1], s.shape[2], s.shape[3], lambda H, W: (s.shape[0], H, W, s.shape[3])
+    else:
+        raise error("remap: bad source shape")
+    H, W = mx.shape
+    out = torch.empty(oshape(H, W), dtype=torch.uint8, device=s.device)
+    with torch.cuda.device(s.device):
+        _lib.check(_lib.load().b2s_remap_u8(_ptr(s), sH, sW, cn, _ptr(mx), _ptr(my), H, W, B, _ptr(out), _stream()))
+    res = _from_device(out, kind)
+    if dst is not None:
+        if isinstance(dst, np.ndarray):
+            dst[...] = res
+        else:
+            dst.copy_(out)
+        return dst
+    return res
+
+
+def cvtColor(src, code):
+    """cv2.cvtColor(src, cv2.COLOR_BGR2GRAY) for uint8 (disparity_calculation.py:286-287)."""
+    if code != COLOR_BGR2GRAY:
+        raise error("cvtColor: only COLOR_BGR2GRAY is supported", _lib.E_UNSUPPORTED)
+    s, kind = _to_device(src, "src")
+    if s.dtype != torch.uint8 or s.dim() < 3 or s.shape[-1] != 3:
+        raise error("cvtColor: expected (..., 3) uint8 BGR")
+    out = torch.empty(s.shape[:-1], dtype=torch.uint8, device=s.device)
+    with torch.cuda.device(s.device):
+        _lib.check(_lib.load().b2s_bgr2gray(_ptr(s), out.numel(), _ptr(out), _stream()))
+    return _from_device(out, kind)
+
+
+def medianBlur(src, ksize):
+    """cv2.medianBlur(int16 image, 3), replicate border (the blur StereoSGBM.compute applies, A.4)."""
+    if ksize != 3:
+        raise error("medianBlur: only ksize=3 is supported", _lib.E_UNSUPPORTED)
+    s, kind = _to_device(src, "src")
+    if s.dtype != torch.int16:
+        raise error("medianBlur: only int16 images are supported", _lib.E_UNSUPPORTED)
+    squeeze = s.dim() == 2
+    if squeeze:
+        s = s[None]
+    B, H, W = s.shape
+    out = torch.empty_like(s)
+    with torch.cuda.device(s.device):
+        _lib.check(_lib.load().b2s_median3_i16(_ptr(s), H, W, B, _ptr(out), _stream()))
+    return _from_device(out[0] if squeeze else out, kind)
+
+
+def filterSpeckles(img, newVal, maxSpeckleSize, maxDiff, buf=None):
+    """cv2.filterSpeckles: in place for torch CUDA tensors; numpy arrays are updated in place too
+    and returned (cv2 returns (img, buf))."""
+    s, kind = _to_device(img, "img")
+    if s.dtype != torch.int16:
+        raise error("filterSpeckles: only int16 images are supported", _lib.E_UNSUPPORTED)
+    view = s[None] if s.dim() == 2 else s
+    B, H, W = view.shape
+    labels = torch.empty(B * H * W, dtype=torch.int32, device=s.device)
+    counts = torch.empty(B * H * W, dtype=torch.int32, device=s.device)
+    with torch.cuda.device(s.device):
+        _lib.check(_lib.load().b2s_filter_speckles(_ptr(view), H, W, B, int(newVal), int(maxSpeckleSize), int(maxDiff),
+                                                   _ptr(labels), _ptr(counts), _stream()))
+    if kind == "numpy":
+        img[...] = s.cpu().numpy()
+        return img, buf
+    if kind == "torch_cpu":
+        img.copy_(s.cpu())
+        return img, buf
+    if s.data_ptr() != img.data_ptr():
+        img.copy_(s)
+    return img, buf

@@ -1,0 +1,234 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the oracle, bit-exact.
+
+Checkers: oracle.port (C restatement, gives per-stage intermediates) and oracle.cv2ref
+(live cv2 4.13.0).  Sizes are chosen so the CPU side finishes in seconds; the full
+BASELINE.json shapes are in test_gpu_fullsize.py.
+"""
+import numpy as np
+import pytest
+import torch
+
+import stereo_match_b200 as sm
+from stereo_match_b200.synth import synth_pair, KITTI_Q
+from vectors import (SGBM_VECTORS, SGBM_ERROR_VECTORS, SGBM_UNPINNED_VECTORS, BM_VECTORS, sgbm_kwargs, sgbm_pair)
+
+pytestmark = pytest.mark.gpu
+
+
+def _ids(vs):
+    return ["-".join(str(x) for x in v[:5]) + ("-m%d" % v[10] if len(v) > 10 else "") for v in vs]
+
+
+@pytest.mark.parametrize("i,v", list(enumerate(SGBM_VECTORS)), ids=_ids(SGBM_VECTORS))
+def test_sgbm_matches_oracle(i, v, port, cv2ref):
+    l, r = sgbm_pair(i, v)
+    kw = sgbm_kwargs(v)
+    want = port.sgbm_compute(l, r, **kw)
+    assert np.array_equal(want, cv2ref.sgbm_compute(l, r, **kw)), "oracle port disagrees with cv2"
+    m = sm.StereoSGBM_create(**kw)
+    got = m.compute(l, r)
+    assert got.dtype == np.int16 and got.shape == l.shape
+    assert np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
+
+
+@pytest.mark.parametrize("i", [1, 7, 11, 13, 15])
+def test_sgbm_volumes_match_oracle(i, port):
+    """Stage taps: raw block cost and aggregated S against the restatement."""
+    v = SGBM_VECTORS[i]
+    l, r = sgbm_pair(i, v)
+    kw = sgbm_kwargs(v)
+    _, Cw, Sw, _ = port.sgbm_compute(l, r, want_volumes=True, **kw)
+    m = sm.StereoSGBM_create(**kw)
+    m.compute(torch.from_numpy(l).cuda(), torch.from_numpy(r).cuda())
+    cost, S, g = m.debug_volumes(1, l.shape[0], l.shape[1])
+    D = kw["numDisparities"]
+    cost = cost[0, :, :, :D].cpu().numpy().astype(np.int32) & 0xffff
+    S = S[0, :, :, :D].cpu().numpy()
+    assert np.array_equal(cost + g["P2"], Cw.astype(np.int32)), "block cost differs"
+    assert np.array_equal(S, Sw), "aggregated S differs"
+
+
+def test_sgbm_batch_equals_singles(cv2ref):
+    """Pairs are independent: a batched call equals per-pair calls (and cv2)."""
+    kw = sgbm_kwargs(SGBM_VECTORS[3])
+    pairs = [synth_pair(120, 70, 32, seed=s) for s in range(5)]
+    L = torch.from_numpy(np.stack([p[0] for p in pairs])).cuda()
+    R = torch.from_numpy(np.stack([p[1] for p in pairs])).cuda()
+    m = sm.StereoSGBM_create(**kw)
+    out = m.compute(L, R)
+    assert isinstance(out, torch.Tensor) and out.is_cuda and out.shape == L.shape
+    for k, (l, r) in enumerate(pairs):
+        assert np.array_equal(out[k].cpu().numpy(), cv2ref.sgbm_compute(l, r, **kw))
+
+
+def test_sgbm_idempotent_and_handle_reuse(cv2ref):
+    """Same handle, different shapes and parameters in sequence; results never depend on history."""
+    m = sm.StereoSGBM_create(**sgbm_kwargs(SGBM_VECTORS[0]))
+    for i in (0, 7, 2, 0):
+        v = SGBM_VECTORS[i]
+        kw = sgbm_kwargs(v)
+        for k, val in kw.items():
+            getattr(m, "set" + k[0].upper() + k[1:])(val)
+        l, r = sgbm_pair(i, v)
+        assert np.array_equal(m.compute(l, r), cv2ref.sgbm_compute(l, r, **kw))
+
+
+@pytest.mark.parametrize("v", SGBM_ERROR_VECTORS, ids=_ids(SGBM_ERROR_VECTORS))
+def test_sgbm_rejects_what_cv2_rejects(v, cv2ref):
+    l, r = sgbm_pair(0, v)
+    import cv2
+    with pytest.raises(cv2.error):
+        cv2ref.sgbm_compute(l, r, **sgbm_kwargs(v))
+    with pytest.raises(sm.error, match="too small"):
+        sm.StereoSGBM_create(**sgbm_kwargs(v)).compute(l, r)
+
+
+def test_sgbm_bad_inputs():
+    m = sm.StereoSGBM_create(numDisparities=16, blockSize=5)
+    l, r = synth_pair(64, 32, 16, seed=0)
+    with pytest.raises(sm.error, match="left.size"):
+        m.compute(l, r[:, :-1])
+    with pytest.raises(sm.error, match="CV_8U"):
+        m.compute(l.astype(np.int16), r.astype(np.int16))
+    with pytest.raises(sm.error):
+        sm.StereoSGBM_create(numDisparities=16, mode=sm.STEREO_SGBM_MODE_SGBM_3WAY).compute(l, r)
+
+
+@pytest.mark.parametrize("v", SGBM_UNPINNED_VECTORS, ids=_ids(SGBM_UNPINNED_VECTORS))
+def test_sgbm_flags_unpinned_domain(v):
+    l, r = sgbm_pair(9, v)
+    m = sm.StereoSGBM_create(**sgbm_kwargs(v))
+    m.compute(l, r)
+    assert m.overflowed()
+    m2 = sm.StereoSGBM_create(**sgbm_kwargs(SGBM_VECTORS[0]))
+    m2.compute(*sgbm_pair(0, SGBM_VECTORS[0]))
+    assert not m2.overflowed()
+
+
+@pytest.mark.parametrize("i,v", list(enumerate(BM_VECTORS)), ids=_ids(BM_VECTORS))
+def test_bm_matches_oracle(i, v, port, cv2ref):
+    w, h, D, bs, setters = v
+    l, r = synth_pair(w, h, D, seed=200 + i)
+    want = cv2ref.bm_compute(l, r, D, bs, **setters)
+    assert np.array_equal(want, port.bm_compute(l, r, D, bs, **setters))
+    m = sm.StereoBM_create(numDisparities=D, blockSize=bs)
+    for k, val in setters.items():
+        getattr(m, "set" + k[0].upper() + k[1:])(val)
+    got = m.compute(l, r)
+    assert np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
+
+
+def test_bm_errors():
+    l, r = synth_pair(64, 32, 16, seed=0)
+    with pytest.raises(sm.error, match="divisible by 16"):
+        sm.StereoBM_create(numDisparities=24, blockSize=5).compute(l, r)
+    with pytest.raises(sm.error, match="odd"):
+        sm.StereoBM_create(numDisparities=16, blockSize=6).compute(l, r)
+    with pytest.raises(sm.error, match="CV_8UC1"):
+        sm.StereoBM_create(numDisparities=16, blockSize=5).compute(np.dstack([l] * 3), np.dstack([r] * 3))
+
+
+@pytest.mark.parametrize("shape", [(37, 53), (1, 1), (1, 9), (9, 1), (375, 1242)])
+def test_median3(shape, cv2ref):
+    rng = np.random.default_rng(1)
+    img = rng.integers(-16, 2048, shape).astype(np.int16)
+    assert np.array_equal(sm.medianBlur(img, 3), cv2ref.median3(img))
+
+
+@pytest.mark.parametrize("size,diff", [(0, 0), (10, 16), (100, 32), (400, 48)])
+def test_filter_speckles(size, diff, cv2ref, port):
+    rng = np.random.default_rng(2)
+    for s in range(4):
+        img = (rng.integers(0, 40, (60, 80)) * 16).astype(np.int16)
+        img[rng.random((60, 80)) < 0.3] = -16
+        if s == 3:
+            img[:] = 160            # one component covering the image
+        want = cv2ref.filter_speckles(img, -16, size, diff)
+        assert np.array_equal(want, port.filter_speckles(img, -16, size, diff))
+        got = torch.from_numpy(img.copy()).cuda()
+        sm.filterSpeckles(got, -16, size, diff)
+        assert np.array_equal(got.cpu().numpy(), want)
+
+
+def test_filter_speckles_batched(cv2ref):
+    rng = np.random.default_rng(3)
+    imgs = (rng.integers(0, 30, (3, 40, 50)) * 16).astype(np.int16)
+    imgs[rng.random(imgs.shape) < 0.3] = -16
+    got = torch.from_numpy(imgs.copy()).cuda()
+    sm.filterSpeckles(got, -16, 20, 32)
+    for k in range(3):   # components must not leak across images of a batch
+        assert np.array_equal(got[k].cpu().numpy(), cv2ref.filter_speckles(imgs[k], -16, 20, 32))
+
+
+def test_reproject_bitwise(cv2ref):
+    rng = np.random.default_rng(4)
+    d16 = rng.integers(-16, 2048, (375, 1242)).astype(np.int16)
+    d16[0, :5] = 0                                           # W = 0 -> +-inf / NaN
+    Qh = np.float32([[1, 0, 0, -360], [0, -1, 0, 640], [0, 0, 0, -1164], [0, 0, 1, 0]])   # disparity_calculation.py:293-299
+    for Q in (KITTI_Q, Qh):
+        for d in (d16, d16.astype(np.float32) / 16, d16.astype(np.int32), (d16 & 0xff).astype(np.uint8)):
+            for hm in (False, True):
+                want = cv2ref.reproject(d, Q, hm)
+                got = sm.reprojectImageTo3D(d, Q, handleMissingValues=hm)
+                assert got.dtype == np.float32 and got.shape == want.shape
+                assert np.array_equal(got.view(np.uint32), want.view(np.uint32))   # bitwise, incl. inf/NaN
+                # the stated tolerance of north_star: <= 1e-5 relative on finite entries
+                fin = np.isfinite(want)
+                assert np.all(np.abs(got[fin] - want[fin]) <= 1e-5 * np.maximum(np.abs(want[fin]), 1e-30))
+
+
+def test_project_points_3d_matches_reference_semantics(cv2ref):
+    """stereo_vision.py:203-209: /16 then reprojectImageTo3D with a float32 Q."""
+    rng = np.random.default_rng(5)
+    d16 = rng.integers(-16, 2048, (60, 80)).astype(np.int16)
+    want = cv2ref.reproject(d16.astype(np.float32) / 16.0, KITTI_Q.astype(np.float32))
+    got = sm.project_points_3D(d16, KITTI_Q)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+def test_remap_and_gray(cv2ref):
+    rng = np.random.default_rng(6)
+    mx, my = cv2ref.kitti_rect_maps()
+    img3 = rng.integers(0, 256, (375, 1242, 3), dtype=np.uint8)
+    img1 = np.ascontiguousarray(img3[..., 0])
+    rx = (rng.random((200, 300), dtype=np.float32) * (1242 + 6) - 3).astype(np.float32)
+    ry = (rng.random((200, 300), dtype=np.float32) * (375 + 6) - 3).astype(np.float32)
+    for src in (img3, img1):
+        assert np.array_equal(sm.remap(src, mx, my, sm.INTER_LINEAR), cv2ref.remap(src, mx, my))
+        assert np.array_equal(sm.remap(src, rx, ry, sm.INTER_LINEAR), cv2ref.remap(src, rx, ry))
+    assert np.array_equal(sm.cvtColor(img3, sm.COLOR_BGR2GRAY), cv2ref.bgr2gray(img3))
+    batch = np.stack([img3, img3[::-1].copy()])
+    out = sm.remap(batch, mx, my, sm.INTER_LINEAR)
+    assert np.array_equal(out[1], cv2ref.remap(batch[1], mx, my))
+
+
+def test_compute_disparity_surface(cv2ref):
+    """The reference's compute_disparity (stereo_vision.py:132-184) with settings.ini values."""
+    settings = sm.parse_config_file(None)
+    settings.update(window_size=5, num_disparities=64)
+    l, r = synth_pair(200, 80, 64, seed=11)
+    displ, filtered = sm.compute_disparity(l, r, settings)
+    want = cv2ref.sgbm_compute(l, r, minDisparity=0, numDisparities=64, blockSize=5, P1=600, P2=2400, disp12MaxDiff=1,
+                               uniquenessRatio=15, speckleWindowSize=0, speckleRange=2, preFilterCap=63)
+    assert np.array_equal(displ, want) and filtered is None
+    with pytest.raises(RuntimeError, match="Method not supported"):
+        sm.compute_disparity(l, r, settings, method="ELAS")
+    settings["num_disparities"] = 32
+    displ_bm, _ = sm.compute_disparity(l, r, settings, method="BM")
+    assert np.array_equal(displ_bm, cv2ref.bm_compute(l, r, 32, 5))
+    # right-view matcher = plain SGBM over the mirrored range, compute(right, left)
+    _, _, dispr = sm.compute_disparity(l, r, settings, return_right=True)
+    want_r = cv2ref.sgbm_compute(r, l, minDisparity=-31, numDisparities=32, blockSize=5, P1=600, P2=2400,
+                                 disp12MaxDiff=1000000, uniquenessRatio=0, speckleWindowSize=0, speckleRange=2,
+                                 preFilterCap=63)
+    assert np.array_equal(dispr, want_r)
+
+
+def test_launch_counter_and_library_loaded():
+    from stereo_match_b200 import _lib
+    before = _lib.load().b2s_launch_count()
+    l, r = synth_pair(96, 64, 16, seed=0)
+    sm.StereoSGBM_create(numDisparities=16, blockSize=5).compute(l, r)
+    assert _lib.load().b2s_launch_count() - before >= 10
+    with open("/proc/self/maps") as f:
+        assert "libb2stereo.so" in f.read()

@@ -1,0 +1,70 @@
+"""Parity vectors shared by the oracle tests and the GPU parity tests."""
+from stereo_match_b200.synth import synth_pair
+
+# (w, h, minD, D, blockSize, P1, P2, disp12MaxDiff, preFilterCap, uniquenessRatio, mode, speckleWindow, speckleRange)
+SGBM_VECTORS = [
+    (96, 64, 0, 16, 5, 600, 2400, 1, 63, 15, 0, 0, 0),
+    (96, 64, 0, 16, 5, 600, 2400, 1, 63, 15, 1, 0, 0),
+    (120, 70, 0, 32, 3, 72, 288, 1, 63, 10, 0, 0, 0),
+    (120, 70, 0, 32, 7, 72, 288, 2, 31, 0, 1, 0, 0),
+    (131, 77, 4, 32, 9, 100, 1000, 1, 0, 5, 1, 0, 0),
+    (131, 77, -8, 32, 5, 100, 1000, -1, 10, 5, 0, 0, 0),
+    (131, 77, -40, 32, 5, 100, 1000, 1, 10, 5, 1, 0, 0),
+    (150, 90, 0, 48, 11, 968, 3872, 1, 63, 15, 1, 50, 2),
+    (150, 90, 0, 48, 1, 8, 32, 1, 63, 15, 0, 100, 1),
+    (150, 90, 0, 16, 11, 50, 200, 20, 1, 0, 0, 0, 0),       # large block, inside the guaranteed domain
+    (150, 90, 0, 48, 5, 0, 0, 0, 0, -1, 0, 0, 0),           # every silent fallback
+    (150, 90, 0, 48, 5, 3000, 12000, 1, 63, 15, 1, 0, 0),   # int16 pressure
+    (150, 90, 0, 24, 5, 100, 400, 1, 63, 15, 0, 0, 0),      # D not a multiple of 16
+    (150, 90, 0, 40, 5, 100, 400, 1, 63, 15, 1, 0, 0),
+    (200, 60, 0, 160, 5, 600, 2400, 1, 63, 15, 0, 0, 2),    # settings.ini as shipped (D=160)
+    (330, 40, 0, 272, 3, 72, 288, 1, 63, 10, 1, 0, 0),      # D > 256: 32-lane kernels
+    (70, 40, 0, 64, 5, 600, 2400, 1, 63, 15, 1, 0, 0),      # width1 = 6
+    (40, 3, 0, 16, 5, 600, 2400, 1, 63, 15, 1, 0, 0),       # H smaller than the block
+    (1, 1, -1, 1, 1, 8, 32, 1, 63, 15, 0, 0, 0),            # one pixel, one disparity
+]
+
+
+# cv2 4.13.0 raises cv2.error for these (width - maxD <= blockSize/2, stereosgbm.cpp:511)
+SGBM_ERROR_VECTORS = [
+    (50, 30, 0, 64, 5, 600, 2400, 1, 63, 15, 0, 0, 0),
+    (66, 30, 0, 64, 5, 600, 2400, 1, 63, 15, 1, 0, 0),
+]
+
+# outside the guaranteed-parity domain (cv2's own SIMD and scalar code disagree there,
+# SURVEY.md A.0): the engine must raise its overflow flag.  disparity_test.py:165-177
+SGBM_UNPINNED_VECTORS = [
+    (150, 90, 0, 16, 23, 222, 887, 20, 1, 0, 0, 0, 0),
+]
+
+
+def sgbm_kwargs(v):
+    w, h, minD, D, bs, P1, P2, lr, cap, uq, mode, spw, spr = v
+    return dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=P1, P2=P2, disp12MaxDiff=lr,
+                preFilterCap=cap, uniquenessRatio=uq, speckleWindowSize=spw, speckleRange=spr, mode=mode)
+
+
+def sgbm_pair(i, v):
+    w, h, minD, D = v[:4]
+    return synth_pair(w, h, max(D + minD, 8), seed=100 + i)
+
+
+# (w, h, D, blockSize, setters)
+BM_VECTORS = [
+    (100, 60, 16, 5, {}),
+    (100, 61, 16, 7, {}),                                   # odd height
+    (140, 80, 32, 15, {}),
+    (140, 80, 32, 9, dict(preFilterCap=63, textureThreshold=0, uniquenessRatio=0)),
+    (90, 50, 64, 21, {}),
+    (40, 30, 32, 5, {}),                                    # a handful of valid columns
+    (30, 30, 32, 5, {}),                                    # no valid column
+]
+
+# full-size configurations of BASELINE.json
+CFG1 = dict(w=640, h=480, seed=1, kw=dict(minDisparity=0, numDisparities=64, blockSize=5, P1=600, P2=2400,
+            disp12MaxDiff=1, uniquenessRatio=15, speckleWindowSize=0, speckleRange=2, preFilterCap=63, mode=0))
+CFG2 = dict(w=1280, h=720, seed=2, D=128, bs=15)
+CFG3 = dict(w=1242, h=375, seed=1, kw=dict(minDisparity=0, numDisparities=128, blockSize=5, P1=600, P2=2400,
+            disp12MaxDiff=1, uniquenessRatio=15, speckleWindowSize=100, speckleRange=2, preFilterCap=63, mode=1))
+CFG4 = dict(w=2864, h=1988, seed=4, kw=dict(minDisparity=0, numDisparities=256, blockSize=5, P1=600, P2=2400,
+            disp12MaxDiff=1, uniquenessRatio=15, speckleWindowSize=100, speckleRange=2, preFilterCap=63, mode=1))
