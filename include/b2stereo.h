@@ -123,6 +123,15 @@ B2S_API int b2s_sgbm_debug_volumes(b2s_handle h, uint16_t* cost_out, uint16_t* S
    are unpinned (they may still match).  Synchronises the stream. */
 B2S_API int b2s_sgbm_overflow_flag(b2s_handle h, int* flag_host);
 
+/* opt-in stage timing for bench.py: when enabled, compute records CUDA events on its
+   stream between stages; b2s_sgbm_stage_ms waits for the last compute and writes the
+   B2S_NSTAGES stage durations (milliseconds) to a HOST array:
+   0 descriptors, 1 cost volume, 2 path aggregation (all directions), 3 WTA + LR check,
+   4 median, 5 speckle filter. */
+#define B2S_NSTAGES 6
+B2S_API int b2s_sgbm_enable_timing(b2s_handle h, int on);
+B2S_API int b2s_sgbm_stage_ms(b2s_handle h, float* ms_host);
+
 /* ---- StereoBM ------------------------------------------------------------ */
 B2S_API int b2s_bm_create(const b2s_bm_params* params, b2s_handle* out);
 B2S_API int b2s_bm_compute(b2s_handle h, const uint8_t* left, const uint8_t* right,

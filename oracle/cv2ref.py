@@ -48,8 +48,6 @@ def bgr2gray(bgr):
 
 
 def kitti_rect_maps(w=1242, h=375):
-    """cfg5 rectification maps, SURVEY.md 8(d)."""
-    K = np.array([[721.5377, 0, 609.5593], [0, 721.5377, 172.854], [0, 0, 1]], np.float64)
-    dist = np.array([-0.05, 0.01, 5e-4, -3e-4, 0], np.float64)
-    R, _ = cv2.Rodrigues(np.array([0.002, -0.004, 0.003], np.float64))
-    return cv2.initUndistortRectifyMap(K, dist, R, K, (w, h), cv2.CV_32FC1)
+    """cfg5 rectification maps, SURVEY.md 8(d) (shared input generator)."""
+    from stereo_match_b200.synth import kitti_rect_maps as f
+    return f(w, h)

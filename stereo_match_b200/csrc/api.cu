@@ -37,6 +37,10 @@ struct b2s_matcher {
     const uint16_t* last_S = nullptr;
     size_t last_elems = 0;
     cudaStream_t last_stream = nullptr;
+    // opt-in stage timing: events recorded on the compute stream between stages
+    bool timing = false;
+    cudaEvent_t ev[B2S_NSTAGES + 1] = {};
+    bool ev_valid = false;
 };
 
 static size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
@@ -206,18 +210,29 @@ extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t
     uint32_t* key = (uint32_t*)(ws + l.key);
 
     B2S_CUDA_CHECK(cudaMemsetAsync(h->flag, 0, sizeof(int), st));
+    h->ev_valid = false;
+#define B2S_MARK(i) do { if (h->timing) B2S_CUDA_CHECK(cudaEventRecord(h->ev[i], st)); } while (0)
+    B2S_MARK(0);
     if ((rc = b2s_launch_descriptors(left, e, descL, st))) return rc;
     if ((rc = b2s_launch_descriptors(right, e, descR, st))) return rc;
+    B2S_MARK(1);
     if ((rc = b2s_launch_cost(descL, descR, e, cost, h->flag, st))) return rc;
+    B2S_MARK(2);
     for (int k = 0; k < e.ndirs; k++)
         if ((rc = b2s_launch_aggregate(cost, S, e, k, k == 0, st))) return rc;
+    B2S_MARK(3);
     if ((rc = b2s_launch_wta(S, e, raw, key, st))) return rc;
+    B2S_MARK(4);
     if ((rc = b2s_launch_median3(raw, H, W, batch, disp, st))) return rc;
+    B2S_MARK(5);
     if (speckle) {
         rc = b2s_launch_speckles(disp, H, W, batch, e.invalid, h->sp.speckleWindowSize, 16 * h->sp.speckleRange,
                                  (int32_t*)(ws + l.labels), (int32_t*)(ws + l.counts), st);
         if (rc) return rc;
     }
+    B2S_MARK(6);
+#undef B2S_MARK
+    h->ev_valid = h->timing;
     h->last_cost = cost; h->last_S = S; h->last_stream = st;
     h->last_elems = (size_t)batch * H * e.width1 * e.Dp;
     return B2S_OK;
@@ -299,9 +314,29 @@ extern "C" int b2s_bm_compute(b2s_handle h, const uint8_t* left, const uint8_t* 
     return B2S_OK;
 }
 
+extern "C" int b2s_sgbm_enable_timing(b2s_handle h, int on)
+{
+    if (!h || h->kind != 0) { b2s_set_error("enable_timing: bad handle"); return B2S_E_INVALID; }
+    if (on && !h->ev[0])
+        for (int i = 0; i <= B2S_NSTAGES; i++) B2S_CUDA_CHECK(cudaEventCreate(&h->ev[i]));
+    h->timing = on != 0;
+    h->ev_valid = false;
+    return B2S_OK;
+}
+
+extern "C" int b2s_sgbm_stage_ms(b2s_handle h, float* ms_host)
+{
+    if (!h || h->kind != 0 || !ms_host) { b2s_set_error("stage_ms: bad argument"); return B2S_E_INVALID; }
+    if (!h->ev_valid) { b2s_set_error("stage_ms: no timed compute on this handle (call b2s_sgbm_enable_timing first)"); return B2S_E_INVALID; }
+    B2S_CUDA_CHECK(cudaEventSynchronize(h->ev[B2S_NSTAGES]));
+    for (int i = 0; i < B2S_NSTAGES; i++) B2S_CUDA_CHECK(cudaEventElapsedTime(&ms_host[i], h->ev[i], h->ev[i + 1]));
+    return B2S_OK;
+}
+
 extern "C" void b2s_destroy(b2s_handle h)
 {
     if (!h) return;
+    for (int i = 0; i <= B2S_NSTAGES; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     if (h->ws) cudaFree(h->ws);
     if (h->flag) cudaFree(h->flag);
     delete h;

@@ -140,6 +140,17 @@ class StereoSGBM(_Matcher):
         _lib.check(_lib.load().b2s_sgbm_overflow_flag(self._h, C.byref(f)))
         return bool(f.value)
 
+    STAGES = ("descriptors", "cost", "aggregate", "wta_lr", "median", "speckle")
+
+    def enable_timing(self, on=True):
+        _lib.check(_lib.load().b2s_sgbm_enable_timing(self._h, int(bool(on))))
+
+    def stage_ms(self):
+        """Per-stage device time of the last compute (CUDA events on its stream)."""
+        ms = (C.c_float * len(self.STAGES))()
+        _lib.check(_lib.load().b2s_sgbm_stage_ms(self._h, ms))
+        return dict(zip(self.STAGES, [float(v) for v in ms]))
+
     def debug_volumes(self, B, H, W):
         """(cost, S, geometry) of the last compute; torch int16 views of the uint16 volumes
         [B, H, width1, Dp] (test tap)."""

@@ -32,3 +32,13 @@ def synth_pair(w, h, maxd, seed, noise=2.0):
     right += rng.normal(0.0, noise, right.shape).astype(np.float32)
     right = np.clip(np.rint(right), 0, 255).astype(np.uint8)
     return left, right
+
+
+def kitti_rect_maps(w=1242, h=375):
+    """Rectification maps of cfg5: float32 mapx, mapy from a mild distortion
+    plus a small rotation.  Input generation only (cv2 used as a calibration library)."""
+    import cv2
+    K = np.array([[721.5377, 0, 609.5593], [0, 721.5377, 172.854], [0, 0, 1]], np.float64)
+    dist = np.array([-0.05, 0.01, 5e-4, -3e-4, 0], np.float64)
+    R, _ = cv2.Rodrigues(np.array([0.002, -0.004, 0.003], np.float64))
+    return cv2.initUndistortRectifyMap(K, dist, R, K, (w, h), cv2.CV_32FC1)
