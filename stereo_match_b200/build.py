@@ -54,7 +54,7 @@ def build(force=False, verbose=False):
         list(ex.map(compile_one, jobs))
     objs = [os.path.join(OBJ, s.replace(".cu", ".o")) for s in SOURCES]
     if force or jobs or _stale(LIB, objs):
-        subprocess.check_call([_nvcc(), "-shared", "-o", LIB] + objs + ["-lcudart"])
+        subprocess.check_call([_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB] + objs + ["-lcudart"])
     return LIB
 
 
