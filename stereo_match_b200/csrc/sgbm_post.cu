@@ -1,5 +1,5 @@
 // sgbm_post.cu -- winner-take-all, uniqueness, sub-pixel, LR check,
-// 3x3 median (A.4) and speckle filter (A.5): the tail of cv2.StereoSGBM.compute
+// and the 3x3 median (A.4): the tail of cv2.StereoSGBM.compute
 // (reference call site stereo_vision/stereo_vision.py:178).
 #include "common.cuh"
 
@@ -193,88 +193,3 @@ int b2s_launch_median3(const int16_t* src, int H, int W, int batch, int16_t* dst
     return B2S_OK;
 }
 
-// ---------------------------------------------------------------------------
-// filterSpeckles as parallel connected components (union-find with atomicMin roots).
-// cv2's sequential flood fill is order independent, so any exact
-// component labelling gives the same pixels removed.
-// ---------------------------------------------------------------------------
-__device__ __forceinline__ int uf_find(const int32_t* L, int i)
-{
-    int p = ((volatile const int32_t*)L)[i];
-    while (p != i) { i = p; p = ((volatile const int32_t*)L)[i]; }
-    return i;
-}
-
-__device__ __forceinline__ void uf_union(int32_t* L, int a, int b)
-{
-    bool done;
-    do {
-        a = uf_find(L, a);
-        b = uf_find(L, b);
-        if (a < b) { int old = atomicMin(&L[b], a); done = (old == b); b = old; }
-        else if (b < a) { int old = atomicMin(&L[a], b); done = (old == a); a = old; }
-        else done = true;
-    } while (!done);
-}
-
-__global__ void __launch_bounds__(256)
-k_speckle_init(const int16_t* __restrict__ img, size_t n, int newVal, int32_t* __restrict__ labels,
-               int32_t* __restrict__ counts)
-{
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    labels[i] = (img[i] != newVal) ? (int32_t)i : -1;
-    counts[i] = 0;
-}
-
-__global__ void __launch_bounds__(256)
-k_speckle_merge(const int16_t* __restrict__ img, int H, int W, int newVal, int maxDiff, int32_t* labels)
-{
-    const int x = blockIdx.x * blockDim.x + threadIdx.x;
-    const int y = blockIdx.y;
-    if (x >= W) return;
-    const size_t i = ((size_t)blockIdx.z * H + y) * W + x;
-    const int v = img[i];
-    if (v == newVal) return;
-    if (x + 1 < W) { int w = img[i + 1]; if (w != newVal && abs(v - w) <= maxDiff) uf_union(labels, (int)i, (int)i + 1); }
-    if (y + 1 < H) { int w = img[i + W]; if (w != newVal && abs(v - w) <= maxDiff) uf_union(labels, (int)i, (int)i + W); }
-}
-
-__global__ void __launch_bounds__(256)
-k_speckle_count(size_t n, int32_t* labels, int32_t* counts)
-{
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int root = -1;
-    if (i < n && labels[i] >= 0) { root = uf_find(labels, (int)i); labels[i] = root; }
-    // one atomic per distinct root per warp
-    unsigned peers = __match_any_sync(0xffffffffu, root);
-    if (root >= 0 && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&counts[root], __popc(peers));
-}
-
-__global__ void __launch_bounds__(256)
-k_speckle_apply(int16_t* img, size_t n, int newVal, int maxSize, const int32_t* __restrict__ labels,
-                const int32_t* __restrict__ counts)
-{
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    int r = labels[i];
-    if (r >= 0 && counts[r] <= maxSize) img[i] = (int16_t)newVal;
-}
-
-int b2s_launch_speckles(int16_t* img, int H, int W, int batch, int newVal, int maxSize, int maxDiff,
-                        int32_t* labels, int32_t* counts, cudaStream_t st)
-{
-    const size_t n = (size_t)batch * H * W;
-    if (n >= (size_t)1 << 31) { b2s_set_error("filterSpeckles: batch*H*W must be < 2^31"); return B2S_E_INVALID; }
-    const int nb = b2s_cdiv((long long)n, 256);
-    dim3 grid(b2s_cdiv(W, 256), H, batch);
-    k_speckle_init<<<nb, 256, 0, st>>>(img, n, newVal, labels, counts);
-    B2S_LAUNCH_CHECK();
-    k_speckle_merge<<<grid, 256, 0, st>>>(img, H, W, newVal, maxDiff, labels);
-    B2S_LAUNCH_CHECK();
-    k_speckle_count<<<nb, 256, 0, st>>>(n, labels, counts);
-    B2S_LAUNCH_CHECK();
-    k_speckle_apply<<<nb, 256, 0, st>>>(img, n, newVal, maxSize, labels, counts);
-    B2S_LAUNCH_CHECK();
-    return B2S_OK;
-}

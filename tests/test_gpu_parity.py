@@ -232,3 +232,26 @@ def test_launch_counter_and_library_loaded():
     assert _lib.load().b2s_launch_count() - before >= 10
     with open("/proc/self/maps") as f:
         assert "libb2stereo.so" in f.read()
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_filter_speckles_stress(seed, cv2ref):
+    """Disparity-like maps at KITTI size (smooth surfaces, holes, noise), a serpentine component
+    (long union-find chains) and a batch: exact agreement with cv2's flood fill."""
+    rng = np.random.default_rng(50 + seed)
+    H, W = 375, 1242
+    yy, xx = np.mgrid[0:H, 0:W]
+    base = (200 + 3 * yy + (xx // 97) * 40 + rng.integers(-8, 9, (H, W))).astype(np.int16)
+    base[rng.random((H, W)) < 0.15] = -16
+    base[rng.random((H, W)) < 0.02] = 3000
+    snake = np.full((H, W), -16, np.int16)
+    snake[::2, :] = 500
+    snake[1::4, -1] = 500
+    snake[3::4, 0] = 500
+    imgs = np.stack([base, snake, (base // 4 * 4).astype(np.int16)])
+    for size, diff in ((100, 32), (1000, 16), (400000, 48)):
+        got = torch.from_numpy(imgs.copy()).cuda()
+        sm.filterSpeckles(got, -16, size, diff)
+        for k in range(len(imgs)):
+            want = cv2ref.filter_speckles(imgs[k], -16, size, diff)
+            assert np.array_equal(got[k].cpu().numpy(), want), (k, size, diff, int((got[k].cpu().numpy() != want).sum()))
