@@ -114,7 +114,10 @@ B2S_API int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t* r
 /* stage taps for parity tests: copies the last compute's volumes (device to device, on
    `stream`) into caller buffers of `elems` uint16 each (either may be NULL); layout
    [batch][H][width1][Dp].  cost = raw block cost (cv2's C minus P2, padded cells 0);
-   S = min(32767, sum of path costs) (padded cells 32767). */
+   S = min(32767, sum of path costs) (padded cells 32767).  The production pipeline never
+   materialises the full S (the last sweep feeds the winner-take-all from registers); call
+   b2s_sgbm_keep_volumes(h, 1) before compute to have it written as well. */
+B2S_API int b2s_sgbm_keep_volumes(b2s_handle h, int on);
 B2S_API int b2s_sgbm_debug_volumes(b2s_handle h, uint16_t* cost_out, uint16_t* S_out,
                                    size_t elems, void* stream);
 /* 1 if the last compute left the domain in which bit-exact parity with cv2 is

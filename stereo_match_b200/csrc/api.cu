@@ -1,6 +1,7 @@
 // api.cu -- C ABI of libb2stereo.so (see include/b2stereo.h): handles, parameter rules,
 // workspace, and the per-call kernel pipeline.  No CPU fallback anywhere.
 #include "common.cuh"
+#include "sgbm_wave.cuh"
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -38,6 +39,7 @@ struct b2s_matcher {
     size_t last_elems = 0;
     cudaStream_t last_stream = nullptr;
     // opt-in stage timing: events recorded on the compute stream between stages
+    bool keep_volumes = false;   // debug tap: the fused WTA pass also writes the full S volume
     bool timing = false;
     cudaEvent_t ev[B2S_NSTAGES + 1] = {};
     bool ev_valid = false;
@@ -79,19 +81,23 @@ static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, Sgb
     if (e.ftzero > 127) { b2s_set_error("StereoSGBM: preFilterCap must be <= 127"); return B2S_E_UNSUPPORTED; }
     if (e.P2 > 32767) { b2s_set_error("StereoSGBM: P2 must be <= 32767 (int16 cost domain)"); return B2S_E_UNSUPPORTED; }
     // lanes per pixel / registers per lane
-    static const int R8[] = { 1, 2, 3, 4, 6, 8, 12, 16 };
-    static const int R32[] = { 6, 8, 12, 16 };
+    // G lanes x R packed registers cover Dp = 2*R*G >= D disparities.  R <= 8: fused wavefront
+    // aggregation (sgbm_wave); R in {12, 16} (D > 512): one launch per direction (sgbm_agg).
+    static const int RS[] = { 2, 4, 6, 8 };
     e.G = 0;
-    for (int r : R8) if (16 * r >= e.D) { e.G = 8; e.R = r; break; }
-    if (!e.G) for (int r : R32) if (64 * r >= e.D) { e.G = 32; e.R = r; break; }
+    for (int g = 8; g <= 32 && !e.G; g *= 2)
+        for (int r : RS) if (2 * r * g >= e.D) { e.G = g; e.R = r; break; }
+    if (!e.G) for (int r : { 12, 16 }) if (64 * r >= e.D) { e.G = 32; e.R = r; break; }
     if (!e.G) { b2s_set_error("StereoSGBM: numDisparities > 1024 is not supported"); return B2S_E_UNSUPPORTED; }
     e.Dp = 2 * e.R * e.G;
     return B2S_OK;
 }
 
-struct SgbmLayout { size_t descL, descR, cost, S, raw, key, labels, counts, total; };
+struct SgbmLayout { size_t descL, descR, cost, S, Sdbg, raw, key, rec, edge, labels, counts, total; };
 
-static SgbmLayout sgbm_layout(const SgbmEff& e, bool speckle)
+static bool uses_wave(const SgbmEff& e) { return e.R <= 8; }
+
+static SgbmLayout sgbm_layout(const SgbmEff& e, bool speckle, bool keep_volumes)
 {
     SgbmLayout l;
     const size_t npix = (size_t)e.batch * e.H * e.W;
@@ -101,8 +107,11 @@ static SgbmLayout sgbm_layout(const SgbmEff& e, bool speckle)
     l.descR = o; o += align_up(npix * sizeof(uint2));
     l.cost = o; o += align_up(vol);
     l.S = o; o += align_up(vol);
+    l.Sdbg = o; o += (keep_volumes && uses_wave(e)) ? align_up(vol) : 0;
     l.raw = o; o += align_up(npix * sizeof(int16_t));
     l.key = o; o += align_up(npix * sizeof(uint32_t));
+    l.rec = o; o += uses_wave(e) ? align_up(npix * sizeof(uint2)) : 0;
+    l.edge = o; o += (uses_wave(e) && e.width1 > 0) ? align_up(b2s_wave_edge_bytes(e)) : 0;
     l.labels = o; o += speckle ? align_up(npix * sizeof(int32_t)) : 0;
     l.counts = o; o += speckle ? align_up(npix * sizeof(int32_t)) : 0;
     l.total = o;
@@ -171,7 +180,7 @@ extern "C" size_t b2s_sgbm_workspace_bytes(b2s_handle h, int H, int W, int batch
     if (!h || h->kind != 0) return 0;
     SgbmEff e;
     if (sgbm_effective(h->sp, H, W, batch, e)) return 0;
-    return sgbm_layout(e, h->sp.speckleWindowSize > 0).total;
+    return sgbm_layout(e, h->sp.speckleWindowSize > 0, h->keep_volumes).total;
 }
 
 __global__ void k_fill16(int16_t* p, size_t n, int16_t v)
@@ -198,7 +207,7 @@ extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t
         return B2S_OK;
     }
     const bool speckle = h->sp.speckleWindowSize > 0;
-    const SgbmLayout l = sgbm_layout(e, speckle);
+    const SgbmLayout l = sgbm_layout(e, speckle, h->keep_volumes);
     rc = ensure_ws(h, l.total, st);
     if (rc) return rc;
     char* ws = (char*)h->ws;
@@ -218,10 +227,19 @@ extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t
     B2S_MARK(1);
     if ((rc = b2s_launch_cost(descL, descR, e, cost, h->flag, st))) return rc;
     B2S_MARK(2);
-    for (int k = 0; k < e.ndirs; k++)
-        if ((rc = b2s_launch_aggregate(cost, S, e, k, k == 0, st))) return rc;
-    B2S_MARK(3);
-    if ((rc = b2s_launch_wta(S, e, raw, key, st))) return rc;
+    uint16_t* Sfull = S;
+    if (uses_wave(e)) {
+        // two fused sweeps; the second one ends in the winner-take-all (stage 2 = both sweeps)
+        Sfull = h->keep_volumes ? (uint16_t*)(ws + l.Sdbg) : nullptr;
+        if ((rc = b2s_launch_wave(e, cost, S, Sfull, ws + l.edge, (uint2*)(ws + l.rec), key, st))) return rc;
+        B2S_MARK(3);
+        if ((rc = b2s_launch_finish_rec(e, (const uint2*)(ws + l.rec), key, raw, st))) return rc;
+    } else {
+        for (int k = 0; k < e.ndirs; k++)
+            if ((rc = b2s_launch_aggregate(cost, S, e, k, k == 0, st))) return rc;
+        B2S_MARK(3);
+        if ((rc = b2s_launch_wta(S, e, raw, key, st))) return rc;
+    }
     B2S_MARK(4);
     if ((rc = b2s_launch_median3(raw, H, W, batch, disp, st))) return rc;
     B2S_MARK(5);
@@ -233,7 +251,7 @@ extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t
     B2S_MARK(6);
 #undef B2S_MARK
     h->ev_valid = h->timing;
-    h->last_cost = cost; h->last_S = S; h->last_stream = st;
+    h->last_cost = cost; h->last_S = Sfull; h->last_stream = st;
     h->last_elems = (size_t)batch * H * e.width1 * e.Dp;
     return B2S_OK;
 }
@@ -241,10 +259,18 @@ extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t
 extern "C" int b2s_sgbm_debug_volumes(b2s_handle h, uint16_t* cost_out, uint16_t* S_out, size_t elems, void* stream)
 {
     if (!h || h->kind != 0 || !h->last_cost) { b2s_set_error("debug_volumes: no completed compute on this handle"); return B2S_E_INVALID; }
+    if (S_out && !h->last_S) { b2s_set_error("debug_volumes: the S volume is only kept after b2s_sgbm_keep_volumes(h, 1)"); return B2S_E_INVALID; }
     if (elems > h->last_elems) { b2s_set_error("debug_volumes: %zu elements requested, volume has %zu", elems, h->last_elems); return B2S_E_INVALID; }
     cudaStream_t st = (cudaStream_t)stream;
     if (cost_out) B2S_CUDA_CHECK(cudaMemcpyAsync(cost_out, h->last_cost, elems * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
     if (S_out) B2S_CUDA_CHECK(cudaMemcpyAsync(S_out, h->last_S, elems * sizeof(uint16_t), cudaMemcpyDeviceToDevice, st));
+    return B2S_OK;
+}
+
+extern "C" int b2s_sgbm_keep_volumes(b2s_handle h, int on)
+{
+    if (!h || h->kind != 0) { b2s_set_error("keep_volumes: bad handle"); return B2S_E_INVALID; }
+    h->keep_volumes = on != 0;
     return B2S_OK;
 }
 

@@ -15,7 +15,7 @@ struct SgbmEff {
     int minX1, maxX1, width1;
     int invalid;              // (minD-1)*16
     int ndirs;                // 5 or 8
-    int G;                    // lanes per pixel in the aggregation/WTA kernels (8 or 32)
+    int G;                    // lanes per pixel in the aggregation/WTA kernels (8, 16 or 32)
     int R;                    // packed u16x2 registers per lane: Dp = 2*R*G
 };
 
@@ -55,6 +55,7 @@ int b2s_launch_aggregate(const uint16_t* cost, uint16_t* S, const SgbmEff& e, in
                          cudaStream_t st);
 int b2s_launch_wta(const uint16_t* S, const SgbmEff& e, int16_t* disp_raw, uint32_t* disp2key,
                    cudaStream_t st);
+int b2s_launch_finish_rec(const SgbmEff& e, const uint2* rec, const uint32_t* disp2key, int16_t* disp_raw, cudaStream_t st);
 int b2s_launch_median3(const int16_t* src, int H, int W, int batch, int16_t* dst, cudaStream_t st);
 int b2s_launch_speckles(int16_t* img, int H, int W, int batch, int newVal, int maxSize, int maxDiff,
                         int32_t* labels, int32_t* counts, cudaStream_t st);

@@ -1,4 +1,5 @@
-// sgbm_agg.cu -- SGBM path aggregation, one direction per launch.
+// sgbm_agg.cu -- SGBM path aggregation, one direction per launch: the generic path for
+// 512 < numDisparities <= 1024 (everything else runs the fused wavefront in sgbm_wave*.cu).
 // Replaces the L_r recurrence inside cv2.StereoSGBM.compute (MODE_SGBM: 5 paths,
 // MODE_HH: 8 paths; reference call site stereo_vision/stereo_vision.py:178).
 //
@@ -211,9 +212,7 @@ int b2s_launch_aggregate(const uint16_t* cost, uint16_t* S, const SgbmEff& e, in
                          cudaStream_t st)
 {
 #define AGG_CASE(RR, GG) if (e.R == RR && e.G == GG) return launch_agg_rg<RR, GG>(cost, S, e, dir, first, st);
-    AGG_CASE(1, 8) AGG_CASE(2, 8) AGG_CASE(3, 8) AGG_CASE(4, 8) AGG_CASE(6, 8) AGG_CASE(8, 8)
-    AGG_CASE(12, 8) AGG_CASE(16, 8)
-    AGG_CASE(6, 32) AGG_CASE(8, 32) AGG_CASE(12, 32) AGG_CASE(16, 32)
+    AGG_CASE(12, 32) AGG_CASE(16, 32)          // D > 512 only; smaller D runs sgbm_wave
 #undef AGG_CASE
     b2s_set_error("no aggregation kernel for R=%d G=%d (numDisparities=%d)", e.R, e.G, e.D);
     return B2S_E_UNSUPPORTED;

@@ -98,7 +98,28 @@ k_wta(const uint16_t* __restrict__ S, SgbmEff e, int16_t* __restrict__ disp, uin
     drow[x + e.minX1] = (int16_t)(dq + e.minD * 16);
 }
 
-// LR consistency check, in place; also fills the never-computed columns with INVALID.
+// LR consistency check of one pixel (second loop): true = keep d1.
+__device__ __forceinline__ bool lr_consistent(const SgbmEff& e, const uint32_t* __restrict__ keyrow, int x, int d1)
+{
+    const int _d = d1 >> 4, d_ = (d1 + 15) >> 4;
+    const int _x = x - _d, x_ = x - d_;
+    if (!(0 <= _x && _x < e.W)) return true;
+    {
+        uint32_t k = keyrow[_x];
+        // disp2 = best + minD of the winning x;  empty slots read as the scaled INVALID (cv2 quirk)
+        int v = (k == 0xffffffffu) ? e.invalid : ((0xffff - (int)(k & 0xffffu)) + e.minX1 - _x);
+        if (!(v >= e.minD && abs(v - _d) > e.lrmax)) return true;
+    }
+    if (!(0 <= x_ && x_ < e.W)) return true;
+    {
+        uint32_t k = keyrow[x_];
+        int v = (k == 0xffffffffu) ? e.invalid : ((0xffff - (int)(k & 0xffffu)) + e.minX1 - x_);
+        if (!(v >= e.minD && abs(v - d_) > e.lrmax)) return true;
+    }
+    return false;
+}
+
+// in place on the pre-check disparity; also fills the never-computed columns with INVALID.
 __global__ void __launch_bounds__(256)
 k_lrcheck(SgbmEff e, int16_t* __restrict__ disp, const uint32_t* __restrict__ disp2key)
 {
@@ -108,27 +129,41 @@ k_lrcheck(SgbmEff e, int16_t* __restrict__ disp, const uint32_t* __restrict__ di
     if (x < e.minX1 || x >= e.maxX1) { disp[row + x] = (int16_t)e.invalid; return; }
     const int d1 = disp[row + x];
     if (d1 == e.invalid) return;
-    const int _d = d1 >> 4, d_ = (d1 + 15) >> 4;
-    const int _x = x - _d, x_ = x - d_;
-    bool fail = true;
-    {
-        if (!(0 <= _x && _x < e.W)) fail = false;
-        else {
-            uint32_t k = disp2key[row + _x];
-            // disp2 = best + minD of the winning x;  empty slots read as the scaled INVALID (cv2 quirk)
-            int v = (k == 0xffffffffu) ? e.invalid : ((0xffff - (int)(k & 0xffffu)) + e.minX1 - _x);
-            if (!(v >= e.minD && abs(v - _d) > e.lrmax)) fail = false;
+    if (!lr_consistent(e, disp2key + row, x, d1)) disp[row + x] = (int16_t)e.invalid;
+}
+
+// Tail of the fused WTA (sgbm_wave): record -> sub-pixel disparity -> LR check -> raw map.
+// rec.x = minS | best << 16 (best = 0xffff: rejected by the uniqueness test), rec.y = S(best-1) | S(best+1) << 16
+__global__ void __launch_bounds__(256)
+k_finish_rec(SgbmEff e, const uint2* __restrict__ rec, const uint32_t* __restrict__ disp2key, int16_t* __restrict__ disp)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= e.W) return;
+    const size_t row = ((size_t)blockIdx.z * e.H + blockIdx.y) * e.W;
+    int out = e.invalid;
+    if (x >= e.minX1 && x < e.maxX1) {
+        const uint2 r = rec[row + x];
+        const int best = (int)(r.x >> 16);
+        if (best != 0xffff) {
+            const int minS = (int)(r.x & 0xffffu), sm1 = (int)(r.y & 0xffffu), sp1 = (int)(r.y >> 16);
+            int dq = best * 16;
+            if (best > 0 && best < e.D - 1) {
+                int denom2 = max(sm1 + sp1 - 2 * minS, 1);
+                dq += ((sm1 - sp1) * 16 + denom2) / (denom2 * 2);
+            }
+            const int d1 = dq + e.minD * 16;
+            if (lr_consistent(e, disp2key + row, x, d1)) out = d1;
         }
     }
-    if (fail) {
-        if (!(0 <= x_ && x_ < e.W)) fail = false;
-        else {
-            uint32_t k = disp2key[row + x_];
-            int v = (k == 0xffffffffu) ? e.invalid : ((0xffff - (int)(k & 0xffffu)) + e.minX1 - x_);
-            if (!(v >= e.minD && abs(v - d_) > e.lrmax)) fail = false;
-        }
-    }
-    if (fail) disp[row + x] = (int16_t)e.invalid;
+    disp[row + x] = (int16_t)out;
+}
+
+int b2s_launch_finish_rec(const SgbmEff& e, const uint2* rec, const uint32_t* disp2key, int16_t* disp_raw, cudaStream_t st)
+{
+    dim3 grid(b2s_cdiv(e.W, 256), e.H, e.batch);
+    k_finish_rec<<<grid, 256, 0, st>>>(e, rec, disp2key, disp_raw);
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
 }
 
 template <int R, int G>
@@ -145,9 +180,7 @@ int b2s_launch_wta(const uint16_t* S, const SgbmEff& e, int16_t* disp_raw, uint3
     B2S_CUDA_CHECK(cudaMemsetAsync(disp2key, 0xff, (size_t)e.batch * e.H * e.W * sizeof(uint32_t), st));
     int rc = B2S_E_UNSUPPORTED;
 #define WTA_CASE(RR, GG) if (e.R == RR && e.G == GG) rc = launch_wta_rg<RR, GG>(S, e, disp_raw, disp2key, st);
-    WTA_CASE(1, 8) WTA_CASE(2, 8) WTA_CASE(3, 8) WTA_CASE(4, 8) WTA_CASE(6, 8) WTA_CASE(8, 8)
-    WTA_CASE(12, 8) WTA_CASE(16, 8)
-    WTA_CASE(6, 32) WTA_CASE(8, 32) WTA_CASE(12, 32) WTA_CASE(16, 32)
+    WTA_CASE(12, 32) WTA_CASE(16, 32)          // D > 512 only; smaller D runs the fused wavefront WTA
 #undef WTA_CASE
     if (rc != B2S_OK) {
         if (rc == B2S_E_UNSUPPORTED) b2s_set_error("no WTA kernel for R=%d G=%d", e.R, e.G);

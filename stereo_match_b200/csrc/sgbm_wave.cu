@@ -1,0 +1,67 @@
+// sgbm_wave.cu -- host side of the fused wavefront aggregation (see sgbm_wave.cuh).
+#include "sgbm_wave.cuh"
+
+int b2s_wave_rows_per_band(const SgbmEff& e) { return 256 / e.G; }
+
+static size_t al256(size_t v) { return (v + 255) / 256 * 256; }
+
+struct EdgeLayout { size_t edge, edge_min, progress, total; int nbands; };
+static EdgeLayout edge_layout(const SgbmEff& e)
+{
+    EdgeLayout l;
+    l.nbands = (e.H + b2s_wave_rows_per_band(e) - 1) / b2s_wave_rows_per_band(e);
+    const size_t items = (size_t)e.batch * l.nbands;
+    size_t o = 0;
+    l.edge = o; o += al256(items * e.width1 * 3 * e.Dp * sizeof(uint16_t));
+    l.edge_min = o; o += al256(items * e.width1 * 4 * sizeof(uint32_t));
+    l.progress = o; o += al256((items + 1) * sizeof(int));      // progress[items] then the ticket
+    l.total = o;
+    return l;
+}
+
+size_t b2s_wave_edge_bytes(const SgbmEff& e) { return edge_layout(e).total; }
+
+static int launch_pass(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
+{
+    switch (e.G) {
+    case 8: return b2s_launch_wave_g8(e, a, vert, final, st);
+    case 16: return b2s_launch_wave_g16(e, a, vert, final, st);
+    case 32: return b2s_launch_wave_g32(e, a, vert, final, st);
+    }
+    b2s_set_error("wave: no kernel for G=%d", e.G);
+    return B2S_E_UNSUPPORTED;
+}
+
+// cost -> (S1) -> WTA records + disp2 keys.  S holds S1 after the call; S_dbg (optional) the full S.
+int b2s_launch_wave(const SgbmEff& e, const uint16_t* cost, uint16_t* S, uint16_t* S_dbg, void* edge_ws,
+                    uint2* rec, uint32_t* disp2key, cudaStream_t st)
+{
+    const EdgeLayout l = edge_layout(e);
+    char* ws = (char*)edge_ws;
+    const size_t items = (size_t)e.batch * l.nbands;
+    WaveArgs a;
+    a.cost = cost; a.S = S; a.S_out = nullptr;
+    a.edge = (uint16_t*)(ws + l.edge);
+    a.edge_min = (uint32_t*)(ws + l.edge_min);
+    a.progress = (int*)(ws + l.progress);
+    a.ticket = (unsigned int*)(a.progress + items);
+    a.rec = rec; a.disp2key = disp2key;
+    const int mul = 100 - e.uniq;
+    a.magic = mul > 0 ? ((1ull << 40) + (unsigned long long)mul - 1) / (unsigned long long)mul : 0ull;
+    a.nbands = l.nbands;
+    int rc;
+    B2S_CUDA_CHECK(cudaMemsetAsync(disp2key, 0xff, (size_t)e.batch * e.H * e.W * sizeof(uint32_t), st));
+    // pass 1: -> , down-right, down, down-left
+    B2S_CUDA_CHECK(cudaMemsetAsync(a.progress, 0, (items + 1) * sizeof(int), st));
+    a.flip = 0;
+    if ((rc = launch_pass(e, a, 1, 0, st))) return rc;
+    a.flip = 1;
+    a.S_out = S_dbg;
+    if (e.ndirs == 8) {          // MODE_HH: the mirrored sweep adds <- , up-left, up, up-right
+        B2S_CUDA_CHECK(cudaMemsetAsync(a.progress, 0, (items + 1) * sizeof(int), st));
+        rc = launch_pass(e, a, 1, 1, st);
+    } else {                     // MODE_SGBM: only <-
+        rc = launch_pass(e, a, 0, 1, st);
+    }
+    return rc;
+}

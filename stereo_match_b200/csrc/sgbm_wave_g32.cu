@@ -1,0 +1,6 @@
+// sgbm_wave_g32.cu -- instantiations of the wavefront aggregation kernel for G = 32 lanes per pixel.
+#include "sgbm_wave_impl.cuh"
+int b2s_launch_wave_g32(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
+{
+    return wave::launch_g<32>(e, a, vert, final, st);
+}

@@ -1,0 +1,462 @@
+// sgbm_wave_impl.cuh -- the wavefront kernel template (see sgbm_wave.cuh for the design).
+#pragma once
+#include "sgbm_wave.cuh"
+
+namespace wave {
+
+constexpr int NT = 256;
+
+// ---- R packed registers <-> memory (generic address space; 16/8/4-byte vectors) ---------------
+template <int R>
+__device__ __forceinline__ void ld_regs(const uint16_t* p, uint32_t (&r)[R])
+{
+    if constexpr (R % 4 == 0) {
+#pragma unroll
+        for (int i = 0; i < R / 4; i++) {
+            uint4 v = reinterpret_cast<const uint4*>(p)[i];
+            r[4 * i] = v.x; r[4 * i + 1] = v.y; r[4 * i + 2] = v.z; r[4 * i + 3] = v.w;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < R / 2; i++) {
+            uint2 v = reinterpret_cast<const uint2*>(p)[i];
+            r[2 * i] = v.x; r[2 * i + 1] = v.y;
+        }
+    }
+}
+
+template <int R>
+__device__ __forceinline__ void ldg_regs_stream(const uint16_t* p, uint32_t (&r)[R])
+{
+    if constexpr (R % 4 == 0) {
+#pragma unroll
+        for (int i = 0; i < R / 4; i++) {
+            uint4 v = __ldcs(reinterpret_cast<const uint4*>(p) + i);
+            r[4 * i] = v.x; r[4 * i + 1] = v.y; r[4 * i + 2] = v.z; r[4 * i + 3] = v.w;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < R / 2; i++) {
+            uint2 v = __ldcs(reinterpret_cast<const uint2*>(p) + i);
+            r[2 * i] = v.x; r[2 * i + 1] = v.y;
+        }
+    }
+}
+
+template <int R>
+__device__ __forceinline__ void st_regs(uint16_t* p, const uint32_t (&r)[R])
+{
+    if constexpr (R % 4 == 0) {
+#pragma unroll
+        for (int i = 0; i < R / 4; i++)
+            reinterpret_cast<uint4*>(p)[i] = make_uint4(r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]);
+    } else {
+#pragma unroll
+        for (int i = 0; i < R / 2; i++) reinterpret_cast<uint2*>(p)[i] = make_uint2(r[2 * i], r[2 * i + 1]);
+    }
+}
+
+template <int G>
+__device__ __forceinline__ uint32_t group_min_x2(uint32_t v)     // two independent u16 minima at once
+{
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) v = __vminu2(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+__device__ __forceinline__ uint32_t half_min(uint32_t v) { return min(v & 0xffffu, v >> 16); }
+
+// One recurrence step of one direction for this lane's 2R disparities:
+//   L(d) <- C(d) + min( L(d), min(L(d-1), L(d+1), minL + P2 - P1) + P1 ) - minL
+// L in/out; returns the packed lane-local minimum of the new L.
+template <int R, int G, bool PAD>
+__device__ __forceinline__ uint32_t step(uint32_t (&L)[R], const uint32_t (&C)[R], int lane, uint32_t p1x2,
+                                         uint32_t p2m1x2, uint32_t minx2, const uint32_t (&padm)[R])
+{
+    uint32_t up = __shfl_up_sync(0xffffffffu, L[R - 1], 1, G);
+    uint32_t dn = __shfl_down_sync(0xffffffffu, L[0], 1, G);
+    if (lane == 0) up = 0x7fff0000u;          // L(q,-1) = 32767
+    if (lane == G - 1) dn = 0x00007fffu;      // L(q, D) = 32767
+    uint32_t sh[R + 1];                       // sh[i] = (L(d-1), L(d)) for register i's low cell
+    sh[0] = __byte_perm(up, L[0], 0x5432);
+#pragma unroll
+    for (int i = 1; i < R; i++) sh[i] = __byte_perm(L[i - 1], L[i], 0x5432);
+    sh[R] = __byte_perm(L[R - 1], dn, 0x5432);
+    const uint32_t dmp = minx2 + p2m1x2;      // minL + P2 - P1  (P2 > P1)
+    uint32_t mn = 0xffffffffu;
+#pragma unroll
+    for (int i = 0; i < R; i++) {
+        uint32_t m = __vimin3_u16x2(sh[i], sh[i + 1], dmp);
+        uint32_t u = __viaddmin_u16x2(m, p1x2, L[i]);
+        uint32_t l = C[i] + u - minx2;        // halves never borrow: u >= minL
+        if (PAD) l |= padm[i];                // padded cells (d >= D) stay pinned at 0x7fff
+        L[i] = l;
+        mn = __vminu2(mn, l);
+    }
+    return mn;
+}
+
+__device__ __forceinline__ int ld_acquire(const int* p)
+{
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release(int* p, int v)
+{
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
+{
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// shared-memory plan (bytes), shared by host and device
+template <int R, int G, bool VERT, bool FINAL>
+struct Plan {
+    static constexpr int RB = NT / G;
+    static constexpr int DP = 2 * R * G;
+    static constexpr int CH = (G == 8) ? 8 : 4;
+    static constexpr int ring1 = 0;                                        // [RB][4][DP] u16
+    static constexpr int ring2 = ring1 + (VERT ? RB * 4 * DP * 2 : 0);     // [RB][4][DP]
+    static constexpr int ring3 = ring2 + (VERT ? RB * 4 * DP * 2 : 0);     // [RB][2][DP]
+    static constexpr int stage = ring3 + (VERT ? RB * 2 * DP * 2 : 0);     // [2][CH][3][DP]
+    static constexpr int zero = stage + (VERT ? 2 * CH * 3 * DP * 2 : 0);  // [DP]
+    static constexpr int scratch = zero + (VERT ? DP * 2 : 0);             // [RB][DP] (FINAL)
+    static constexpr int ringmin = scratch + (FINAL ? RB * DP * 2 : 0);    // [RB][4][4] u32
+    static constexpr int stagemin = ringmin + (VERT ? RB * 16 * 4 : 0);    // [2][CH][4] u32
+    static constexpr int zeromin = stagemin + (VERT ? 2 * CH * 4 * 4 : 0); // [4] u32
+    static constexpr int item = zeromin + 16;
+    static constexpr int total = item + 16;
+};
+
+// ---- fused winner-take-all on the registers of one group (first loop) --------
+template <int R, int G, bool PAD>
+__device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const SgbmEff& e, unsigned long long magic,
+                                    uint16_t* scr, bool act, size_t rowpix, int xreal, uint2* rec,
+                                    uint32_t* disp2key)
+{
+    const int dbase = lane * 2 * R;
+    uint32_t key = 0xffffffffu;
+#pragma unroll
+    for (int i = 0; i < R; i++) {
+        uint32_t k0 = __byte_perm(Sv[i], 2 * i, 0x1054);          // S(lo) << 16 | cell
+        uint32_t k1 = __byte_perm(Sv[i], 2 * i + 1, 0x3254);      // S(hi) << 16 | cell
+        key = __vimin3_u32(key, k0, k1);
+    }
+    key += dbase;                                                  // cell -> disparity index
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, o));
+    const int best = (int)(key & 0xffffu);                         // first minimum (lowest d on ties)
+    const int minS = (int)(key >> 16);
+
+    // uniqueness: exists d, |d - best| > 1, S(d) * (100 - uniq) < minS * 100
+    const int mul = 100 - e.uniq;
+    bool bad_lane = false;
+    if (mul > 0) {
+        // S * mul < minS * 100  <=>  S < T,  T = ceil(minS * 100 / mul)   (exact magic division)
+        const unsigned a = (unsigned)(minS * 100 + mul - 1);
+        unsigned T = (unsigned)(((unsigned long long)a * magic) >> 40);
+        T = min(T, 0x8000u);
+        const uint32_t K = (0x8000u - T) * 0x10001u;               // S + K has bit 15 set  <=>  S >= T
+        uint32_t acc = 0;
+#pragma unroll
+        for (int i = 0; i < R; i++) acc = (acc >> 1) | ((Sv[i] + K) & 0x80008000u);
+        // register i, low cell -> bit 16-R+i ; high cell -> bit 32-R+i
+        uint32_t cells = (((1u << R) - 1u) << (16 - R)) * 0x10001u;
+        if (PAD) {
+            cells = 0;
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                if (dbase + 2 * i < e.D) cells |= 1u << (16 - R + i);
+                if (dbase + 2 * i + 1 < e.D) cells |= 1u << (32 - R + i);
+            }
+        }
+        uint32_t excl = 0;
+        const int bl = best - dbase;
+#pragma unroll
+        for (int k = -1; k <= 1; k++) {
+            int c = bl + k;
+            if (c >= 0 && c < 2 * R) excl |= 1u << ((c & 1) * 16 + 16 - R + (c >> 1));
+        }
+        bad_lane = (~acc & cells & ~excl) != 0;
+    } else {
+        const int thr = minS * 100;
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                int d = dbase + 2 * i + h;
+                int val = h ? (int)(Sv[i] >> 16) : (int)(Sv[i] & 0xffffu);
+                int ad = d - best;
+                if (d < e.D && (ad > 1 || ad < -1) && val * mul < thr) bad_lane = true;
+            }
+        }
+    }
+    const unsigned gshift = (threadIdx.x & 31) & ~(G - 1);
+    const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << (G & 31)) - 1u) << gshift);
+    const bool bad = (__ballot_sync(0xffffffffu, bad_lane) & gmask) != 0;
+
+    // neighbours of the winner through the group's scratch row
+    st_regs<R>(scr + dbase, Sv);
+    __syncwarp();
+    if (lane == 0 && act) {
+        const uint32_t sm1 = best > 0 ? scr[best - 1] : 0u;
+        const uint32_t sp1 = best < e.D - 1 ? scr[best + 1] : 0u;
+        const int xi = xreal + e.minX1;
+        rec[rowpix + xi] = make_uint2((uint32_t)minS | (bad ? 0xffff0000u : (uint32_t)best << 16), sm1 | (sp1 << 16));
+        if (!bad) {
+            const int x2 = xi - best - e.minD;
+            atomicMin(disp2key + rowpix + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - xreal));
+        }
+    }
+    __syncwarp();
+}
+
+template <int R, int G, bool PAD, bool VERT, bool FINAL>
+__global__ void __launch_bounds__(NT, (G == 32 ? 1 : 2))
+k_wave(SgbmEff e, WaveArgs a)
+{
+    using P = Plan<R, G, VERT, FINAL>;
+    constexpr int RB = P::RB, DP = P::DP, CH = P::CH;
+    extern __shared__ __align__(16) unsigned char smem[];
+    uint16_t* const ring1 = reinterpret_cast<uint16_t*>(smem + P::ring1);
+    uint16_t* const ring2 = reinterpret_cast<uint16_t*>(smem + P::ring2);
+    uint16_t* const ring3 = reinterpret_cast<uint16_t*>(smem + P::ring3);
+    uint16_t* const stage = reinterpret_cast<uint16_t*>(smem + P::stage);
+    uint16_t* const zero = reinterpret_cast<uint16_t*>(smem + P::zero);
+    uint16_t* const scratch = reinterpret_cast<uint16_t*>(smem + P::scratch);
+    uint32_t* const ringmin = reinterpret_cast<uint32_t*>(smem + P::ringmin);
+    uint32_t* const stagemin = reinterpret_cast<uint32_t*>(smem + P::stagemin);
+    uint32_t* const zeromin = reinterpret_cast<uint32_t*>(smem + P::zeromin);
+    int* const s_item = reinterpret_cast<int*>(smem + P::item);
+
+    if (threadIdx.x == 0) *s_item = VERT ? (int)atomicAdd(a.ticket, 1u) : (int)blockIdx.x;
+    if (VERT) {
+        for (int i = threadIdx.x; i < DP / 2; i += NT) reinterpret_cast<uint32_t*>(zero)[i] = 0u;
+        if (threadIdx.x < 4) zeromin[threadIdx.x] = 0u;
+    }
+    __syncthreads();
+    const int item = *s_item;
+    const int b = item / a.nbands, band = item - b * a.nbands;
+    const int g = threadIdx.x / G, lane = threadIdx.x % G;
+    const int w1 = e.width1;
+    const int ys = band * RB + g;
+    const bool rowact = ys < e.H;
+    const int nrows = min(RB, e.H - band * RB);
+    const int gl = nrows - 1;
+    const bool has_above = VERT && band > 0;
+    const bool has_below = VERT && band < a.nbands - 1;
+    constexpr int SKEW = VERT ? 2 : 0;
+    const int T = w1 + SKEW * (nrows - 1);
+    const int yreal = a.flip ? e.H - 1 - min(ys, e.H - 1) : min(ys, e.H - 1);
+    const int xsign = a.flip ? -1 : 1, xorg = a.flip ? w1 - 1 : 0;      // xreal = xorg + xsign * xs
+
+    const size_t rowoff = ((size_t)b * e.H + yreal) * w1 * DP + (size_t)lane * 2 * R;
+    const uint16_t* const cb = a.cost + rowoff;
+    uint16_t* const sb = a.S + rowoff;
+    const size_t rowpix = ((size_t)b * e.H + yreal) * e.W;
+
+    uint32_t padm[R];
+#pragma unroll
+    for (int i = 0; i < R; i++) {
+        int d0 = lane * 2 * R + 2 * i;
+        padm[i] = PAD ? ((d0 >= e.D ? 0x7fffu : 0u) | (d0 + 1 >= e.D ? 0x7fff0000u : 0u)) : 0u;
+    }
+    const uint32_t p1x2 = (uint32_t)e.P1 * 0x10001u;
+    const uint32_t p2m1x2 = (uint32_t)(e.P2 - e.P1) * 0x10001u;
+
+    uint32_t Lh[R], C[R], Cn[R], S1[R], S1n[R];
+    uint32_t minh = 0;
+#pragma unroll
+    for (int i = 0; i < R; i++) { Lh[i] = 0; C[i] = 0; Cn[i] = 0; S1[i] = 0; S1n[i] = 0; }
+
+    // edge stream of the band above: producer item = item - 1
+    const uint16_t* const eabove = a.edge + (size_t)(item - 1) * w1 * 3 * DP;
+    const uint32_t* const eabove_min = a.edge_min + (size_t)(item - 1) * w1 * 4;
+    uint16_t* const ebelow = a.edge + (size_t)item * w1 * 3 * DP;
+    uint32_t* const ebelow_min = a.edge_min + (size_t)item * w1 * 4;
+    auto stage_chunk = [&](int c) {          // cp.async chunk c of the edge stream into stage[c & 1]
+        const int x0 = c * CH, npx = min(CH, w1 - x0);
+        const int n16 = npx * 3 * DP * 2 / 16;
+        const unsigned char* src = reinterpret_cast<const unsigned char*>(eabove + (size_t)x0 * 3 * DP);
+        unsigned char* dst = reinterpret_cast<unsigned char*>(stage + (size_t)(c & 1) * CH * 3 * DP);
+        for (int i = threadIdx.x; i < n16; i += NT) cp_async16(dst + 16 * i, src + 16 * i);
+        if ((int)threadIdx.x < npx)
+            cp_async16(stagemin + ((c & 1) * CH + threadIdx.x) * 4, eabove_min + (size_t)(x0 + threadIdx.x) * 4);
+    };
+    auto wait_progress = [&](int need) {
+        const int* p = a.progress + (item - 1);
+        while (ld_acquire(p) < need) __nanosleep(64);
+    };
+    if (has_above) {
+        if (threadIdx.x == 0) wait_progress(min(CH, w1));
+        __syncthreads();
+        stage_chunk(0);
+        cp_async_wait_all();
+        __syncthreads();
+    }
+
+    // first operands
+    {
+        const int xs = -SKEW * g;
+        if (rowact && xs >= 0 && xs < w1) {
+            const size_t off = (size_t)(xorg + xsign * xs) * DP;
+            ldg_regs_stream<R>(cb + off, C);
+            if (FINAL) ldg_regs_stream<R>(sb + off, S1);
+        }
+    }
+    int pend = 0;
+
+    for (int t = 0; t < T; t++) {
+        if (VERT && pend) { __threadfence(); st_release(a.progress + item, pend); pend = 0; }
+        const int xs = t - SKEW * g;
+        const bool act = rowact && xs >= 0 && xs < w1;
+        const int xreal = xorg + xsign * xs;
+        const size_t off = (size_t)xreal * DP;
+        if (has_above && (t % CH) == 2 % CH && t >= 2) {         // chunk staging (polled at the end of step t-1)
+            const int c = (t - 2) / CH + 1;
+            if (c * CH < w1) stage_chunk(c);
+        }
+        // prefetch the next pixel's operands
+        {
+            const int xn = xs + 1;
+            const bool actn = rowact && xn >= 0 && xn < w1;
+#pragma unroll
+            for (int i = 0; i < R; i++) { Cn[i] = 0; }
+            if (actn) {
+                const size_t offn = (size_t)(xorg + xsign * xn) * DP;
+                ldg_regs_stream<R>(cb + offn, Cn);
+                if (FINAL) ldg_regs_stream<R>(sb + offn, S1n);
+            }
+        }
+
+        uint32_t Sv[R];
+        // ---- direction 0: along the row, state in registers -------------------------------
+        uint32_t mn0 = step<R, G, PAD>(Lh, C, lane, p1x2, p2m1x2, minh, padm);
+#pragma unroll
+        for (int i = 0; i < R; i++) Sv[i] = FINAL ? __viaddmin_u16x2(S1[i], Lh[i], 0x7fff7fffu) : Lh[i];
+
+        if (VERT) {
+            uint32_t Lv[R];
+            uint32_t mnv[3];
+#pragma unroll
+            for (int k = 1; k <= 3; k++) {
+                const int xp = xs + (k == 1 ? -1 : (k == 3 ? 1 : 0));
+                const bool has_pred = xp >= 0 && xp < w1 && (g > 0 || has_above);
+                const uint16_t* src = zero;
+                const uint32_t* msrc = zeromin;
+                if (has_pred) {
+                    if (g > 0) {
+                        if (k == 1) src = ring1 + ((g - 1) * 4 + (xp & 3)) * DP;
+                        else if (k == 2) src = ring2 + ((g - 1) * 4 + (xp & 3)) * DP;
+                        else src = ring3 + ((g - 1) * 2 + (xp & 1)) * DP;
+                        msrc = ringmin + ((g - 1) * 4 + (xp & 3)) * 4 + k;
+                    } else {
+                        const int slot = ((xp / CH) & 1) * CH + (xp % CH);
+                        src = stage + (slot * 3 + (k - 1)) * DP;
+                        msrc = stagemin + slot * 4 + (k - 1);
+                    }
+                }
+                ld_regs<R>(src + lane * 2 * R, Lv);
+                const uint32_t minv = *msrc;
+                mnv[k - 1] = step<R, G, PAD>(Lv, C, lane, p1x2, p2m1x2, minv, padm);
+#pragma unroll
+                for (int i = 0; i < R; i++) Sv[i] = __viaddmin_u16x2(Sv[i], Lv[i], 0x7fff7fffu);
+                if (act) {
+                    uint16_t* dst;
+                    if (k == 1) dst = ring1 + (g * 4 + (xs & 3)) * DP;
+                    else if (k == 2) dst = ring2 + (g * 4 + (xs & 3)) * DP;
+                    else dst = ring3 + (g * 2 + (xs & 1)) * DP;
+                    st_regs<R>(dst + lane * 2 * R, Lv);
+                    if (has_below && g == gl) st_regs<R>(ebelow + ((size_t)xs * 3 + (k - 1)) * DP + lane * 2 * R, Lv);
+                }
+            }
+            // two packed reductions for the four minima
+            uint32_t r01 = group_min_x2<G>(half_min(mn0) | (half_min(mnv[0]) << 16));
+            uint32_t r23 = group_min_x2<G>(half_min(mnv[1]) | (half_min(mnv[2]) << 16));
+            minh = (r01 & 0xffffu) * 0x10001u;
+            if (act && lane == 0) {
+                uint32_t* md = ringmin + (g * 4 + (xs & 3)) * 4;
+                const uint32_t m1 = (r01 >> 16) * 0x10001u, m2 = (r23 & 0xffffu) * 0x10001u, m3 = (r23 >> 16) * 0x10001u;
+                md[1] = m1; md[2] = m2; md[3] = m3;
+                if (has_below && g == gl) {
+                    uint32_t* ge = ebelow_min + (size_t)xs * 4;
+                    ge[0] = m1; ge[1] = m2; ge[2] = m3;
+                }
+            }
+        } else {
+            minh = group_min_x2<G>(half_min(mn0)) * 0x10001u;
+        }
+
+        // ---- S ------------------------------------------------------------------------------
+        if (FINAL) {
+            wta<R, G, PAD>(Sv, lane, e, a.magic, scratch + g * DP, act, rowpix, xreal, a.rec, a.disp2key);
+            if (a.S_out != nullptr && act) st_regs<R>(a.S_out + rowoff + off, Sv);
+        } else {
+            if (act) st_regs<R>(sb + off, Sv);
+        }
+
+        // ---- band pipeline bookkeeping -----------------------------------------------------------
+        if (VERT) {
+            if (has_below && g == gl && act && (((xs + 1) % CH) == 0 || xs == w1 - 1)) {
+                __threadfence();
+                if (lane == 0) pend = xs + 1;
+            }
+            if (has_above) {
+                if ((t % CH) == CH - 2) cp_async_wait_all();
+                if ((t % CH) == 1 && threadIdx.x == 0) {
+                    const int c = t / CH + 1;
+                    if (c * CH < w1) wait_progress(min((c + 1) * CH, w1));
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < R; i++) { C[i] = Cn[i]; if (FINAL) S1[i] = S1n[i]; }
+        if (VERT) __syncthreads();
+    }
+    if (VERT && pend) { __threadfence(); st_release(a.progress + item, pend); }
+}
+
+template <int R, int G, bool PAD, bool VERT, bool FINAL>
+int launch_one(const SgbmEff& e, const WaveArgs& a, cudaStream_t st)
+{
+    using P = Plan<R, G, VERT, FINAL>;
+    static bool configured = false;
+    if (!configured) {
+        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_wave<R, G, PAD, VERT, FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
+        configured = true;
+    }
+    const int grid = e.batch * a.nbands;
+    k_wave<R, G, PAD, VERT, FINAL><<<grid, NT, P::total, st>>>(e, a);
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}
+
+template <int R, int G>
+int launch_rg(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
+{
+    const bool pad = e.D != e.Dp;
+    if (vert && !final) return pad ? launch_one<R, G, true, true, false>(e, a, st) : launch_one<R, G, false, true, false>(e, a, st);
+    if (vert && final) return pad ? launch_one<R, G, true, true, true>(e, a, st) : launch_one<R, G, false, true, true>(e, a, st);
+    if (!vert && final) return pad ? launch_one<R, G, true, false, true>(e, a, st) : launch_one<R, G, false, false, true>(e, a, st);
+    b2s_set_error("wave: unsupported pass combination");
+    return B2S_E_INVALID;
+}
+
+template <int G>
+int launch_g(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
+{
+    switch (e.R) {
+    case 2: return launch_rg<2, G>(e, a, vert, final, st);
+    case 4: return launch_rg<4, G>(e, a, vert, final, st);
+    case 6: return launch_rg<6, G>(e, a, vert, final, st);
+    case 8: return launch_rg<8, G>(e, a, vert, final, st);
+    }
+    b2s_set_error("wave: no kernel for R=%d G=%d", e.R, G);
+    return B2S_E_UNSUPPORTED;
+}
+
+}  // namespace wave

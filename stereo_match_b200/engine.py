@@ -151,9 +151,13 @@ class StereoSGBM(_Matcher):
         _lib.check(_lib.load().b2s_sgbm_stage_ms(self._h, ms))
         return dict(zip(self.STAGES, [float(v) for v in ms]))
 
+    def keep_volumes(self, on=True):
+        """Debug tap: make the following computes also write the full S volume."""
+        _lib.check(_lib.load().b2s_sgbm_keep_volumes(self._h, int(bool(on))))
+
     def debug_volumes(self, B, H, W):
         """(cost, S, geometry) of the last compute; torch int16 views of the uint16 volumes
-        [B, H, width1, Dp] (test tap)."""
+        [B, H, width1, Dp] (test tap; needs keep_volumes() before the compute)."""
         g = self.geometry(W)
         n = B * H * g["width1"] * g["Dp"]
         cost = torch.empty(n, dtype=torch.int16, device="cuda")

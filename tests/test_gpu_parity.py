@@ -39,6 +39,7 @@ def test_sgbm_volumes_match_oracle(i, port):
     kw = sgbm_kwargs(v)
     _, Cw, Sw, _ = port.sgbm_compute(l, r, want_volumes=True, **kw)
     m = sm.StereoSGBM_create(**kw)
+    m.keep_volumes(True)
     m.compute(torch.from_numpy(l).cuda(), torch.from_numpy(r).cuda())
     cost, S, g = m.debug_volumes(1, l.shape[0], l.shape[1])
     D = kw["numDisparities"]
@@ -229,7 +230,7 @@ def test_launch_counter_and_library_loaded():
     before = _lib.load().b2s_launch_count()
     l, r = synth_pair(96, 64, 16, seed=0)
     sm.StereoSGBM_create(numDisparities=16, blockSize=5).compute(l, r)
-    assert _lib.load().b2s_launch_count() - before >= 10
+    assert _lib.load().b2s_launch_count() - before >= 6
     with open("/proc/self/maps") as f:
         assert "libb2stereo.so" in f.read()
 

@@ -22,6 +22,11 @@ SGBM_VECTORS = [
     (70, 40, 0, 64, 5, 600, 2400, 1, 63, 15, 1, 0, 0),      # width1 = 6
     (40, 3, 0, 16, 5, 600, 2400, 1, 63, 15, 1, 0, 0),       # H smaller than the block
     (1, 1, -1, 1, 1, 8, 32, 1, 63, 15, 0, 0, 0),            # one pixel, one disparity
+    (640, 24, 0, 528, 3, 72, 288, 1, 63, 10, 1, 0, 0),      # D > 512: per-direction kernels
+    (300, 200, 0, 96, 5, 600, 2400, 1, 63, 15, 1, 60, 2),   # 7 bands of 32 rows, R = 6
+    (300, 200, 0, 96, 5, 600, 2400, 1, 63, 15, 0, 0, 0),
+    (420, 70, 0, 200, 3, 100, 800, 1, 63, 10, 1, 0, 0),     # G = 16, padded (Dp = 256), 5 bands
+    (23, 50, 0, 16, 3, 100, 800, 1, 63, 10, 1, 0, 0),       # width1 = 7 < one staging chunk
 ]
 
 
