@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb2stereo.so")
+LIB_PATH = os.environ.get("B2S_LIB_PATH") or os.path.join(_HERE, "libb2stereo.so")   # override: A/B builds
 
 OK, E_INVALID, E_UNSUPPORTED, E_CUDA, E_NOMEM = 0, 1, 2, 3, 4
 DT_U8, DT_I16, DT_I32, DT_F32 = 0, 1, 2, 3

@@ -29,6 +29,11 @@ def _stale(target, deps):
 
 
 def build(force=False, verbose=False):
+    global OBJ, LIB
+    extra = os.environ.get("B2S_NVCC_EXTRA", "").split()      # A/B builds: e.g. -DB2S_WAVE_NT8=256
+    if extra:
+        tag = "".join(c if c.isalnum() else "_" for c in "".join(extra))
+        OBJ, LIB = os.path.join(HERE, "_obj" + tag), os.path.join(HERE, "libb2stereo%s.so" % tag)
     os.makedirs(OBJ, exist_ok=True)
     headers = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "sgbm_wave.cuh"), os.path.join(CSRC, "sgbm_wave_impl.cuh"), os.path.join(HERE, "..", "include", "b2stereo.h")]
     jobs = []
@@ -40,7 +45,7 @@ def build(force=False, verbose=False):
 
     def compile_one(job):
         src, obj = job
-        r = subprocess.run([_nvcc()] + NVCC_FLAGS + ["-c", src, "-o", obj], capture_output=True, text=True)
+        r = subprocess.run([_nvcc()] + NVCC_FLAGS + extra + ["-c", src, "-o", obj], capture_output=True, text=True)
         log = obj.replace(".o", ".ptxas.log")
         with open(log, "w") as f:
             f.write(r.stderr)

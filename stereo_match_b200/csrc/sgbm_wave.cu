@@ -1,7 +1,7 @@
 // sgbm_wave.cu -- host side of the fused wavefront aggregation (see sgbm_wave.cuh).
 #include "sgbm_wave.cuh"
 
-int b2s_wave_rows_per_band(const SgbmEff& e) { return 256 / e.G; }
+int b2s_wave_rows_per_band(const SgbmEff& e) { return wave::threads_for(e.G) / e.G; }
 
 static size_t al256(size_t v) { return (v + 255) / 256 * 256; }
 

@@ -40,6 +40,12 @@ struct WaveArgs {
     int nbands;
 };
 
+// threads per CTA of the wavefront kernel: small CTAs keep the per-step barrier cheap and let
+// several independent bands share an SM
+#ifndef B2S_WAVE_NT8
+#define B2S_WAVE_NT8 256
+#endif
+namespace wave { constexpr int threads_for(int G) { return G == 8 ? B2S_WAVE_NT8 : 256; } }
 int b2s_wave_rows_per_band(const SgbmEff& e);
 size_t b2s_wave_edge_bytes(const SgbmEff& e);       // edge + edge_min + progress + ticket
 int b2s_launch_wave(const SgbmEff& e, const uint16_t* cost, uint16_t* S, uint16_t* S_dbg, void* edge_ws,

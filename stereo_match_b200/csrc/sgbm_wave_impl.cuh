@@ -4,7 +4,6 @@
 
 namespace wave {
 
-constexpr int NT = 256;
 
 // ---- R packed registers <-> memory (generic address space; 16/8/4-byte vectors) ---------------
 template <int R>
@@ -114,7 +113,7 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // shared-memory plan (bytes), shared by host and device
-template <int R, int G, bool VERT, bool FINAL>
+template <int R, int G, int NT, bool VERT, bool FINAL>
 struct Plan {
     static constexpr int RB = NT / G;
     static constexpr int DP = 2 * R * G;
@@ -215,11 +214,11 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
     __syncwarp();
 }
 
-template <int R, int G, bool PAD, bool VERT, bool FINAL>
-__global__ void __launch_bounds__(NT, (G == 32 ? 1 : 2))
+template <int R, int G, int NT, bool PAD, bool VERT, bool FINAL>
+__global__ void __launch_bounds__(NT, (G == 32 ? 1 : 512 / NT))
 k_wave(SgbmEff e, WaveArgs a)
 {
-    using P = Plan<R, G, VERT, FINAL>;
+    using P = Plan<R, G, NT, VERT, FINAL>;
     constexpr int RB = P::RB, DP = P::DP, CH = P::CH;
     extern __shared__ __align__(16) unsigned char smem[];
     uint16_t* const ring1 = reinterpret_cast<uint16_t*>(smem + P::ring1);
@@ -240,7 +239,10 @@ k_wave(SgbmEff e, WaveArgs a)
     }
     __syncthreads();
     const int item = *s_item;
-    const int b = item / a.nbands, band = item - b * a.nbands;
+    // band-major order: every band-k item precedes all band-(k+1) items, so a consumer's producer
+    // holds an earlier ticket and, with more than a few pairs in flight, is already far ahead
+    const int band = item / e.batch, b = item - band * e.batch;
+    const int eitem = b * a.nbands + band;              // slot in the edge / progress arrays
     const int g = threadIdx.x / G, lane = threadIdx.x % G;
     const int w1 = e.width1;
     const int ys = band * RB + g;
@@ -274,10 +276,10 @@ k_wave(SgbmEff e, WaveArgs a)
     for (int i = 0; i < R; i++) { Lh[i] = 0; C[i] = 0; Cn[i] = 0; S1[i] = 0; S1n[i] = 0; }
 
     // edge stream of the band above: producer item = item - 1
-    const uint16_t* const eabove = a.edge + (size_t)(item - 1) * w1 * 3 * DP;
-    const uint32_t* const eabove_min = a.edge_min + (size_t)(item - 1) * w1 * 4;
-    uint16_t* const ebelow = a.edge + (size_t)item * w1 * 3 * DP;
-    uint32_t* const ebelow_min = a.edge_min + (size_t)item * w1 * 4;
+    const uint16_t* const eabove = a.edge + (size_t)(eitem - 1) * w1 * 3 * DP;
+    const uint32_t* const eabove_min = a.edge_min + (size_t)(eitem - 1) * w1 * 4;
+    uint16_t* const ebelow = a.edge + (size_t)eitem * w1 * 3 * DP;
+    uint32_t* const ebelow_min = a.edge_min + (size_t)eitem * w1 * 4;
     auto stage_chunk = [&](int c) {          // cp.async chunk c of the edge stream into stage[c & 1]
         const int x0 = c * CH, npx = min(CH, w1 - x0);
         const int n16 = npx * 3 * DP * 2 / 16;
@@ -288,7 +290,7 @@ k_wave(SgbmEff e, WaveArgs a)
             cp_async16(stagemin + ((c & 1) * CH + threadIdx.x) * 4, eabove_min + (size_t)(x0 + threadIdx.x) * 4);
     };
     auto wait_progress = [&](int need) {
-        const int* p = a.progress + (item - 1);
+        const int* p = a.progress + (eitem - 1);
         while (ld_acquire(p) < need) __nanosleep(64);
     };
     if (has_above) {
@@ -311,7 +313,12 @@ k_wave(SgbmEff e, WaveArgs a)
     int pend = 0;
 
     for (int t = 0; t < T; t++) {
-        if (VERT && pend) { __threadfence(); st_release(a.progress + item, pend); pend = 0; }
+        if (has_below) {                       // uniform: last row finished pixel t-1-SKEW*gl in the previous step
+            const int xdone = t - SKEW * gl;
+            if ((xdone % CH) == 0 || xdone == w1) {
+                if (pend) { st_release(a.progress + eitem, pend); pend = 0; }
+            }
+        }
         const int xs = t - SKEW * g;
         const bool act = rowact && xs >= 0 && xs < w1;
         const int xreal = xorg + xsign * xs;
@@ -340,8 +347,9 @@ k_wave(SgbmEff e, WaveArgs a)
         for (int i = 0; i < R; i++) Sv[i] = FINAL ? __viaddmin_u16x2(S1[i], Lh[i], 0x7fff7fffu) : Lh[i];
 
         if (VERT) {
-            uint32_t Lv[R];
-            uint32_t mnv[3];
+            // all shared-memory reads of the step first, all writes last: the three directions
+            // and the row direction are then independent instruction streams
+            uint32_t Lv[3][R], minv[3], mnv[3];
 #pragma unroll
             for (int k = 1; k <= 3; k++) {
                 const int xp = xs + (k == 1 ? -1 : (k == 3 ? 1 : 0));
@@ -360,18 +368,24 @@ k_wave(SgbmEff e, WaveArgs a)
                         msrc = stagemin + slot * 4 + (k - 1);
                     }
                 }
-                ld_regs<R>(src + lane * 2 * R, Lv);
-                const uint32_t minv = *msrc;
-                mnv[k - 1] = step<R, G, PAD>(Lv, C, lane, p1x2, p2m1x2, minv, padm);
+                ld_regs<R>(src + lane * 2 * R, Lv[k - 1]);
+                minv[k - 1] = *msrc;
+            }
 #pragma unroll
-                for (int i = 0; i < R; i++) Sv[i] = __viaddmin_u16x2(Sv[i], Lv[i], 0x7fff7fffu);
-                if (act) {
-                    uint16_t* dst;
-                    if (k == 1) dst = ring1 + (g * 4 + (xs & 3)) * DP;
-                    else if (k == 2) dst = ring2 + (g * 4 + (xs & 3)) * DP;
-                    else dst = ring3 + (g * 2 + (xs & 1)) * DP;
-                    st_regs<R>(dst + lane * 2 * R, Lv);
-                    if (has_below && g == gl) st_regs<R>(ebelow + ((size_t)xs * 3 + (k - 1)) * DP + lane * 2 * R, Lv);
+            for (int k = 0; k < 3; k++) {
+                mnv[k] = step<R, G, PAD>(Lv[k], C, lane, p1x2, p2m1x2, minv[k], padm);
+#pragma unroll
+                for (int i = 0; i < R; i++) Sv[i] = __viaddmin_u16x2(Sv[i], Lv[k][i], 0x7fff7fffu);
+            }
+            if (act) {
+                st_regs<R>(ring1 + (g * 4 + (xs & 3)) * DP + lane * 2 * R, Lv[0]);
+                st_regs<R>(ring2 + (g * 4 + (xs & 3)) * DP + lane * 2 * R, Lv[1]);
+                st_regs<R>(ring3 + (g * 2 + (xs & 1)) * DP + lane * 2 * R, Lv[2]);
+                if (has_below && g == gl) {
+                    uint16_t* ge = ebelow + (size_t)xs * 3 * DP + lane * 2 * R;
+                    st_regs<R>(ge, Lv[0]);
+                    st_regs<R>(ge + DP, Lv[1]);
+                    st_regs<R>(ge + 2 * DP, Lv[2]);
                 }
             }
             // two packed reductions for the four minima
@@ -401,10 +415,9 @@ k_wave(SgbmEff e, WaveArgs a)
 
         // ---- band pipeline bookkeeping -----------------------------------------------------------
         if (VERT) {
-            if (has_below && g == gl && act && (((xs + 1) % CH) == 0 || xs == w1 - 1)) {
-                __threadfence();
-                if (lane == 0) pend = xs + 1;
-            }
+            // publish after the step's barrier: the release store of one thread is cumulative over
+            // the edge stores the other lanes made before that barrier
+            if (has_below && g == gl && act && lane == 0 && (((xs + 1) % CH) == 0 || xs == w1 - 1)) pend = xs + 1;
             if (has_above) {
                 if ((t % CH) == CH - 2) cp_async_wait_all();
                 if ((t % CH) == 1 && threadIdx.x == 0) {
@@ -417,20 +430,20 @@ k_wave(SgbmEff e, WaveArgs a)
         for (int i = 0; i < R; i++) { C[i] = Cn[i]; if (FINAL) S1[i] = S1n[i]; }
         if (VERT) __syncthreads();
     }
-    if (VERT && pend) { __threadfence(); st_release(a.progress + item, pend); }
+    if (VERT && pend) st_release(a.progress + eitem, pend);
 }
 
-template <int R, int G, bool PAD, bool VERT, bool FINAL>
+template <int R, int G, int NT, bool PAD, bool VERT, bool FINAL>
 int launch_one(const SgbmEff& e, const WaveArgs& a, cudaStream_t st)
 {
-    using P = Plan<R, G, VERT, FINAL>;
+    using P = Plan<R, G, NT, VERT, FINAL>;
     static bool configured = false;
     if (!configured) {
-        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_wave<R, G, PAD, VERT, FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
+        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_wave<R, G, NT, PAD, VERT, FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
         configured = true;
     }
     const int grid = e.batch * a.nbands;
-    k_wave<R, G, PAD, VERT, FINAL><<<grid, NT, P::total, st>>>(e, a);
+    k_wave<R, G, NT, PAD, VERT, FINAL><<<grid, NT, P::total, st>>>(e, a);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
 }
@@ -438,10 +451,11 @@ int launch_one(const SgbmEff& e, const WaveArgs& a, cudaStream_t st)
 template <int R, int G>
 int launch_rg(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
 {
+    constexpr int NT = threads_for(G);
     const bool pad = e.D != e.Dp;
-    if (vert && !final) return pad ? launch_one<R, G, true, true, false>(e, a, st) : launch_one<R, G, false, true, false>(e, a, st);
-    if (vert && final) return pad ? launch_one<R, G, true, true, true>(e, a, st) : launch_one<R, G, false, true, true>(e, a, st);
-    if (!vert && final) return pad ? launch_one<R, G, true, false, true>(e, a, st) : launch_one<R, G, false, false, true>(e, a, st);
+    if (vert && !final) return pad ? launch_one<R, G, NT, true, true, false>(e, a, st) : launch_one<R, G, NT, false, true, false>(e, a, st);
+    if (vert && final) return pad ? launch_one<R, G, NT, true, true, true>(e, a, st) : launch_one<R, G, NT, false, true, true>(e, a, st);
+    if (!vert && final) return pad ? launch_one<R, G, NT, true, false, true>(e, a, st) : launch_one<R, G, NT, false, false, true>(e, a, st);
     b2s_set_error("wave: unsupported pass combination");
     return B2S_E_INVALID;
 }
