@@ -83,6 +83,7 @@ __device__ __forceinline__ uint32_t bt_pair(uint32_t wl, uint32_t wa, uint32_t w
     return __vminu2(c0, c1) - B2S_BIAS;
 }
 
+// Generic cost kernel (any blockSize, Dp <= 2048).
 // One CTA: column strip [x0, x0+TW) of the cropped axis, row band [yb, yb+TR), all Dp.
 // Marches down the band; per row: pixel costs for TW+2*SW2 columns -> smem, horizontal
 // sum, vertical running sum through a ring of blockSize horizontal sums in smem.
@@ -170,7 +171,215 @@ k_cost(const uint2* __restrict__ descL, const uint2* __restrict__ descR, SgbmEff
     if (2 * (int)m + 3 * e.P2 > 32767) atomicOr(overflow_flag, 1);
 }
 
+// ---------------------------------------------------------------------------
+// Fast cost kernel (blockSize <= 11, Dp <= 256).
+// CTA = 32 columns of pixel costs (32 - (BS-1) output columns) x all Dp disparities, marching
+// down a band of rows.  Warp w owns disparities [8w, 8w+8); lane l owns column l.
+//   stage   : left descriptor words of the row -> smem; right descriptors -> six u16 planes
+//             (value, lo, hi of the Sobel and of the raw channel) in REVERSED x order, each in
+//             two copies offset by one element, so that the pair (x-d, x-d-1) is one aligned
+//             32-bit word: packed u16x2 operands come straight out of LDS with no byte shuffles
+//   phase A : BT cost of (column, 8 disparities) -> pix[column][d] (smem, u16x2)
+//   phase B : horizontal BS-sum from smem, vertical running sum through a ring of BS rows held
+//             in registers (the row loop is unrolled by BS), one 16-byte store per thread
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t bt2(uint32_t u, uint32_t lo1, uint32_t hi1, uint32_t v, uint32_t lo2, uint32_t hi2)
+{
+    uint32_t A = u + B2S_BIAS - hi2;
+    uint32_t Bv = lo2 + B2S_BIAS - u;
+    uint32_t Cv = v + B2S_BIAS - hi1;
+    uint32_t Dv = lo1 + B2S_BIAS - v;
+    return __vminu2(__vimax3_u16x2(A, Bv, B2S_BIAS), __vimax3_u16x2(Cv, Dv, B2S_BIAS));   // biased by 0x0100
+}
+
+template <int BS, int MAXW, bool PAD>
+__global__ void __launch_bounds__(32 * MAXW, (MAXW == 16 && BS <= 7) ? 2 : 1)
+k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, SgbmEff e, int TR, int NELP,
+            uint16_t* __restrict__ cost, int* __restrict__ overflow_flag)
+{
+    constexpr int SW2 = BS / 2, TW = 32 - (BS - 1);
+    extern __shared__ __align__(16) unsigned char smem_c[];
+    const int Dp = e.Dp;
+    const int lane = threadIdx.x & 31, oct = threadIdx.x >> 5, nthreads = blockDim.x;
+    // smem: [2] x { LW[32] uint2 , planes[6][2][NELP] u16 }  then per-warp pix exchange [32 lanes][8] u16
+    const int stage_bytes = 256 + 12 * NELP * 2;
+    uint16_t* const pixw = reinterpret_cast<uint16_t*>(smem_c + 2 * stage_bytes) + (size_t)oct * 32 * 8;
+    const int x0 = blockIdx.x * TW, yb = blockIdx.y * TR;
+    const size_t b = blockIdx.z;
+    const int yend = min(yb + TR, e.H);
+    const uint2* const dL = descL + b * (size_t)e.H * e.W;
+    const uint2* const dR = descR + b * (size_t)e.H * e.W;
+    uint16_t* const out = cost + b * (size_t)e.H * e.width1 * Dp;
+
+    // phase A geometry of this thread (row independent)
+    const int xiA = min(max(x0 - SW2 + lane, 0), e.width1 - 1) + e.minX1;     // clamp on the cropped axis
+    const int XRM = min(max(x0 - SW2 + 31, 0), e.width1 - 1) + e.minX1 - e.minD;
+    const int e0 = XRM - (xiA - e.minD - 8 * oct);                            // first reversed element
+    const int par = e0 & 1;
+    const int roff = 256 + (par * NELP) * 2 + ((e0 - par) >> 1) * 4;          // byte offset inside a stage buffer
+    const int pstride = NELP;                                                 // u32 words between planes (2 copies each)
+    // phase B geometry
+    const int xB = x0 + lane;
+    const bool outB = lane < TW && xB < e.width1;
+    uint32_t pmask[4];
+#pragma unroll
+    for (int w = 0; w < 4; w++) {
+        int d0 = 8 * oct + 2 * w;
+        pmask[w] = (d0 < e.D ? 0xffffu : 0u) | (d0 + 1 < e.D ? 0xffff0000u : 0u);
+    }
+    // staging role of this thread: element `sel` of the reversed right row (threads beyond nel idle),
+    // threads of the last warp additionally fetch the left words
+    const int nel = 32 + Dp;
+    const int sel = threadIdx.x;                         // nel <= blockDim.x + 32: second element for the first 32 threads
+    const int xr1 = XRM - sel, xr2 = XRM - (sel + nthreads);
+    const bool st1 = sel < nel && xr1 >= 0 && xr1 < e.W, st2 = sel + nthreads < nel && xr2 >= 0 && xr2 < e.W;
+    const bool stL = oct == (nthreads >> 5) - 1;
+
+    auto stage_load = [&](int yv, uint2& w1, uint2& w2, uint2& wl) {
+        const int yr = min(max(yv, 0), e.H - 1);
+        const uint2* rowR = dR + (size_t)yr * e.W;
+        w1 = make_uint2(0u, 0u); w2 = make_uint2(0u, 0u); wl = make_uint2(0u, 0u);
+        if (st1) w1 = __ldg(rowR + xr1);
+        if (st2) w2 = __ldg(rowR + xr2);
+        if (stL) wl = __ldg(dL + (size_t)yr * e.W + xiA);
+    };
+    auto stage_put = [&](unsigned char* buf, int el, const uint2& w) {
+        uint16_t* planes = reinterpret_cast<uint16_t*>(buf + 256);
+        const uint32_t vals[6] = { w.x & 0xffu, (w.x >> 8) & 0xffu, (w.x >> 16) & 0xffu,
+                                   w.y & 0xffu, (w.y >> 8) & 0xffu, (w.y >> 16) & 0xffu };
+#pragma unroll
+        for (int p = 0; p < 6; p++) {
+            planes[(2 * p) * NELP + el] = (uint16_t)vals[p];
+            if (el > 0) planes[(2 * p + 1) * NELP + el - 1] = (uint16_t)vals[p];
+        }
+    };
+    auto stage_store = [&](int bufi, const uint2& w1, const uint2& w2, const uint2& wl) {
+        unsigned char* buf = smem_c + bufi * stage_bytes;
+        if (sel < nel) stage_put(buf, sel, w1);
+        if (sel + nthreads < nel) stage_put(buf, sel + nthreads, w2);
+        if (stL) reinterpret_cast<uint2*>(buf)[lane] = wl;
+    };
+
+    uint32_t acc[4] = { 0, 0, 0, 0 }, ring[BS][4], vmax = 0;
+#pragma unroll
+    for (int s = 0; s < BS; s++) { ring[s][0] = ring[s][1] = ring[s][2] = ring[s][3] = 0; }
+
+    {   // first row
+        uint2 w1, w2, wl;
+        stage_load(yb - SW2, w1, w2, wl);
+        stage_store(0, w1, w2, wl);
+    }
+    __syncthreads();
+    int cur = 0;
+    for (int yv0 = yb - SW2; yv0 < yend + SW2; yv0 += BS) {
+#pragma unroll
+        for (int s = 0; s < BS; s++) {
+            const int yv = yv0 + s;
+            if (yv >= yend + SW2) break;                   // uniform
+            // next row's descriptors travel while this row is computed
+            uint2 nw1, nw2, nwl;
+            const bool more = yv + 1 < yend + SW2;
+            if (more) stage_load(yv + 1, nw1, nw2, nwl);
+            const unsigned char* const buf = smem_c + cur * stage_bytes;
+            // ---- phase A: pixel costs of (column, 8 disparities) --------------------------------
+            {
+                const uint2 wl = reinterpret_cast<const uint2*>(buf)[lane];
+                const uint32_t* const rbase = reinterpret_cast<const uint32_t*>(buf + roff);
+                const uint32_t ug = __byte_perm(wl.x, 0, 0x4040), log = __byte_perm(wl.x, 0, 0x4141), hig = __byte_perm(wl.x, 0, 0x4242);
+                const uint32_t ur = __byte_perm(wl.y, 0, 0x4040), lor = __byte_perm(wl.y, 0, 0x4141), hir = __byte_perm(wl.y, 0, 0x4242);
+                uint32_t pc[4];
+#pragma unroll
+                for (int w = 0; w < 4; w++) {
+                    const uint32_t cg = bt2(ug, log, hig, rbase[w], rbase[pstride + w], rbase[2 * pstride + w]);
+                    const uint32_t cr = bt2(ur, lor, hir, rbase[3 * pstride + w], rbase[4 * pstride + w], rbase[5 * pstride + w]);
+                    // (cr - bias) >> 2 == ((cr >> 2) & 0x7f) - 0x40 per half
+                    pc[w] = cg + ((cr >> 2) & 0x007f007fu) - (B2S_BIAS + 0x00400040u);
+                }
+                *reinterpret_cast<uint4*>(pixw + lane * 8) = make_uint4(pc[0], pc[1], pc[2], pc[3]);
+            }
+            __syncwarp();
+            // ---- phase B: box sums (the BS columns are neighbouring lanes of this warp) -----------
+            {
+                uint32_t hs[4] = { 0, 0, 0, 0 };
+#pragma unroll
+                for (int k = 0; k < BS; k++) {
+                    const uint4 v = *reinterpret_cast<const uint4*>(pixw + (lane < TW ? lane + k : lane) * 8);
+                    hs[0] += v.x; hs[1] += v.y; hs[2] += v.z; hs[3] += v.w;
+                }
+#pragma unroll
+                for (int w = 0; w < 4; w++) {
+                    acc[w] += hs[w] - ring[s][w];          // halves never borrow: acc >= old contribution
+                    ring[s][w] = hs[w];
+                }
+                // a half can only wrap past 0xffff after first being seen >= 0x8000
+                vmax = __vimax3_u16x2(vmax, __vmaxu2(acc[0], acc[1]), __vmaxu2(acc[2], acc[3]));
+                const int yo = yv - SW2;
+                if (outB && yo >= yb) {
+                    uint4 o = make_uint4(acc[0], acc[1], acc[2], acc[3]);
+                    if (PAD) { o.x &= pmask[0]; o.y &= pmask[1]; o.z &= pmask[2]; o.w &= pmask[3]; }
+                    *reinterpret_cast<uint4*>(out + ((size_t)yo * e.width1 + xB) * Dp + 8 * oct) = o;
+                }
+            }
+            if (more) stage_store(cur ^ 1, nw1, nw2, nwl);
+            cur ^= 1;
+            __syncthreads();
+        }
+    }
+    if (PAD) vmax &= (pmask[0] | pmask[1] | pmask[2] | pmask[3]);   // coarse: padded lanes never decide
+    uint32_t m = max(vmax & 0xffffu, vmax >> 16);
+    if (lane >= TW) m = 0;
+    if (2 * (int)m + 3 * e.P2 > 32767) atomicOr(overflow_flag, 1);
+}
+
+template <int BS, int MAXW>
+static int launch_cost_fast(const uint2* descL, const uint2* descR, const SgbmEff& e, uint16_t* cost, int* flag, cudaStream_t st)
+{
+    constexpr int TW = 32 - (BS - 1);
+    const int nel = 32 + e.Dp;
+    const int NELP = (nel + 63) / 64 * 64 + 32;            // copies land 64 bytes apart modulo 128: disjoint banks
+    const size_t smem = 2 * (256 + (size_t)12 * NELP * 2) + (size_t)(e.Dp / 8) * 512;
+    const int TR = 75;
+    dim3 grid(b2s_cdiv(e.width1, TW), b2s_cdiv(e.H, TR), e.batch);
+    const int nthreads = 32 * (e.Dp / 8);
+    if (e.D != e.Dp) {
+        if (smem > 48 * 1024) B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_cost_fast<BS, MAXW, true><<<grid, nthreads, smem, st>>>(descL, descR, e, TR, NELP, cost, flag);
+    } else {
+        if (smem > 48 * 1024) B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_cost_fast<BS, MAXW, false><<<grid, nthreads, smem, st>>>(descL, descR, e, TR, NELP, cost, flag);
+    }
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}
+
+static int b2s_launch_cost_generic(const uint2* descL, const uint2* descR, const SgbmEff& e, uint16_t* cost,
+                                   int* overflow_flag, cudaStream_t st);
+
 int b2s_launch_cost(const uint2* descL, const uint2* descR, const SgbmEff& e, uint16_t* cost,
+                    int* overflow_flag, cudaStream_t st)
+{
+    const int bs = 2 * e.SW2 + 1;
+    if (e.Dp <= 128) {
+        switch (bs) {
+        case 1: return launch_cost_fast<1, 16>(descL, descR, e, cost, overflow_flag, st);
+        case 3: return launch_cost_fast<3, 16>(descL, descR, e, cost, overflow_flag, st);
+        case 5: return launch_cost_fast<5, 16>(descL, descR, e, cost, overflow_flag, st);
+        case 7: return launch_cost_fast<7, 16>(descL, descR, e, cost, overflow_flag, st);
+        case 9: return launch_cost_fast<9, 16>(descL, descR, e, cost, overflow_flag, st);
+        case 11: return launch_cost_fast<11, 16>(descL, descR, e, cost, overflow_flag, st);
+        }
+    } else if (e.Dp <= 256) {
+        switch (bs) {
+        case 1: return launch_cost_fast<1, 32>(descL, descR, e, cost, overflow_flag, st);
+        case 3: return launch_cost_fast<3, 32>(descL, descR, e, cost, overflow_flag, st);
+        case 5: return launch_cost_fast<5, 32>(descL, descR, e, cost, overflow_flag, st);
+        case 7: return launch_cost_fast<7, 32>(descL, descR, e, cost, overflow_flag, st);
+        }
+    }
+    return b2s_launch_cost_generic(descL, descR, e, cost, overflow_flag, st);
+}
+
+static int b2s_launch_cost_generic(const uint2* descL, const uint2* descR, const SgbmEff& e, uint16_t* cost,
                     int* overflow_flag, cudaStream_t st)
 {
     const int DP2 = e.Dp / 2, bs = 2 * e.SW2 + 1;
