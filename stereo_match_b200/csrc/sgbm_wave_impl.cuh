@@ -110,6 +110,24 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
     unsigned s = (unsigned)__cvta_generic_to_shared(smem);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
 }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar)
+{
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // shared-memory plan (bytes), shared by host and device
@@ -128,6 +146,7 @@ struct Plan {
     static constexpr int stagemin = ringmin + (VERT ? RB * 16 * 4 : 0);    // [2][CH][4] u32
     static constexpr int zeromin = stagemin + (VERT ? 2 * CH * 4 * 4 : 0); // [4] u32
     static constexpr int item = zeromin + 16;
+    static constexpr int bar = item + 8;                                   // mbarrier (8 bytes, 8-aligned)
     static constexpr int total = item + 16;
 };
 
@@ -231,8 +250,13 @@ k_wave(SgbmEff e, WaveArgs a)
     uint32_t* const stagemin = reinterpret_cast<uint32_t*>(smem + P::stagemin);
     uint32_t* const zeromin = reinterpret_cast<uint32_t*>(smem + P::zeromin);
     int* const s_item = reinterpret_cast<int*>(smem + P::item);
+    unsigned long long* const s_bar = reinterpret_cast<unsigned long long*>(smem + P::bar);
 
-    if (threadIdx.x == 0) *s_item = VERT ? (int)atomicAdd(a.ticket, 1u) : (int)blockIdx.x;
+    if (threadIdx.x == 0) {
+        *s_item = VERT ? (int)atomicAdd(a.ticket, 1u) : (int)blockIdx.x;
+        mbar_init((unsigned)__cvta_generic_to_shared(s_bar), NT / 32);        // one arrival per warp and step
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     if (VERT) {
         for (int i = threadIdx.x; i < DP / 2; i += NT) reinterpret_cast<uint32_t*>(zero)[i] = 0u;
         if (threadIdx.x < 4) zeromin[threadIdx.x] = 0u;
@@ -311,8 +335,13 @@ k_wave(SgbmEff e, WaveArgs a)
         }
     }
     int pend = 0;
+    unsigned phase = 0;
+    const unsigned bar_addr = (unsigned)__cvta_generic_to_shared(s_bar);
 
-    for (int t = 0; t < T; t++) {
+    // One wavefront step.  Cc/S1c: operands of this step, Cx/S1x: prefetch targets for the next one
+    // (the caller alternates the two register sets, so nothing is copied).
+    auto body = [&](const int t, uint32_t (&Cc)[R], uint32_t (&Cx)[R], uint32_t (&S1c)[R], uint32_t (&S1x)[R]) {
+        if (VERT && t > 0) { mbar_wait(bar_addr, phase); phase ^= 1u; }   // every warp finished step t-1's ring stores
         if (has_below) {                       // uniform: last row finished pixel t-1-SKEW*gl in the previous step
             const int xdone = t - SKEW * gl;
             if ((xdone % CH) == 0 || xdone == w1) {
@@ -323,7 +352,7 @@ k_wave(SgbmEff e, WaveArgs a)
         const bool act = rowact && xs >= 0 && xs < w1;
         const int xreal = xorg + xsign * xs;
         const size_t off = (size_t)xreal * DP;
-        if (has_above && (t % CH) == 2 % CH && t >= 2) {         // chunk staging (polled at the end of step t-1)
+        if (has_above && (t % CH) == 2 && t >= 2) {              // chunk staging (polled during step t-1)
             const int c = (t - 2) / CH + 1;
             if (c * CH < w1) stage_chunk(c);
         }
@@ -332,23 +361,17 @@ k_wave(SgbmEff e, WaveArgs a)
             const int xn = xs + 1;
             const bool actn = rowact && xn >= 0 && xn < w1;
 #pragma unroll
-            for (int i = 0; i < R; i++) { Cn[i] = 0; }
+            for (int i = 0; i < R; i++) { Cx[i] = 0; }
             if (actn) {
                 const size_t offn = (size_t)(xorg + xsign * xn) * DP;
-                ldg_regs_stream<R>(cb + offn, Cn);
-                if (FINAL) ldg_regs_stream<R>(sb + offn, S1n);
+                ldg_regs_stream<R>(cb + offn, Cx);
+                if (FINAL) ldg_regs_stream<R>(sb + offn, S1x);
             }
         }
 
         uint32_t Sv[R];
-        // ---- direction 0: along the row, state in registers -------------------------------
-        uint32_t mn0 = step<R, G, PAD>(Lh, C, lane, p1x2, p2m1x2, minh, padm);
-#pragma unroll
-        for (int i = 0; i < R; i++) Sv[i] = FINAL ? __viaddmin_u16x2(S1[i], Lh[i], 0x7fff7fffu) : Lh[i];
-
         if (VERT) {
-            // all shared-memory reads of the step first, all writes last: the three directions
-            // and the row direction are then independent instruction streams
+            // ---- the three directions that come from the row above: ring -> registers -> ring -----
             uint32_t Lv[3][R], minv[3], mnv[3];
 #pragma unroll
             for (int k = 1; k <= 3; k++) {
@@ -363,7 +386,7 @@ k_wave(SgbmEff e, WaveArgs a)
                         else src = ring3 + ((g - 1) * 2 + (xp & 1)) * DP;
                         msrc = ringmin + ((g - 1) * 4 + (xp & 3)) * 4 + k;
                     } else {
-                        const int slot = ((xp / CH) & 1) * CH + (xp % CH);
+                        const int slot = xp & (2 * CH - 1);
                         src = stage + (slot * 3 + (k - 1)) * DP;
                         msrc = stagemin + slot * 4 + (k - 1);
                     }
@@ -372,11 +395,7 @@ k_wave(SgbmEff e, WaveArgs a)
                 minv[k - 1] = *msrc;
             }
 #pragma unroll
-            for (int k = 0; k < 3; k++) {
-                mnv[k] = step<R, G, PAD>(Lv[k], C, lane, p1x2, p2m1x2, minv[k], padm);
-#pragma unroll
-                for (int i = 0; i < R; i++) Sv[i] = __viaddmin_u16x2(Sv[i], Lv[k][i], 0x7fff7fffu);
-            }
+            for (int k = 0; k < 3; k++) mnv[k] = step<R, G, PAD>(Lv[k], Cc, lane, p1x2, p2m1x2, minv[k], padm);
             if (act) {
                 st_regs<R>(ring1 + (g * 4 + (xs & 3)) * DP + lane * 2 * R, Lv[0]);
                 st_regs<R>(ring2 + (g * 4 + (xs & 3)) * DP + lane * 2 * R, Lv[1]);
@@ -388,36 +407,17 @@ k_wave(SgbmEff e, WaveArgs a)
                     st_regs<R>(ge + 2 * DP, Lv[2]);
                 }
             }
-            // two packed reductions for the four minima
-            uint32_t r01 = group_min_x2<G>(half_min(mn0) | (half_min(mnv[0]) << 16));
-            uint32_t r23 = group_min_x2<G>(half_min(mnv[1]) | (half_min(mnv[2]) << 16));
-            minh = (r01 & 0xffffu) * 0x10001u;
+            const uint32_t r12 = group_min_x2<G>(half_min(mnv[0]) | (half_min(mnv[1]) << 16));
+            const uint32_t r3 = group_min_x2<G>(half_min(mnv[2]));
             if (act && lane == 0) {
                 uint32_t* md = ringmin + (g * 4 + (xs & 3)) * 4;
-                const uint32_t m1 = (r01 >> 16) * 0x10001u, m2 = (r23 & 0xffffu) * 0x10001u, m3 = (r23 >> 16) * 0x10001u;
+                const uint32_t m1 = (r12 & 0xffffu) * 0x10001u, m2 = (r12 >> 16) * 0x10001u, m3 = (r3 & 0xffffu) * 0x10001u;
                 md[1] = m1; md[2] = m2; md[3] = m3;
                 if (has_below && g == gl) {
                     uint32_t* ge = ebelow_min + (size_t)xs * 4;
                     ge[0] = m1; ge[1] = m2; ge[2] = m3;
                 }
             }
-        } else {
-            minh = group_min_x2<G>(half_min(mn0)) * 0x10001u;
-        }
-
-        // ---- S ------------------------------------------------------------------------------
-        if (FINAL) {
-            wta<R, G, PAD>(Sv, lane, e, a.magic, scratch + g * DP, act, rowpix, xreal, a.rec, a.disp2key);
-            if (a.S_out != nullptr && act) st_regs<R>(a.S_out + rowoff + off, Sv);
-        } else {
-            if (act) st_regs<R>(sb + off, Sv);
-        }
-
-        // ---- band pipeline bookkeeping -----------------------------------------------------------
-        if (VERT) {
-            // publish after the step's barrier: the release store of one thread is cumulative over
-            // the edge stores the other lanes made before that barrier
-            if (has_below && g == gl && act && lane == 0 && (((xs + 1) % CH) == 0 || xs == w1 - 1)) pend = xs + 1;
             if (has_above) {
                 if ((t % CH) == CH - 2) cp_async_wait_all();
                 if ((t % CH) == 1 && threadIdx.x == 0) {
@@ -425,12 +425,50 @@ k_wave(SgbmEff e, WaveArgs a)
                     if (c * CH < w1) wait_progress(min((c + 1) * CH, w1));
                 }
             }
-        }
+            // this warp's part of step t is visible: arrive, and keep working on what no other row needs
+            __syncwarp();
+            if ((threadIdx.x & 31) == 0) mbar_arrive(bar_addr);
 #pragma unroll
-        for (int i = 0; i < R; i++) { C[i] = Cn[i]; if (FINAL) S1[i] = S1n[i]; }
-        if (VERT) __syncthreads();
+            for (int i = 0; i < R; i++) {
+                uint32_t v = __viaddmin_u16x2(Lv[0][i], Lv[1][i], 0x7fff7fffu);
+                v = __viaddmin_u16x2(v, Lv[2][i], 0x7fff7fffu);
+                Sv[i] = FINAL ? __viaddmin_u16x2(v, S1c[i], 0x7fff7fffu) : v;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < R; i++) Sv[i] = FINAL ? S1c[i] : 0u;
+        }
+        // ---- direction 0: along the row, state in registers -----------------------------------
+        const uint32_t mn0 = step<R, G, PAD>(Lh, Cc, lane, p1x2, p2m1x2, minh, padm);
+#pragma unroll
+        for (int i = 0; i < R; i++) Sv[i] = __viaddmin_u16x2(Sv[i], Lh[i], 0x7fff7fffu);
+        minh = (group_min_x2<G>(half_min(mn0)) & 0xffffu) * 0x10001u;
+
+        // ---- S ----------------------------------------------------------------------------------
+        if (FINAL) {
+            wta<R, G, PAD>(Sv, lane, e, a.magic, scratch + g * DP, act, rowpix, xreal, a.rec, a.disp2key);
+            if (a.S_out != nullptr && act) st_regs<R>(a.S_out + rowoff + off, Sv);
+        } else {
+            if (act) st_regs<R>(sb + off, Sv);
+        }
+        // publish after the next barrier: the release store of one thread is cumulative over the edge
+        // stores the other lanes made before they arrived
+        if (has_below && g == gl && act && lane == 0 && (((xs + 1) % CH) == 0 || xs == w1 - 1)) pend = xs + 1;
+    };
+
+    uint32_t C2[R], S2[R];
+#pragma unroll
+    for (int i = 0; i < R; i++) { C2[i] = 0; S2[i] = 0; }
+    (void)Cn; (void)S1n;
+#pragma unroll 1
+    for (int t = 0; t < T; t += 2) {
+        body(t, C, C2, S1, S2);
+        if (t + 1 < T) body(t + 1, C2, C, S2, S1);
     }
-    if (VERT && pend) st_release(a.progress + eitem, pend);
+    if (VERT && pend) {
+        mbar_wait(bar_addr, phase);
+        st_release(a.progress + eitem, pend);
+    }
 }
 
 template <int R, int G, int NT, bool PAD, bool VERT, bool FINAL>
