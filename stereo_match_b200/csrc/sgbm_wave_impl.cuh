@@ -55,6 +55,46 @@ __device__ __forceinline__ void st_regs(uint16_t* p, const uint32_t (&r)[R])
     }
 }
 
+// same, through a 32-bit shared-window address (no generic-pointer arithmetic in the hot loop)
+template <int R>
+__device__ __forceinline__ void lds_regs(unsigned addr, uint32_t (&r)[R])
+{
+    if constexpr (R % 4 == 0) {
+#pragma unroll
+        for (int i = 0; i < R / 4; i++)
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(r[4 * i]), "=r"(r[4 * i + 1]), "=r"(r[4 * i + 2]), "=r"(r[4 * i + 3]) : "r"(addr + 16 * i));
+    } else {
+#pragma unroll
+        for (int i = 0; i < R / 2; i++)
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(r[2 * i]), "=r"(r[2 * i + 1]) : "r"(addr + 8 * i));
+    }
+}
+template <int R>
+__device__ __forceinline__ void sts_regs(unsigned addr, const uint32_t (&r)[R])
+{
+    if constexpr (R % 4 == 0) {
+#pragma unroll
+        for (int i = 0; i < R / 4; i++)
+            asm volatile("st.shared.v4.u32 [%4], {%0, %1, %2, %3};"
+                         ::"r"(r[4 * i]), "r"(r[4 * i + 1]), "r"(r[4 * i + 2]), "r"(r[4 * i + 3]), "r"(addr + 16 * i) : "memory");
+    } else {
+#pragma unroll
+        for (int i = 0; i < R / 2; i++)
+            asm volatile("st.shared.v2.u32 [%2], {%0, %1};" ::"r"(r[2 * i]), "r"(r[2 * i + 1]), "r"(addr + 8 * i) : "memory");
+    }
+}
+__device__ __forceinline__ uint32_t lds_u32(unsigned addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts_u32(unsigned addr, uint32_t v)
+{
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
 template <int G>
 __device__ __forceinline__ uint32_t group_min_x2(uint32_t v)     // two independent u16 minima at once
 {
@@ -105,6 +145,8 @@ __device__ __forceinline__ void st_release(int* p, int v)
 {
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+// out of line on purpose: the fence sequence of a release store must not be if-converted into the step
+static __device__ __noinline__ void publish_progress(int* p, int v) { st_release(p, v); }
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
 {
     unsigned s = (unsigned)__cvta_generic_to_shared(smem);
@@ -123,7 +165,7 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity)
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, 0x989680;\n\t"
         "@p bra DONE_%=;\n\t"
         "bra WAIT_%=;\n\t"
         "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
@@ -325,6 +367,40 @@ k_wave(SgbmEff e, WaveArgs a)
         __syncthreads();
     }
 
+    // ---- loop-invariant addressing (32-bit shared-window addresses, running global pointers) -------
+    const unsigned sm0 = (unsigned)__cvta_generic_to_shared(smem);
+    const unsigned laneb = (unsigned)lane * 2 * R * 2;                 // byte offset of this lane's cells
+    // predecessor sources of the three vertical directions: the row above in the rings, or, for the
+    // band's first row, the staged edge stream; `rowok` false (very first row of the sweep): zeros
+    const bool rowok = g > 0 || has_above;
+    unsigned rsrc[3], rmask[3], msrc[3];
+    const unsigned rstr = (g > 0) ? DP * 2 : 3 * DP * 2;               // bytes between consecutive slots
+    const unsigned mmask = (g > 0) ? 3u : (unsigned)(2 * CH - 1);
+    if (g > 0) {
+        rsrc[0] = sm0 + P::ring1 + (g - 1) * 4 * DP * 2 + laneb; rmask[0] = 3;
+        rsrc[1] = sm0 + P::ring2 + (g - 1) * 4 * DP * 2 + laneb; rmask[1] = 3;
+        rsrc[2] = sm0 + P::ring3 + (g - 1) * 2 * DP * 2 + laneb; rmask[2] = 1;
+#pragma unroll
+        for (int k = 0; k < 3; k++) msrc[k] = sm0 + P::ringmin + (g - 1) * 64 + (k + 1) * 4;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            rsrc[k] = sm0 + P::stage + k * DP * 2 + laneb; rmask[k] = 2 * CH - 1;
+            msrc[k] = sm0 + P::stagemin + k * 4;
+        }
+    }
+    const unsigned zsrc = sm0 + P::zero + laneb, zmin = sm0 + P::zeromin;
+    const unsigned wdst1 = sm0 + P::ring1 + g * 4 * DP * 2 + laneb, wdst2 = sm0 + P::ring2 + g * 4 * DP * 2 + laneb,
+                   wdst3 = sm0 + P::ring3 + g * 2 * DP * 2 + laneb, wmin = sm0 + P::ringmin + g * 64;
+    const bool edgerow = has_below && g == gl;
+    const unsigned pubthread = (unsigned)gl * G;                        // lane 0 of the band's last row
+
+    // running pointers: element xs of this thread's row (linear in xs, also while xs is out of range)
+    const long long xstep = (long long)xsign * DP;
+    const uint16_t* cptr = cb + ((long long)xorg + (long long)xsign * (-SKEW * g + 1)) * DP;   // next pixel's C
+    const uint16_t* s1ptr = sb + ((long long)xorg + (long long)xsign * (-SKEW * g + 1)) * DP;  // next pixel's S1
+    uint16_t* optr = (FINAL ? a.S_out + rowoff : sb) + ((long long)xorg + (long long)xsign * (-SKEW * g)) * DP;
+    uint16_t* eptr = ebelow + (long long)(-SKEW * g) * 3 * DP + lane * 2 * R;
     // first operands
     {
         const int xs = -SKEW * g;
@@ -334,39 +410,37 @@ k_wave(SgbmEff e, WaveArgs a)
             if (FINAL) ldg_regs_stream<R>(sb + off, S1);
         }
     }
-    int pend = 0;
     unsigned phase = 0;
-    const unsigned bar_addr = (unsigned)__cvta_generic_to_shared(s_bar);
+    const unsigned bar_addr = sm0 + P::bar;
 
     // One wavefront step.  Cc/S1c: operands of this step, Cx/S1x: prefetch targets for the next one
     // (the caller alternates the two register sets, so nothing is copied).
     auto body = [&](const int t, uint32_t (&Cc)[R], uint32_t (&Cx)[R], uint32_t (&S1c)[R], uint32_t (&S1x)[R]) {
         if (VERT && t > 0) { mbar_wait(bar_addr, phase); phase ^= 1u; }   // every warp finished step t-1's ring stores
-        if (has_below) {                       // uniform: last row finished pixel t-1-SKEW*gl in the previous step
+        if (has_below) {
+            // uniform: the band's last row finished `xdone` pixels in the steps before this one.  The release
+            // store of one thread is cumulative over the edge stores the other lanes made before they arrived.
             const int xdone = t - SKEW * gl;
-            if ((xdone % CH) == 0 || xdone == w1) {
-                if (pend) { st_release(a.progress + eitem, pend); pend = 0; }
-            }
+            if (xdone > 0 && ((xdone % CH) == 0 || xdone == w1) && threadIdx.x == pubthread)
+                publish_progress(a.progress + eitem, xdone);
         }
         const int xs = t - SKEW * g;
-        const bool act = rowact && xs >= 0 && xs < w1;
-        const int xreal = xorg + xsign * xs;
-        const size_t off = (size_t)xreal * DP;
+        const bool act = rowact && (unsigned)xs < (unsigned)w1;
         if (has_above && (t % CH) == 2 && t >= 2) {              // chunk staging (polled during step t-1)
             const int c = (t - 2) / CH + 1;
             if (c * CH < w1) stage_chunk(c);
         }
         // prefetch the next pixel's operands
         {
-            const int xn = xs + 1;
-            const bool actn = rowact && xn >= 0 && xn < w1;
+            const bool actn = rowact && (unsigned)(xs + 1) < (unsigned)w1;
 #pragma unroll
             for (int i = 0; i < R; i++) { Cx[i] = 0; }
             if (actn) {
-                const size_t offn = (size_t)(xorg + xsign * xn) * DP;
-                ldg_regs_stream<R>(cb + offn, Cx);
-                if (FINAL) ldg_regs_stream<R>(sb + offn, S1x);
+                ldg_regs_stream<R>(cptr, Cx);
+                if (FINAL) ldg_regs_stream<R>(s1ptr, S1x);
             }
+            cptr += xstep;
+            if (FINAL) s1ptr += xstep;
         }
 
         uint32_t Sv[R];
@@ -374,46 +448,34 @@ k_wave(SgbmEff e, WaveArgs a)
             // ---- the three directions that come from the row above: ring -> registers -> ring -----
             uint32_t Lv[3][R], minv[3], mnv[3];
 #pragma unroll
-            for (int k = 1; k <= 3; k++) {
-                const int xp = xs + (k == 1 ? -1 : (k == 3 ? 1 : 0));
-                const bool has_pred = xp >= 0 && xp < w1 && (g > 0 || has_above);
-                const uint16_t* src = zero;
-                const uint32_t* msrc = zeromin;
-                if (has_pred) {
-                    if (g > 0) {
-                        if (k == 1) src = ring1 + ((g - 1) * 4 + (xp & 3)) * DP;
-                        else if (k == 2) src = ring2 + ((g - 1) * 4 + (xp & 3)) * DP;
-                        else src = ring3 + ((g - 1) * 2 + (xp & 1)) * DP;
-                        msrc = ringmin + ((g - 1) * 4 + (xp & 3)) * 4 + k;
-                    } else {
-                        const int slot = xp & (2 * CH - 1);
-                        src = stage + (slot * 3 + (k - 1)) * DP;
-                        msrc = stagemin + slot * 4 + (k - 1);
-                    }
-                }
-                ld_regs<R>(src + lane * 2 * R, Lv[k - 1]);
-                minv[k - 1] = *msrc;
+            for (int k = 0; k < 3; k++) {
+                const int xp = xs + k - 1;                       // (x-1, x, x+1) of the row above
+                const bool has_pred = rowok && (unsigned)xp < (unsigned)w1;
+                const unsigned src = has_pred ? rsrc[k] + ((unsigned)xp & rmask[k]) * rstr : zsrc;
+                const unsigned ms = has_pred ? msrc[k] + ((unsigned)xp & mmask) * 16 : zmin;
+                lds_regs<R>(src, Lv[k]);
+                minv[k] = lds_u32(ms);
             }
 #pragma unroll
             for (int k = 0; k < 3; k++) mnv[k] = step<R, G, PAD>(Lv[k], Cc, lane, p1x2, p2m1x2, minv[k], padm);
             if (act) {
-                st_regs<R>(ring1 + (g * 4 + (xs & 3)) * DP + lane * 2 * R, Lv[0]);
-                st_regs<R>(ring2 + (g * 4 + (xs & 3)) * DP + lane * 2 * R, Lv[1]);
-                st_regs<R>(ring3 + (g * 2 + (xs & 1)) * DP + lane * 2 * R, Lv[2]);
-                if (has_below && g == gl) {
-                    uint16_t* ge = ebelow + (size_t)xs * 3 * DP + lane * 2 * R;
-                    st_regs<R>(ge, Lv[0]);
-                    st_regs<R>(ge + DP, Lv[1]);
-                    st_regs<R>(ge + 2 * DP, Lv[2]);
+                sts_regs<R>(wdst1 + (xs & 3) * (DP * 2), Lv[0]);
+                sts_regs<R>(wdst2 + (xs & 3) * (DP * 2), Lv[1]);
+                sts_regs<R>(wdst3 + (xs & 1) * (DP * 2), Lv[2]);
+                if (edgerow) {
+                    st_regs<R>(eptr, Lv[0]);
+                    st_regs<R>(eptr + DP, Lv[1]);
+                    st_regs<R>(eptr + 2 * DP, Lv[2]);
                 }
             }
+            eptr += 3 * DP;
             const uint32_t r12 = group_min_x2<G>(half_min(mnv[0]) | (half_min(mnv[1]) << 16));
             const uint32_t r3 = group_min_x2<G>(half_min(mnv[2]));
             if (act && lane == 0) {
-                uint32_t* md = ringmin + (g * 4 + (xs & 3)) * 4;
                 const uint32_t m1 = (r12 & 0xffffu) * 0x10001u, m2 = (r12 >> 16) * 0x10001u, m3 = (r3 & 0xffffu) * 0x10001u;
-                md[1] = m1; md[2] = m2; md[3] = m3;
-                if (has_below && g == gl) {
+                const unsigned md = wmin + (xs & 3) * 16;
+                sts_u32(md + 4, m1); sts_u32(md + 8, m2); sts_u32(md + 12, m3);
+                if (edgerow) {
                     uint32_t* ge = ebelow_min + (size_t)xs * 4;
                     ge[0] = m1; ge[1] = m2; ge[2] = m3;
                 }
@@ -446,28 +508,26 @@ k_wave(SgbmEff e, WaveArgs a)
 
         // ---- S ----------------------------------------------------------------------------------
         if (FINAL) {
-            wta<R, G, PAD>(Sv, lane, e, a.magic, scratch + g * DP, act, rowpix, xreal, a.rec, a.disp2key);
-            if (a.S_out != nullptr && act) st_regs<R>(a.S_out + rowoff + off, Sv);
+            wta<R, G, PAD>(Sv, lane, e, a.magic, scratch + g * DP, act, rowpix, xorg + xsign * xs, a.rec, a.disp2key);
+            if (a.S_out != nullptr && act) st_regs<R>(optr, Sv);
         } else {
-            if (act) st_regs<R>(sb + off, Sv);
+            if (act) st_regs<R>(optr, Sv);
         }
-        // publish after the next barrier: the release store of one thread is cumulative over the edge
-        // stores the other lanes made before they arrived
-        if (has_below && g == gl && act && lane == 0 && (((xs + 1) % CH) == 0 || xs == w1 - 1)) pend = xs + 1;
+        optr += xstep;
     };
 
     uint32_t C2[R], S2[R];
 #pragma unroll
     for (int i = 0; i < R; i++) { C2[i] = 0; S2[i] = 0; }
-    (void)Cn; (void)S1n;
+    (void)Cn; (void)S1n; (void)ring1; (void)ring2; (void)ring3; (void)ringmin; (void)zero; (void)zeromin;
 #pragma unroll 1
     for (int t = 0; t < T; t += 2) {
         body(t, C, C2, S1, S2);
         if (t + 1 < T) body(t + 1, C2, C, S2, S1);
     }
-    if (VERT && pend) {
+    if (has_below) {                       // the last chunk(s) of the edge stream
         mbar_wait(bar_addr, phase);
-        st_release(a.progress + eitem, pend);
+        if (threadIdx.x == pubthread) publish_progress(a.progress + eitem, w1);
     }
 }
 
