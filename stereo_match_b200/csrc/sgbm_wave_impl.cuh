@@ -170,6 +170,7 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity)
         "bra WAIT_%=;\n\t"
         "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
 }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // shared-memory plan (bytes), shared by host and device
@@ -412,6 +413,7 @@ k_wave(SgbmEff e, WaveArgs a)
     }
     unsigned phase = 0;
     const unsigned bar_addr = sm0 + P::bar;
+    constexpr int PFD = 6;                                              // L2 prefetch distance in steps
 
     // One wavefront step.  Cc/S1c: operands of this step, Cx/S1x: prefetch targets for the next one
     // (the caller alternates the two register sets, so nothing is copied).
@@ -438,6 +440,12 @@ k_wave(SgbmEff e, WaveArgs a)
             if (actn) {
                 ldg_regs_stream<R>(cptr, Cx);
                 if (FINAL) ldg_regs_stream<R>(s1ptr, S1x);
+            }
+            // pull the lines of a few steps ahead into L2: the register prefetch above then waits for an
+            // L2 hit instead of a DRAM round trip (one step is about as long as the loaded DRAM latency)
+            if (rowact && (unsigned)(xs + 1 + PFD) < (unsigned)w1) {
+                prefetch_l2(cptr + PFD * xstep);
+                if (FINAL) prefetch_l2(s1ptr + PFD * xstep);
             }
             cptr += xstep;
             if (FINAL) s1ptr += xstep;
