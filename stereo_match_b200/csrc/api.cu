@@ -4,6 +4,7 @@
 #include "sgbm_wave.cuh"
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -89,6 +90,7 @@ static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, Sgb
         for (int r : RS) if (2 * r * g >= e.D) { e.G = g; e.R = r; break; }
     if (!e.G) for (int r : { 12, 16 }) if (64 * r >= e.D) { e.G = 32; e.R = r; break; }
     if (!e.G) { b2s_set_error("StereoSGBM: numDisparities > 1024 is not supported"); return B2S_E_UNSUPPORTED; }
+    // (measured on B200 at D = 128: G=8/R=8 195 us per pair; G=4/R=16 287 us; G=16/R=4 237 us)
     e.Dp = 2 * e.R * e.G;
     return B2S_OK;
 }
