@@ -192,6 +192,24 @@ __device__ __forceinline__ uint32_t bt2(uint32_t u, uint32_t lo1, uint32_t hi1, 
     return __vminu2(__vimax3_u16x2(A, Bv, B2S_BIAS), __vimax3_u16x2(Cv, Dv, B2S_BIAS));   // biased by 0x0100
 }
 
+// sum of v over lanes [l, l + BS) (packed u16x2, no overflow: BS * 317 < 65536); lanes whose window
+// leaves the warp return garbage (they are the halo columns and never store)
+template <int BS>
+__device__ __forceinline__ uint32_t window_sum(uint32_t v)
+{
+    uint32_t sum = 0, p = v;              // p = sum over a window of `len` lanes starting at this lane
+    int off = 0;
+#pragma unroll
+    for (int len = 1; len <= BS; len <<= 1) {
+        if (BS & len) {                   // take this power-of-two block at lane offset `off`
+            sum += off ? __shfl_down_sync(0xffffffffu, p, off) : p;
+            off += len;
+        }
+        if (2 * len <= BS) p += __shfl_down_sync(0xffffffffu, p, len);
+    }
+    return sum;
+}
+
 template <int BS, int MAXW, bool PAD>
 __global__ void __launch_bounds__(32 * MAXW, (MAXW == 16 && BS <= 7) ? 2 : 1)
 k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, SgbmEff e, int TR, int NELP,
@@ -201,9 +219,8 @@ k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, Sg
     extern __shared__ __align__(16) unsigned char smem_c[];
     const int Dp = e.Dp;
     const int lane = threadIdx.x & 31, oct = threadIdx.x >> 5, nthreads = blockDim.x;
-    // smem: [2] x { LW[32] uint2 , planes[6][2][NELP] u16 }  then per-warp pix exchange [32 lanes][8] u16
+    // smem: [2] x { LW[32] uint2 , planes[6][2][NELP] u16 }
     const int stage_bytes = 256 + 12 * NELP * 2;
-    uint16_t* const pixw = reinterpret_cast<uint16_t*>(smem_c + 2 * stage_bytes) + (size_t)oct * 32 * 8;
     const int x0 = blockIdx.x * TW, yb = blockIdx.y * TR;
     const size_t b = blockIdx.z;
     const int yend = min(yb + TR, e.H);
@@ -282,6 +299,7 @@ k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, Sg
             if (more) stage_load(yv + 1, nw1, nw2, nwl);
             const unsigned char* const buf = smem_c + cur * stage_bytes;
             // ---- phase A: pixel costs of (column, 8 disparities) --------------------------------
+            uint32_t hs[4];
             {
                 const uint2 wl = reinterpret_cast<const uint2*>(buf)[lane];
                 const uint32_t* const rbase = reinterpret_cast<const uint32_t*>(buf + roff);
@@ -295,17 +313,12 @@ k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, Sg
                     // (cr - bias) >> 2 == ((cr >> 2) & 0x7f) - 0x40 per half
                     pc[w] = cg + ((cr >> 2) & 0x007f007fu) - (B2S_BIAS + 0x00400040u);
                 }
-                *reinterpret_cast<uint4*>(pixw + lane * 8) = make_uint4(pc[0], pc[1], pc[2], pc[3]);
-            }
-            __syncwarp();
-            // ---- phase B: box sums (the BS columns are neighbouring lanes of this warp) -----------
-            {
-                uint32_t hs[4] = { 0, 0, 0, 0 };
+                // ---- phase B: box sums.  The BS columns are the next BS-1 lanes of this warp: window sum
+                // by doubling (p2 = x + x+1, p4 = p2 + p2(x+2), ...) through shuffles, no shared memory.
 #pragma unroll
-                for (int k = 0; k < BS; k++) {
-                    const uint4 v = *reinterpret_cast<const uint4*>(pixw + (lane < TW ? lane + k : lane) * 8);
-                    hs[0] += v.x; hs[1] += v.y; hs[2] += v.z; hs[3] += v.w;
-                }
+                for (int w = 0; w < 4; w++) hs[w] = window_sum<BS>(pc[w]);
+            }
+            {
 #pragma unroll
                 for (int w = 0; w < 4; w++) {
                     acc[w] += hs[w] - ring[s][w];          // halves never borrow: acc >= old contribution
@@ -337,7 +350,7 @@ static int launch_cost_fast(const uint2* descL, const uint2* descR, const SgbmEf
     constexpr int TW = 32 - (BS - 1);
     const int nel = 32 + e.Dp;
     const int NELP = (nel + 63) / 64 * 64 + 32;            // copies land 64 bytes apart modulo 128: disjoint banks
-    const size_t smem = 2 * (256 + (size_t)12 * NELP * 2) + (size_t)(e.Dp / 8) * 512;
+    const size_t smem = 2 * (256 + (size_t)12 * NELP * 2);
     const int TR = 75;
     dim3 grid(b2s_cdiv(e.width1, TW), b2s_cdiv(e.H, TR), e.batch);
     const int nthreads = 32 * (e.Dp / 8);
