@@ -344,7 +344,7 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=64, help="pairs per step per GPU")
+    ap.add_argument("--batch", type=int, default=128, help="pairs per step per GPU")
     ap.add_argument("--cpu-pairs", type=int, default=40, help="cpu_baseline: pairs per worker process")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true")

@@ -95,6 +95,8 @@ typedef struct b2s_sgbm_geometry {
     int32_t invalid;              /* (minDisparity-1)*16 */
     int32_t P1, P2, ftzero, uniquenessRatio, disp12MaxDiff; /* effective values */
     int32_t ndirs;                /* 5 (MODE_SGBM) or 8 (MODE_HH) */
+    int32_t R, G;                 /* Dp = 2*R*G: G lanes per pixel, R packed registers per lane */
+    int32_t swizzled;             /* 1: cell d of a [Dp] record sits at ((o % (R/4))*G + o/(R/4))*8 + d%8, o = d/8 */
 } b2s_sgbm_geometry;
 
 B2S_API const char* b2s_last_error(void);
@@ -113,7 +115,7 @@ B2S_API int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t* r
                      int H, int W, int batch, int16_t* disp, void* stream);
 /* stage taps for parity tests: copies the last compute's volumes (device to device, on
    `stream`) into caller buffers of `elems` uint16 each (either may be NULL); layout
-   [batch][H][width1][Dp].  cost = raw block cost (cv2's C minus P2, padded cells 0);
+   [batch][H][width1][Dp] (cell order inside a record: see b2s_sgbm_geometry.swizzled).  cost = raw block cost (cv2's C minus P2, padded cells 0);
    S = min(32767, sum of path costs) (padded cells 32767).  The production pipeline never
    materialises the full S (the last sweep feeds the winner-take-all from registers); call
    b2s_sgbm_keep_volumes(h, 1) before compute to have it written as well. */

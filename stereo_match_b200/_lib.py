@@ -33,7 +33,7 @@ class BmParams(C.Structure):
 class SgbmGeometry(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "minX1", "maxX1", "width1", "Dp", "invalid", "P1", "P2", "ftzero",
-        "uniquenessRatio", "disp12MaxDiff", "ndirs")]
+        "uniquenessRatio", "disp12MaxDiff", "ndirs", "R", "G", "swizzled")]
 
 
 # every symbol include/b2stereo.h declares: (restype, argtypes)

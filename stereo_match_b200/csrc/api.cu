@@ -92,6 +92,7 @@ static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, Sgb
     if (!e.G) { b2s_set_error("StereoSGBM: numDisparities > 1024 is not supported"); return B2S_E_UNSUPPORTED; }
     // (measured on B200 at D = 128: G=8/R=8 195 us per pair; G=4/R=16 287 us; G=16/R=4 237 us)
     e.Dp = 2 * e.R * e.G;
+    e.swz = (e.R == 8) ? 1 : 0;          // wavefront path with two 16-byte chunks per lane: permuted records
     return B2S_OK;
 }
 
@@ -174,6 +175,7 @@ extern "C" int b2s_sgbm_get_geometry(b2s_handle h, int W, b2s_sgbm_geometry* out
     out->minX1 = e.minX1; out->maxX1 = e.maxX1; out->width1 = e.width1; out->Dp = e.Dp;
     out->invalid = e.invalid; out->P1 = e.P1; out->P2 = e.P2; out->ftzero = e.ftzero;
     out->uniquenessRatio = e.uniq; out->disp12MaxDiff = e.lrmax; out->ndirs = e.ndirs;
+    out->R = e.R; out->G = e.G; out->swizzled = e.swz;
     return B2S_OK;
 }
 

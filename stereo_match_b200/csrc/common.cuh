@@ -17,6 +17,7 @@ struct SgbmEff {
     int ndirs;                // 5 or 8
     int G;                    // lanes per pixel in the aggregation/WTA kernels (8, 16 or 32)
     int R;                    // packed u16x2 registers per lane: Dp = 2*R*G
+    int swz;                  // 1: [Dp] records of the cost/S volumes use the permuted cell order of b2s_cell_pos
 };
 
 // aggregation direction table (step from predecessor to pixel), same order as the
@@ -26,6 +27,16 @@ __host__ __device__ inline void b2s_dir(int k, int& dx, int& dy)
     const int DX[8] = { 1, 1, 0, -1, -1, 1, 0, -1 };
     const int DY[8] = { 0, 1, 1, 1, 0, -1, -1, -1 };
     dx = DX[k]; dy = DY[k];
+}
+
+// Position of disparity cell d inside a [Dp] record.  Natural order unless `swz`: then the 16-byte chunk c of
+// lane j (cells 16j + 8c ... for R = 8) is stored at chunk slot c*G + j, which makes the group-wide vector
+// accesses of the wavefront kernel contiguous (sgbm_wave_impl.cuh).  Whole octets move, pairs stay adjacent.
+__host__ __device__ inline int b2s_cell_pos(int d, int R, int G, int swz)
+{
+    if (!swz) return d;
+    const int nch = R / 4, o = d >> 3;
+    return (((o % nch) * G + o / nch) << 3) | (d & 7);
 }
 
 void b2s_set_error(const char* fmt, ...);

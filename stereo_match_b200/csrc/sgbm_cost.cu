@@ -158,7 +158,7 @@ k_cost(const uint2* __restrict__ descL, const uint2* __restrict__ descR, SgbmEff
                     int d0 = 2 * dp;
                     if (d0 >= e.D) v = 0u;
                     else if (d0 + 1 >= e.D) v = v & 0xffffu;
-                    *reinterpret_cast<uint32_t*>(out + ((size_t)yo * e.width1 + x) * e.Dp + d0) = v;
+                    *reinterpret_cast<uint32_t*>(out + ((size_t)yo * e.width1 + x) * e.Dp + b2s_cell_pos(d0, e.R, e.G, e.swz)) = v;
                 }
             }
         }
@@ -236,6 +236,7 @@ k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, Sg
     const int roff = 256 + (par * NELP) * 2 + ((e0 - par) >> 1) * 4;          // byte offset inside a stage buffer
     const int pstride = NELP;                                                 // u32 words between planes (2 copies each)
     // phase B geometry
+    const int opos = b2s_cell_pos(8 * oct, e.R, e.G, e.swz);                  // where this octet lives in the record
     const int xB = x0 + lane;
     const bool outB = lane < TW && xB < e.width1;
     uint32_t pmask[4];
@@ -330,7 +331,7 @@ k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, Sg
                 if (outB && yo >= yb) {
                     uint4 o = make_uint4(acc[0], acc[1], acc[2], acc[3]);
                     if (PAD) { o.x &= pmask[0]; o.y &= pmask[1]; o.z &= pmask[2]; o.w &= pmask[3]; }
-                    *reinterpret_cast<uint4*>(out + ((size_t)yo * e.width1 + xB) * Dp + 8 * oct) = o;
+                    *reinterpret_cast<uint4*>(out + ((size_t)yo * e.width1 + xB) * Dp + opos) = o;
                 }
             }
             if (more) stage_store(cur ^ 1, nw1, nw2, nwl);

@@ -6,13 +6,13 @@ namespace wave {
 
 
 // ---- R packed registers <-> memory (generic address space; 16/8/4-byte vectors) ---------------
-template <int R>
+template <int R, int CSB = 16>
 __device__ __forceinline__ void ld_regs(const uint16_t* p, uint32_t (&r)[R])
 {
     if constexpr (R % 4 == 0) {
 #pragma unroll
         for (int i = 0; i < R / 4; i++) {
-            uint4 v = reinterpret_cast<const uint4*>(p)[i];
+            uint4 v = *reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(p) + i * CSB);
             r[4 * i] = v.x; r[4 * i + 1] = v.y; r[4 * i + 2] = v.z; r[4 * i + 3] = v.w;
         }
     } else {
@@ -24,13 +24,13 @@ __device__ __forceinline__ void ld_regs(const uint16_t* p, uint32_t (&r)[R])
     }
 }
 
-template <int R>
+template <int R, int CSB = 16>
 __device__ __forceinline__ void ldg_regs_stream(const uint16_t* p, uint32_t (&r)[R])
 {
     if constexpr (R % 4 == 0) {
 #pragma unroll
         for (int i = 0; i < R / 4; i++) {
-            uint4 v = __ldcs(reinterpret_cast<const uint4*>(p) + i);
+            uint4 v = __ldcs(reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(p) + i * CSB));
             r[4 * i] = v.x; r[4 * i + 1] = v.y; r[4 * i + 2] = v.z; r[4 * i + 3] = v.w;
         }
     } else {
@@ -42,13 +42,13 @@ __device__ __forceinline__ void ldg_regs_stream(const uint16_t* p, uint32_t (&r)
     }
 }
 
-template <int R>
+template <int R, int CSB = 16>
 __device__ __forceinline__ void st_regs(uint16_t* p, const uint32_t (&r)[R])
 {
     if constexpr (R % 4 == 0) {
 #pragma unroll
         for (int i = 0; i < R / 4; i++)
-            reinterpret_cast<uint4*>(p)[i] = make_uint4(r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]);
+            *reinterpret_cast<uint4*>(reinterpret_cast<char*>(p) + i * CSB) = make_uint4(r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]);
     } else {
 #pragma unroll
         for (int i = 0; i < R / 2; i++) reinterpret_cast<uint2*>(p)[i] = make_uint2(r[2 * i], r[2 * i + 1]);
@@ -56,28 +56,28 @@ __device__ __forceinline__ void st_regs(uint16_t* p, const uint32_t (&r)[R])
 }
 
 // same, through a 32-bit shared-window address (no generic-pointer arithmetic in the hot loop)
-template <int R>
+template <int R, int CSB = 16>
 __device__ __forceinline__ void lds_regs(unsigned addr, uint32_t (&r)[R])
 {
     if constexpr (R % 4 == 0) {
 #pragma unroll
         for (int i = 0; i < R / 4; i++)
             asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                         : "=r"(r[4 * i]), "=r"(r[4 * i + 1]), "=r"(r[4 * i + 2]), "=r"(r[4 * i + 3]) : "r"(addr + 16 * i));
+                         : "=r"(r[4 * i]), "=r"(r[4 * i + 1]), "=r"(r[4 * i + 2]), "=r"(r[4 * i + 3]) : "r"(addr + CSB * i));
     } else {
 #pragma unroll
         for (int i = 0; i < R / 2; i++)
             asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(r[2 * i]), "=r"(r[2 * i + 1]) : "r"(addr + 8 * i));
     }
 }
-template <int R>
+template <int R, int CSB = 16>
 __device__ __forceinline__ void sts_regs(unsigned addr, const uint32_t (&r)[R])
 {
     if constexpr (R % 4 == 0) {
 #pragma unroll
         for (int i = 0; i < R / 4; i++)
             asm volatile("st.shared.v4.u32 [%4], {%0, %1, %2, %3};"
-                         ::"r"(r[4 * i]), "r"(r[4 * i + 1]), "r"(r[4 * i + 2]), "r"(r[4 * i + 3]), "r"(addr + 16 * i) : "memory");
+                         ::"r"(r[4 * i]), "r"(r[4 * i + 1]), "r"(r[4 * i + 2]), "r"(r[4 * i + 3]), "r"(addr + CSB * i) : "memory");
     } else {
 #pragma unroll
         for (int i = 0; i < R / 2; i++)
@@ -194,7 +194,7 @@ struct Plan {
 };
 
 // ---- fused winner-take-all on the registers of one group (first loop) --------
-template <int R, int G, bool PAD>
+template <int R, int G, bool PAD, int CSB>
 __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const SgbmEff& e, unsigned long long magic,
                                     uint16_t* scr, bool act, size_t rowpix, int xreal, uint2* rec,
                                     uint32_t* disp2key)
@@ -261,11 +261,11 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
     const bool bad = (__ballot_sync(0xffffffffu, bad_lane) & gmask) != 0;
 
     // neighbours of the winner through the group's scratch row
-    st_regs<R>(scr + dbase, Sv);
+    st_regs<R, CSB>(scr + (CSB == 16 ? dbase : lane * 8), Sv);
     __syncwarp();
     if (lane == 0 && act) {
-        const uint32_t sm1 = best > 0 ? scr[best - 1] : 0u;
-        const uint32_t sp1 = best < e.D - 1 ? scr[best + 1] : 0u;
+        const uint32_t sm1 = best > 0 ? scr[b2s_cell_pos(best - 1, R, G, CSB != 16)] : 0u;
+        const uint32_t sp1 = best < e.D - 1 ? scr[b2s_cell_pos(best + 1, R, G, CSB != 16)] : 0u;
         const int xi = xreal + e.minX1;
         rec[rowpix + xi] = make_uint2((uint32_t)minS | (bad ? 0xffff0000u : (uint32_t)best << 16), sm1 | (sp1 << 16));
         if (!bad) {
@@ -282,6 +282,11 @@ k_wave(SgbmEff e, WaveArgs a)
 {
     using P = Plan<R, G, NT, VERT, FINAL>;
     constexpr int RB = P::RB, DP = P::DP, CH = P::CH;
+    // Layout of one [Dp] record (cost, S, rings, edge stream): with R == 8 a lane's two 16-byte chunks sit
+    // G*16 bytes apart (chunk c of lane j at (c*G + j)*16, see b2s_cell_pos), so that every vector access of
+    // a group covers 128 contiguous bytes: conflict-free in shared memory, whole sectors in global memory.
+    constexpr bool SWZ = (R == 8);
+    constexpr int CSB = SWZ ? G * 16 : 16;
     extern __shared__ __align__(16) unsigned char smem[];
     uint16_t* const ring1 = reinterpret_cast<uint16_t*>(smem + P::ring1);
     uint16_t* const ring2 = reinterpret_cast<uint16_t*>(smem + P::ring2);
@@ -323,7 +328,8 @@ k_wave(SgbmEff e, WaveArgs a)
     const int yreal = a.flip ? e.H - 1 - min(ys, e.H - 1) : min(ys, e.H - 1);
     const int xsign = a.flip ? -1 : 1, xorg = a.flip ? w1 - 1 : 0;      // xreal = xorg + xsign * xs
 
-    const size_t rowoff = ((size_t)b * e.H + yreal) * w1 * DP + (size_t)lane * 2 * R;
+    const int lcell = SWZ ? lane * 8 : lane * 2 * R;                   // first cell slot of this lane in a record
+    const size_t rowoff = ((size_t)b * e.H + yreal) * w1 * DP + (size_t)lcell;
     const uint16_t* const cb = a.cost + rowoff;
     uint16_t* const sb = a.S + rowoff;
     const size_t rowpix = ((size_t)b * e.H + yreal) * e.W;
@@ -370,7 +376,7 @@ k_wave(SgbmEff e, WaveArgs a)
 
     // ---- loop-invariant addressing (32-bit shared-window addresses, running global pointers) -------
     const unsigned sm0 = (unsigned)__cvta_generic_to_shared(smem);
-    const unsigned laneb = (unsigned)lane * 2 * R * 2;                 // byte offset of this lane's cells
+    const unsigned laneb = (unsigned)lcell * 2;                        // byte offset of this lane's cells
     // predecessor sources of the three vertical directions: the row above in the rings, or, for the
     // band's first row, the staged edge stream; `rowok` false (very first row of the sweep): zeros
     const bool rowok = g > 0 || has_above;
@@ -401,14 +407,14 @@ k_wave(SgbmEff e, WaveArgs a)
     const uint16_t* cptr = cb + ((long long)xorg + (long long)xsign * (-SKEW * g + 1)) * DP;   // next pixel's C
     const uint16_t* s1ptr = sb + ((long long)xorg + (long long)xsign * (-SKEW * g + 1)) * DP;  // next pixel's S1
     uint16_t* optr = (FINAL ? a.S_out + rowoff : sb) + ((long long)xorg + (long long)xsign * (-SKEW * g)) * DP;
-    uint16_t* eptr = ebelow + (long long)(-SKEW * g) * 3 * DP + lane * 2 * R;
+    uint16_t* eptr = ebelow + (long long)(-SKEW * g) * 3 * DP + lcell;
     // first operands
     {
         const int xs = -SKEW * g;
         if (rowact && xs >= 0 && xs < w1) {
             const size_t off = (size_t)(xorg + xsign * xs) * DP;
-            ldg_regs_stream<R>(cb + off, C);
-            if (FINAL) ldg_regs_stream<R>(sb + off, S1);
+            ldg_regs_stream<R, CSB>(cb + off, C);
+            if (FINAL) ldg_regs_stream<R, CSB>(sb + off, S1);
         }
     }
     unsigned phase = 0;
@@ -438,8 +444,8 @@ k_wave(SgbmEff e, WaveArgs a)
 #pragma unroll
             for (int i = 0; i < R; i++) { Cx[i] = 0; }
             if (actn) {
-                ldg_regs_stream<R>(cptr, Cx);
-                if (FINAL) ldg_regs_stream<R>(s1ptr, S1x);
+                ldg_regs_stream<R, CSB>(cptr, Cx);
+                if (FINAL) ldg_regs_stream<R, CSB>(s1ptr, S1x);
             }
             // pull the lines of a few steps ahead into L2: the register prefetch above then waits for an
             // L2 hit instead of a DRAM round trip (one step is about as long as the loaded DRAM latency)
@@ -461,19 +467,19 @@ k_wave(SgbmEff e, WaveArgs a)
                 const bool has_pred = rowok && (unsigned)xp < (unsigned)w1;
                 const unsigned src = has_pred ? rsrc[k] + ((unsigned)xp & rmask[k]) * rstr : zsrc;
                 const unsigned ms = has_pred ? msrc[k] + ((unsigned)xp & mmask) * 16 : zmin;
-                lds_regs<R>(src, Lv[k]);
+                lds_regs<R, CSB>(src, Lv[k]);
                 minv[k] = lds_u32(ms);
             }
 #pragma unroll
             for (int k = 0; k < 3; k++) mnv[k] = step<R, G, PAD>(Lv[k], Cc, lane, p1x2, p2m1x2, minv[k], padm);
             if (act) {
-                sts_regs<R>(wdst1 + (xs & 3) * (DP * 2), Lv[0]);
-                sts_regs<R>(wdst2 + (xs & 3) * (DP * 2), Lv[1]);
-                sts_regs<R>(wdst3 + (xs & 1) * (DP * 2), Lv[2]);
+                sts_regs<R, CSB>(wdst1 + (xs & 3) * (DP * 2), Lv[0]);
+                sts_regs<R, CSB>(wdst2 + (xs & 3) * (DP * 2), Lv[1]);
+                sts_regs<R, CSB>(wdst3 + (xs & 1) * (DP * 2), Lv[2]);
                 if (edgerow) {
-                    st_regs<R>(eptr, Lv[0]);
-                    st_regs<R>(eptr + DP, Lv[1]);
-                    st_regs<R>(eptr + 2 * DP, Lv[2]);
+                    st_regs<R, CSB>(eptr, Lv[0]);
+                    st_regs<R, CSB>(eptr + DP, Lv[1]);
+                    st_regs<R, CSB>(eptr + 2 * DP, Lv[2]);
                 }
             }
             eptr += 3 * DP;
@@ -516,10 +522,10 @@ k_wave(SgbmEff e, WaveArgs a)
 
         // ---- S ----------------------------------------------------------------------------------
         if (FINAL) {
-            wta<R, G, PAD>(Sv, lane, e, a.magic, scratch + g * DP, act, rowpix, xorg + xsign * xs, a.rec, a.disp2key);
-            if (a.S_out != nullptr && act) st_regs<R>(optr, Sv);
+            wta<R, G, PAD, CSB>(Sv, lane, e, a.magic, scratch + g * DP, act, rowpix, xorg + xsign * xs, a.rec, a.disp2key);
+            if (a.S_out != nullptr && act) st_regs<R, CSB>(optr, Sv);
         } else {
-            if (act) st_regs<R>(optr, Sv);
+            if (act) st_regs<R, CSB>(optr, Sv);
         }
         optr += xstep;
     };

@@ -164,7 +164,13 @@ class StereoSGBM(_Matcher):
         S = torch.empty(n, dtype=torch.int16, device="cuda")
         _lib.check(_lib.load().b2s_sgbm_debug_volumes(self._h, _ptr(cost), _ptr(S), n, _stream()))
         shape = (B, H, g["width1"], g["Dp"])
-        return cost.view(shape), S.view(shape), g
+        cost, S = cost.view(shape), S.view(shape)
+        if g["swizzled"]:                 # records are stored in the wavefront kernel's lane order: undo it
+            d = torch.arange(g["Dp"], device="cuda")
+            o, nch = d // 8, g["R"] // 4
+            pos = ((o % nch) * g["G"] + o // nch) * 8 + d % 8
+            cost, S = cost[..., pos], S[..., pos]
+        return cost, S, g
 
 
 def _make_accessors(cls, fields):
