@@ -145,6 +145,7 @@ static int check_images(const char* who, const void* l, const void* r, const voi
 {
     if (!l || !r || !d) { b2s_set_error("%s: null image pointer", who); return B2S_E_INVALID; }
     if (H <= 0 || W <= 0 || batch <= 0) { b2s_set_error("%s: empty image (H=%d W=%d batch=%d)", who, H, W, batch); return B2S_E_INVALID; }
+    if ((long long)batch * H * W >= (1ll << 31)) { b2s_set_error("%s: batch*H*W must be < 2^31", who); return B2S_E_UNSUPPORTED; }
     if (W > 32768 || H > 65535 || batch > 65535) { b2s_set_error("%s: image or batch too large", who); return B2S_E_UNSUPPORTED; }
     return B2S_OK;
 }

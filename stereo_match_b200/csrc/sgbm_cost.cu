@@ -224,10 +224,6 @@ k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, Sg
     const int x0 = blockIdx.x * TW, yb = blockIdx.y * TR;
     const size_t b = blockIdx.z;
     const int yend = min(yb + TR, e.H);
-    const uint2* const dL = descL + b * (size_t)e.H * e.W;
-    const uint2* const dR = descR + b * (size_t)e.H * e.W;
-    uint16_t* const out = cost + b * (size_t)e.H * e.width1 * Dp;
-
     // phase A geometry of this thread (row independent)
     const int xiA = min(max(x0 - SW2 + lane, 0), e.width1 - 1) + e.minX1;     // clamp on the cropped axis
     const int XRM = min(max(x0 - SW2 + 31, 0), e.width1 - 1) + e.minX1 - e.minD;
@@ -239,6 +235,7 @@ k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, Sg
     const int opos = b2s_cell_pos(8 * oct, e.R, e.G, e.swz);                  // where this octet lives in the record
     const int xB = x0 + lane;
     const bool outB = lane < TW && xB < e.width1;
+    uint16_t* optr = cost + ((b * e.H + yb) * (size_t)e.width1 + min(xB, e.width1 - 1)) * Dp + opos;   // running store pointer
     uint32_t pmask[4];
 #pragma unroll
     for (int w = 0; w < 4; w++) {
@@ -253,13 +250,16 @@ k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, Sg
     const bool st1 = sel < nel && xr1 >= 0 && xr1 < e.W, st2 = sel + nthreads < nel && xr2 >= 0 && xr2 < e.W;
     const bool stL = oct == (nthreads >> 5) - 1;
 
+    // descriptor addresses as 32-bit pixel offsets from the kernel-argument pointers (batch*H*W < 2^31 is
+    // checked on the host): one IMAD.WIDE per load and nothing to keep live across the row loop
+    const unsigned bimg = (unsigned)b * (unsigned)(e.H * e.W);
     auto stage_load = [&](int yv, uint2& w1, uint2& w2, uint2& wl) {
         const int yr = min(max(yv, 0), e.H - 1);
-        const uint2* rowR = dR + (size_t)yr * e.W;
+        const unsigned rb = bimg + (unsigned)(yr * e.W);
         w1 = make_uint2(0u, 0u); w2 = make_uint2(0u, 0u); wl = make_uint2(0u, 0u);
-        if (st1) w1 = __ldg(rowR + xr1);
-        if (st2) w2 = __ldg(rowR + xr2);
-        if (stL) wl = __ldg(dL + (size_t)yr * e.W + xiA);
+        if (st1) w1 = __ldg(descR + (rb + (unsigned)xr1));
+        if (st2) w2 = __ldg(descR + (rb + (unsigned)xr2));
+        if (stL) wl = __ldg(descL + (rb + (unsigned)xiA));
     };
     auto stage_put = [&](unsigned char* buf, int el, const uint2& w) {
         uint16_t* planes = reinterpret_cast<uint16_t*>(buf + 256);
@@ -331,8 +331,9 @@ k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, Sg
                 if (outB && yo >= yb) {
                     uint4 o = make_uint4(acc[0], acc[1], acc[2], acc[3]);
                     if (PAD) { o.x &= pmask[0]; o.y &= pmask[1]; o.z &= pmask[2]; o.w &= pmask[3]; }
-                    *reinterpret_cast<uint4*>(out + ((size_t)yo * e.width1 + xB) * Dp + opos) = o;
+                    *reinterpret_cast<uint4*>(optr) = o;
                 }
+                if (yo >= yb) optr += (size_t)e.width1 * Dp;
             }
             if (more) stage_store(cur ^ 1, nw1, nw2, nwl);
             cur ^= 1;

@@ -178,7 +178,7 @@ template <int R, int G, int NT, bool VERT, bool FINAL>
 struct Plan {
     static constexpr int RB = NT / G;
     static constexpr int DP = 2 * R * G;
-    static constexpr int CH = (G == 8) ? 8 : 4;
+    static constexpr int CH = (G == 8 && NT >= 256) ? 8 : 4;
     static constexpr int ring1 = 0;                                        // [RB][4][DP] u16
     static constexpr int ring2 = ring1 + (VERT ? RB * 4 * DP * 2 : 0);     // [RB][4][DP]
     static constexpr int ring3 = ring2 + (VERT ? RB * 4 * DP * 2 : 0);     // [RB][2][DP]
@@ -277,7 +277,7 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
 }
 
 template <int R, int G, int NT, bool PAD, bool VERT, bool FINAL>
-__global__ void __launch_bounds__(NT, (G == 32 ? 1 : 512 / NT))
+__global__ void __launch_bounds__(NT, (G == 32 ? 1 : 576 / NT))
 k_wave(SgbmEff e, WaveArgs a)
 {
     using P = Plan<R, G, NT, VERT, FINAL>;
