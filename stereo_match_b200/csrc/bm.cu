@@ -130,6 +130,174 @@ k_bm(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, BmEff e, in
     }
 }
 
+// ---------------------------------------------------------------------------
+// Fast StereoBM kernel (blockSize <= 21, D <= 512).
+// CTA = 32 output columns (lane = column) x a band of rows; warp w owns disparities [16w, 16w+16).
+// Every thread keeps the 16 window SADs of its column in registers and marches down the band:
+//   v[d] += h(yin, d) - h(yin - BS, d),   h(y, d) = sum_{dx} |PL[y][x+dx] - PR[y][x+dx-d]|
+// h is evaluated with VABSDIFF4.ACC on 4 neighbouring pixels at a time; the unaligned 4-byte windows of the
+// right row come out of shared memory with funnel shifts whose amounts are compile-time constants relative
+// to the thread's own base word (only the base alignment is a run-time shift).  The row that leaves the
+// vertical window is re-evaluated instead of being kept (a ring of BS+2 staged rows in shared memory).
+// Winner-take-all: per-thread argmin over its 16 disparities -> per-warp candidates in shared memory ->
+// every thread derives the pixel's best and threshold, checks uniqueness on its own registers.
+// ---------------------------------------------------------------------------
+template <int BS>
+__global__ void __launch_bounds__(1024)
+k_bm_fast(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, BmEff e, int TR, int16_t* __restrict__ disp)
+{
+    constexpr int r = BS / 2, NWD = (BS + 3) / 4, NS = BS + 2;      // window words, staged-row ring
+    constexpr uint32_t LASTMASK = (BS % 4) ? ((1u << (8 * (BS % 4))) - 1u) : 0xffffffffu;
+    extern __shared__ __align__(16) unsigned char smb[];
+    const int D = e.D, NW = D / 16;
+    const int LBYTES = ((32 + 2 * r + 8 + 15) / 16) * 16;           // left row segment (+8 for the last funnel)
+    const int RBYTES = ((D + 32 + 2 * r + 4 * NWD + 24 + 15) / 16) * 16;   // right row segment, 8 bytes of front padding
+    unsigned char* const Lrows = smb;                                // [NS][LBYTES]
+    unsigned char* const Rrows = Lrows + NS * LBYTES;                // [NS][RBYTES]
+    uint32_t* const sad = reinterpret_cast<uint32_t*>(Rrows + NS * RBYTES);   // [D][33]
+    uint32_t* const cand_s = sad + (size_t)D * 33;                   // [NW][32]
+    uint32_t* const cand_d = cand_s + NW * 32;                       // [NW][32]
+    uint32_t* const badf = cand_d + NW * 32;                         // [32]
+    int* const tsum_s = reinterpret_cast<int*>(badf + 32);           // [32]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nthreads = blockDim.x;
+    const int xs = D - 1 + r, xe = e.W - r;
+    const int x0 = xs + blockIdx.x * 32, x = x0 + lane;
+    const int y0 = r + blockIdx.y * TR, y1 = min(y0 + TR, e.H - r);
+    const size_t base = (size_t)blockIdx.z * e.H * e.W;
+    const int dlo = 16 * warp;
+    const int xL0 = x0 - r;                                          // image column of Lrows byte 0
+    const int xR0 = x0 - r - (D - 1) - 8;                            // image column of Rrows byte 0
+    // byte offset of the right window start for d = dlo (largest start of this thread's range)
+    const int smax = lane + (D - 1) - dlo + 8;
+    const int rw = smax >> 2, rsh = (smax & 3) * 8;
+    const int lw = lane >> 2, lsh = (lane & 3) * 8;
+
+    auto stage = [&](int y) {                                        // row y -> ring slot (y - (y0 - r)) % NS
+        const int slot = (y - (y0 - r)) % NS;
+        const uint8_t* rl = PL + base + (size_t)y * e.W;
+        const uint8_t* rr = PR + base + (size_t)y * e.W;
+        for (int i = threadIdx.x; i < LBYTES; i += nthreads) {
+            const int xx = xL0 + i;
+            Lrows[slot * LBYTES + i] = (xx >= 0 && xx < e.W) ? rl[xx] : 0;
+        }
+        for (int i = threadIdx.x; i < RBYTES; i += nthreads) {
+            const int xx = xR0 + i;
+            Rrows[slot * RBYTES + i] = (xx >= 0 && xx < e.W) ? rr[xx] : 0;
+        }
+    };
+    // window SADs of row-slot `slot` for this thread's 16 disparities: acc[j] (+)= h(d = dlo + j)
+    auto hrow = [&](int slot, uint32_t (&acc)[16], int& tex) {
+        const uint32_t* lwp = reinterpret_cast<const uint32_t*>(Lrows + slot * LBYTES) + lw;
+        const uint32_t* rwp = reinterpret_cast<const uint32_t*>(Rrows + slot * RBYTES) + rw;
+        uint32_t Lw[NWD], U[NWD + 4];
+        {
+            uint32_t a = lwp[0];
+#pragma unroll
+            for (int i = 0; i < NWD; i++) { uint32_t b = lwp[i + 1]; Lw[i] = __funnelshift_r(a, b, lsh); a = b; }
+            Lw[NWD - 1] &= LASTMASK;
+            a = rwp[-4];
+#pragma unroll
+            for (int q = -4; q < NWD; q++) { uint32_t b = rwp[q + 1]; U[q + 4] = __funnelshift_r(a, b, rsh); a = b; }
+        }
+        const uint32_t ft4 = (uint32_t)e.ftzero * 0x01010101u;
+#pragma unroll
+        for (int i = 0; i < NWD; i++) tex = __vsadu4(Lw[i], i == NWD - 1 ? (ft4 & LASTMASK) : ft4) + tex;
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+            const int g = j >> 2, jj = j & 3;
+            uint32_t a = acc[j];
+#pragma unroll
+            for (int i = 0; i < NWD; i++) {
+                const int q = i - g;                                 // window word = bytes at smax + 4q - jj
+                uint32_t w = jj ? __funnelshift_l(U[q - 1 + 4], U[q + 4], 8 * jj) : U[q + 4];
+                if (i == NWD - 1) w &= LASTMASK;
+                a = __vsadu4(Lw[i], w) + a;
+            }
+            acc[j] = a;
+        }
+    };
+
+    uint32_t v[16];
+#pragma unroll
+    for (int j = 0; j < 16; j++) v[j] = 0;
+    int tsum = 0;
+    stage(y0 - r);
+    __syncthreads();
+    for (int yin = y0 - r; yin < y1 + r; yin++) {
+        if (yin + 1 < y1 + r) stage(yin + 1);                        // lands in a slot nobody reads this step
+        const int slot = (yin - (y0 - r)) % NS;
+        hrow(slot, v, tsum);
+        const int yold = yin - BS;
+        if (yold >= y0 - r) {
+            uint32_t o[16];
+#pragma unroll
+            for (int j = 0; j < 16; j++) o[j] = 0;
+            int to = 0;
+            hrow((yold - (y0 - r)) % NS, o, to);
+#pragma unroll
+            for (int j = 0; j < 16; j++) v[j] -= o[j];
+            tsum -= to;
+        }
+        const int yout = yin - r;
+        if (yout >= y0) {                                            // uniform
+            // per-thread argmin (ties -> largest d) and the SAD row for the sub-pixel neighbours
+            uint32_t bs_ = v[0]; int bd = 0;
+#pragma unroll
+            for (int j = 1; j < 16; j++) if (v[j] <= bs_) { bs_ = v[j]; bd = j; }
+            cand_s[warp * 32 + lane] = bs_;
+            cand_d[warp * 32 + lane] = (uint32_t)(dlo + bd);
+#pragma unroll
+            for (int j = 0; j < 16; j++) sad[(dlo + j) * 33 + lane] = v[j];
+            if (warp == 0) { badf[lane] = 0; tsum_s[lane] = tsum; }
+            __syncthreads();
+            uint32_t best_s = cand_s[lane]; int best_d = (int)cand_d[lane];
+            for (int w = 1; w < NW; w++) {
+                const uint32_t cs = cand_s[w * 32 + lane];
+                if (cs <= best_s) { best_s = cs; best_d = (int)cand_d[w * 32 + lane]; }
+            }
+            if (e.uniq > 0) {
+                const uint32_t thresh = best_s + best_s * (uint32_t)e.uniq / 100u;
+                bool hit = false;
+#pragma unroll
+                for (int j = 0; j < 16; j++) {
+                    const int dd = dlo + j - best_d;
+                    hit = hit || ((dd > 1 || dd < -1) && v[j] <= thresh);
+                }
+                if (hit) badf[lane] = 1;                             // benign race: every writer stores 1
+            }
+            __syncthreads();
+            if (warp == 0 && x < xe) {
+                int out = -16;
+                if (!(tsum_s[lane] < e.tex) && !badf[lane]) {
+                    const int p = (int)sad[(best_d > 0 ? best_d - 1 : best_d + 1) * 33 + lane];
+                    const int n = (int)sad[(best_d < D - 1 ? best_d + 1 : best_d - 1) * 33 + lane];
+                    const int dd = p + n - 2 * (int)best_s + abs(p - n);
+                    out = (best_d * 256 + (dd ? (p - n) * 256 / dd : 0) + 15) >> 4;
+                }
+                disp[base + (size_t)yout * e.W + x] = (int16_t)out;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+template <int BS>
+static int launch_bm_fast(const uint8_t* PL, const uint8_t* PR, const BmEff& e, int16_t* disp, cudaStream_t st)
+{
+    constexpr int r = BS / 2, NWD = (BS + 3) / 4, NS = BS + 2;
+    const int LBYTES = ((32 + 2 * r + 8 + 15) / 16) * 16;
+    const int RBYTES = ((e.D + 32 + 2 * r + 4 * NWD + 24 + 15) / 16) * 16;
+    const int NW = e.D / 16;
+    const size_t smem = (size_t)NS * (LBYTES + RBYTES) + ((size_t)e.D * 33 + 2 * NW * 32 + 64) * 4;
+    if (smem > 48 * 1024) B2S_CUDA_CHECK(cudaFuncSetAttribute(k_bm_fast<BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int xs = e.D - 1 + e.r, xe = e.W - e.r, ys = e.r, ye = e.H - e.r;
+    const int TR = 96;
+    dim3 grid(b2s_cdiv(xe - xs, 32), b2s_cdiv(ye - ys, TR), e.batch);
+    k_bm_fast<BS><<<grid, 32 * NW, smem, st>>>(PL, PR, e, TR, disp);
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}
+
 __global__ void __launch_bounds__(256)
 k_fill_i16(int16_t* p, size_t n, int16_t v)
 {
@@ -153,6 +321,19 @@ int b2s_bm_run(const uint8_t* left, const uint8_t* right, int H, int W, int batc
     B2S_LAUNCH_CHECK();
     k_bm_prefilter<<<gp, 256, 0, st>>>(right, H, W, e.ftzero, PR);
     B2S_LAUNCH_CHECK();
+    if (e.D <= 512) {
+        switch (p.blockSize) {
+        case 5: return launch_bm_fast<5>(PL, PR, e, disp, st);
+        case 7: return launch_bm_fast<7>(PL, PR, e, disp, st);
+        case 9: return launch_bm_fast<9>(PL, PR, e, disp, st);
+        case 11: return launch_bm_fast<11>(PL, PR, e, disp, st);
+        case 13: return launch_bm_fast<13>(PL, PR, e, disp, st);
+        case 15: return launch_bm_fast<15>(PL, PR, e, disp, st);
+        case 17: return launch_bm_fast<17>(PL, PR, e, disp, st);
+        case 19: return launch_bm_fast<19>(PL, PR, e, disp, st);
+        case 21: return launch_bm_fast<21>(PL, PR, e, disp, st);
+        }
+    }
     const int CW = BM_TW + 2 * e.r;
     size_t smem = ((size_t)CW * e.D + (size_t)BM_TW * e.D + CW) * sizeof(uint32_t);
     if (smem > 220 * 1024) {

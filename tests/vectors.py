@@ -63,6 +63,10 @@ BM_VECTORS = [
     (90, 50, 64, 21, {}),
     (40, 30, 32, 5, {}),                                    # a handful of valid columns
     (30, 30, 32, 5, {}),                                    # no valid column
+    (120, 60, 16, 23, {}),                                  # blockSize > 21: generic kernel
+    (300, 250, 48, 11, {}),                                 # several column strips and row bands
+    (260, 120, 160, 13, dict(uniquenessRatio=5)),           # 10 disparity warps
+    (200, 110, 16, 19, dict(textureThreshold=200)),         # one warp per CTA
 ]
 
 # full-size configurations of BASELINE.json
