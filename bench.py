@@ -302,11 +302,21 @@ def run_b200(args):
     peak, peak_src = measured_peaks()
     achieved = alg_bytes_step / (agg_ms / 1e3) / 1e9
     nl = 2                                                   # k_wave launches per step: forward + mirrored sweep
+    traffic, traffic_src = args.traffic, "command line" if args.traffic else None
+    if traffic is None:
+        # dram bytes per k_wave launch from the committed full ncu capture (tools/make_profiles.py);
+        # only valid for the batch it was captured at
+        import glob
+        for fn in sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic_r*.json")))[::-1]:
+            t = json.load(open(fn))
+            if t.get("batch") == B:
+                traffic, traffic_src = t["avg_dram_bytes_per_launch"], "profiles/" + os.path.basename(fn)
+                break
     roofline = {"bound": "hbm", "kernel": "k_wave (2 launches per step: forward sweep of 4 path directions, mirrored sweep of the "
                                           "other 4 with the winner-take-all fused)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes_step / nl,
-                "avg_launch_ms": agg_ms / nl, "traffic": args.traffic,
+                "avg_launch_ms": agg_ms / nl, "traffic": traffic, "traffic_source": traffic_src,
                 "stage_ms_per_step": {k: v / args.steps for k, v in stage_sum.items()},
                 "stage_share_of_step": {k: v / args.steps / (ms_total / args.steps) for k, v in stage_sum.items()}}
 

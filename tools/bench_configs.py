@@ -1,5 +1,5 @@
 """Device-resident throughput of the other BASELINE.json configurations (cfg1, cfg2, cfg4) next to cv2 on one
-host core.  Informational: the judged line is bench.py (cfg3/cfg5).  usage: python tools/bench_configs.py"""
+host core.  Informational: the judged line is bench.py (cfg3/cfg5).  usage: python tools/bench_configs.py [cfg1|cfg2|cfg4]"""
 import json
 import os
 import sys
@@ -37,7 +37,10 @@ def cpu_time(fn, reps=2):
 
 out = []
 cv2.setNumThreads(1)
+ONLY = sys.argv[1] if len(sys.argv) > 1 else ""
 for name, cfg, B, D in (("cfg1_sgbm_640x480_D64", CFG1, 128, 64), ("cfg4_hh_2864x1988_D256", CFG4, 4, 256)):
+    if ONLY and ONLY not in name:
+        continue
     l, r = synth_pair(cfg["w"], cfg["h"], D, seed=cfg["seed"])
     L = torch.from_numpy(np.stack([l] * B)).cuda()
     R = torch.from_numpy(np.stack([r] * B)).cuda()
@@ -51,6 +54,10 @@ for name, cfg, B, D in (("cfg1_sgbm_640x480_D64", CFG1, 128, 64), ("cfg4_hh_2864
                 "gde_per_s": B / ms * 1e3 * cfg["w"] * cfg["h"] * D / 1e9, "cv2_1thread_ms_per_pair": cms, "parity_ok": ok})
     del m, L, R
     torch.cuda.empty_cache()
+if ONLY and ONLY != "cfg2":
+    for o in out:
+        print(json.dumps(o))
+    sys.exit(0)
 l, r = synth_pair(CFG2["w"], CFG2["h"], CFG2["D"], seed=CFG2["seed"])
 B = 64
 L = torch.from_numpy(np.stack([l] * B)).cuda()

@@ -30,7 +30,7 @@ KERNELS = [
     ("speckle.o", r"k_speckle_apply", "k_speckle_apply"),
     ("geom.o", r"k_remap<1>", "k_remap_c1"),
     ("geom.o", r"k_reproject<short>", "k_reproject_i16"),
-    ("bm.o", r"k_bm", "k_bm"),
+    ("bm.o", r"k_bm_fast<15>", "k_bm_fast_BS15"),
 ]
 
 
@@ -98,6 +98,33 @@ def ncu_summary(rep, out_name):
     return True
 
 
+def traffic_json(rep, out_name):
+    """dram bytes per k_wave launch (read + write) from the full capture -> profiles/traffic_<tag>.json,
+    which bench.py quotes as roofline.traffic."""
+    import json
+    p = os.path.join(ROOT, "gpurun_out", rep)
+    if not os.path.exists(p):
+        return False
+    raw = subprocess.run(["ncu", "-i", p, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    if len(rows) < 3:
+        return False
+    H = rows[0]
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    per = []
+    for r in rows[2:]:
+        tot = 0.0
+        for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            i = H.index(m)
+            tot += float(r[i].replace(",", "")) * scale[rows[1][i]]
+        per.append({"kernel": re.sub(r"\(.*", "", r[H.index("Kernel Name")]), "dram_bytes": tot,
+                    "grid": r[H.index("launch__grid_size")]})
+    with open(os.path.join(OUT, out_name), "w") as f:
+        json.dump({"source": "ncu --set full --clock-control none, gpurun_out/%s, tools/run_sgbm_once.py 128 (cfg3, batch 128)" % rep,
+                   "batch": 128, "launches": per, "avg_dram_bytes_per_launch": sum(x["dram_bytes"] for x in per) / len(per)}, f, indent=1)
+    return True
+
+
 def launch_list(csvname, out_name):
     p = os.path.join(ROOT, "gpurun_out", csvname)
     if not os.path.exists(p):
@@ -138,4 +165,6 @@ if __name__ == "__main__":
     for rep, out in (("wave_%s.ncu-rep" % TAG, "ncu_k_wave_%s.txt" % TAG), ("cost_%s.ncu-rep" % TAG, "ncu_k_cost_%s.txt" % TAG),
                      ("all_%s.ncu-rep" % TAG, "ncu_all_kernels_%s.txt" % TAG)):
         print(out, ncu_summary(rep, out))
+    print("ncu_k_bm", ncu_summary("bm_%s.ncu-rep" % TAG, "ncu_k_bm_%s.txt" % TAG))
+    print("traffic", traffic_json("wave_%s.ncu-rep" % TAG, "traffic_%s.json" % TAG))
     print("launches", launch_list("launches_%s.csv" % TAG, "launches_%s.txt" % TAG))
