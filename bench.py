@@ -241,7 +241,7 @@ def run_b200(args):
     # raw pair from pinned memory and reads disparity + XYZ back.  Two CUDA streams (one matcher handle
     # each, handles own their workspace) alternate steps so the copies of one step overlap the kernels
     # of the other; nothing is skipped or cached.
-    NS = 2
+    NS = args.e2e_streams
     streams = [torch.cuda.Stream(device=dev) for _ in range(NS)]
     matchers = [matcher] + [sm.StereoSGBM_create(**SGBM_KW) for _ in range(NS - 1)]
     disp_h = [torch.empty((B, H, W), dtype=torch.int16).pin_memory() for _ in range(NS)]
@@ -339,7 +339,7 @@ def run_b200(args):
                        "l2": "per-step working set %.1f GB >> 126 MB L2 (no flush needed)" % (matcher.workspace_bytes(H, W, B) / 1e9)},
             "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps, "wall_ms_per_step": wall_e2e / args.steps,
-                    "how": "2 streams x 1 matcher handle each, pinned host buffers, H2D + kernels + D2H per step"},
+                    "how": "%d streams x 1 matcher handle each" % NS + ", pinned host buffers, H2D + kernels + D2H per step"},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "parity_ok": parity,
         }
         emit(line)
@@ -378,6 +378,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=128, help="pairs per step per GPU")
     ap.add_argument("--cpu-pairs", type=int, default=40, help="cpu_baseline: pairs per worker process")
+    ap.add_argument("--e2e-streams", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--traffic", type=float, default=None,

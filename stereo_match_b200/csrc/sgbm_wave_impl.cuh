@@ -420,6 +420,7 @@ k_wave(SgbmEff e, WaveArgs a)
     unsigned phase = 0;
     const unsigned bar_addr = sm0 + P::bar;
     constexpr int PFD = 6;                                              // L2 prefetch distance in steps
+    const int pfoff = (SWZ && (lane & 1)) ? CSB / 2 : 0;                // in u16 elements
 
     // One wavefront step.  Cc/S1c: operands of this step, Cx/S1x: prefetch targets for the next one
     // (the caller alternates the two register sets, so nothing is copied).
@@ -450,8 +451,10 @@ k_wave(SgbmEff e, WaveArgs a)
             // pull the lines of a few steps ahead into L2: the register prefetch above then waits for an
             // L2 hit instead of a DRAM round trip (one step is about as long as the loaded DRAM latency)
             if (rowact && (unsigned)(xs + 1 + PFD) < (unsigned)w1) {
-                prefetch_l2(cptr + PFD * xstep);
-                if (FINAL) prefetch_l2(s1ptr + PFD * xstep);
+                // (permuted records: a lane's two 16-byte chunks sit in different 128-byte lines, and a
+                // prefetch touches one 32-byte sector: even lanes cover chunk 0's line, odd lanes chunk 1's)
+                prefetch_l2(cptr + PFD * xstep + pfoff);
+                if (FINAL) prefetch_l2(s1ptr + PFD * xstep + pfoff);
             }
             cptr += xstep;
             if (FINAL) s1ptr += xstep;
