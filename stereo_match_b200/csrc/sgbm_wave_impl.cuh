@@ -95,6 +95,10 @@ __device__ __forceinline__ void sts_u32(unsigned addr, uint32_t v)
     asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
 
+#ifndef B2S_WAVE_PFD
+#define B2S_WAVE_PFD 6
+#endif
+
 template <int G>
 __device__ __forceinline__ uint32_t group_min_x2(uint32_t v)     // two independent u16 minima at once
 {
@@ -130,7 +134,7 @@ __device__ __forceinline__ uint32_t step(uint32_t (&L)[R], const uint32_t (&C)[R
         uint32_t l = C[i] + u - minx2;        // halves never borrow: u >= minL
         if (PAD) l |= padm[i];                // padded cells (d >= D) stay pinned at 0x7fff
         L[i] = l;
-        mn = __vminu2(mn, l);
+        if (i & 1) mn = __vimin3_u16x2(mn, L[i - 1], l);
     }
     return mn;
 }
@@ -419,7 +423,7 @@ k_wave(SgbmEff e, WaveArgs a)
     }
     unsigned phase = 0;
     const unsigned bar_addr = sm0 + P::bar;
-    constexpr int PFD = 6;                                              // L2 prefetch distance in steps
+    constexpr int PFD = B2S_WAVE_PFD;                                            // L2 prefetch distance in steps
     const int pfoff = (SWZ && (lane & 1)) ? CSB / 2 : 0;                // in u16 elements
 
     // One wavefront step.  Cc/S1c: operands of this step, Cx/S1x: prefetch targets for the next one
