@@ -107,7 +107,7 @@ static SgbmLayout sgbm_layout(const SgbmEff& e, bool speckle, bool keep_volumes)
     const size_t vol = e.width1 > 0 ? (size_t)e.batch * e.H * e.width1 * e.Dp * sizeof(uint16_t) : 0;
     size_t o = 0;
     l.descL = o; o += align_up(npix * sizeof(uint2));
-    l.descR = o; o += align_up(npix * sizeof(uint2));
+    l.descR = o; o += align_up(b2s_desc_right_bytes(e));
     l.cost = o; o += align_up(vol);
     l.S = o; o += align_up(vol);
     l.Sdbg = o; o += (keep_volumes && uses_wave(e)) ? align_up(vol) : 0;
@@ -217,7 +217,7 @@ extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t
     if (rc) return rc;
     char* ws = (char*)h->ws;
     uint2* descL = (uint2*)(ws + l.descL);
-    uint2* descR = (uint2*)(ws + l.descR);
+    void* descR = (void*)(ws + l.descR);         // uint2 per pixel or reversed u16 planes (fast cost kernel)
     uint16_t* cost = (uint16_t*)(ws + l.cost);
     uint16_t* S = (uint16_t*)(ws + l.S);
     int16_t* raw = (int16_t*)(ws + l.raw);
@@ -228,7 +228,7 @@ extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t
 #define B2S_MARK(i) do { if (h->timing) B2S_CUDA_CHECK(cudaEventRecord(h->ev[i], st)); } while (0)
     B2S_MARK(0);
     if ((rc = b2s_launch_descriptors(left, e, descL, st))) return rc;
-    if ((rc = b2s_launch_descriptors(right, e, descR, st))) return rc;
+    if ((rc = b2s_launch_descriptors_right(right, e, descR, st))) return rc;
     B2S_MARK(1);
     if ((rc = b2s_launch_cost(descL, descR, e, cost, h->flag, st))) return rc;
     B2S_MARK(2);

@@ -59,7 +59,9 @@ static inline int b2s_cdiv(long long a, long long b) { return (int)((a + b - 1) 
 // ---- stage launchers (each in its own .cu) ---------------------------------
 // descriptors: per image pixel 2 words: (u, lo, hi, 0) for the Sobel channel and the raw channel
 int b2s_launch_descriptors(const uint8_t* img, const SgbmEff& e, uint2* desc, cudaStream_t st);
-int b2s_launch_cost(const uint2* descL, const uint2* descR, const SgbmEff& e, uint16_t* cost,
+size_t b2s_desc_right_bytes(const SgbmEff& e);
+int b2s_launch_descriptors_right(const uint8_t* img, const SgbmEff& e, void* desc, cudaStream_t st);
+int b2s_launch_cost(const uint2* descL, const void* descR, const SgbmEff& e, uint16_t* cost,
                     int* overflow_flag, cudaStream_t st);
 // first!=0: S = L_r (plain store); otherwise S = min(32767, S + L_r)
 int b2s_launch_aggregate(const uint16_t* cost, uint16_t* S, const SgbmEff& e, int dir, int first,

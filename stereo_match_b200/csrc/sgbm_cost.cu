@@ -8,6 +8,7 @@
 //   cost   [batch][H][width1][Dp] uint16 : raw block cost (cv2's C minus P2); padded cells
 //                                 d >= D hold 0 (the aggregation kernel pins their L_r at 0x7fff)
 #include "common.cuh"
+#include <cuda.h>
 
 // ---------------------------------------------------------------------------
 // descriptors
@@ -29,14 +30,8 @@ __device__ __forceinline__ uint32_t pack_desc(int pm, int p, int pp, bool has_l,
     return (uint32_t)p | ((uint32_t)lo << 8) | ((uint32_t)hi << 16);
 }
 
-__global__ void __launch_bounds__(256)
-k_descriptors(const uint8_t* __restrict__ img, int H, int W, int ftzero, uint2* __restrict__ desc)
+__device__ __forceinline__ uint2 desc_at(const uint8_t* base, int x, int y, int H, int W, int ftzero)
 {
-    int x = blockIdx.x * blockDim.x + threadIdx.x;
-    int y = blockIdx.y;
-    size_t b = blockIdx.z;
-    if (x >= W) return;
-    const uint8_t* base = img + b * (size_t)H * W;
     const uint8_t* c = base + (size_t)y * W;
     const uint8_t* n = base + (size_t)(y > 0 ? y - 1 : y) * W;
     const uint8_t* s = base + (size_t)(y < H - 1 ? y + 1 : y) * W;
@@ -50,7 +45,17 @@ k_descriptors(const uint8_t* __restrict__ img, int H, int W, int ftzero, uint2* 
     uint2 o;
     o.x = pack_desc(g0, g1, g2, x > 0, x < W - 1);
     o.y = pack_desc(r0, r1, r2, x > 0, x < W - 1);
-    desc[b * (size_t)H * W + (size_t)y * W + x] = o;
+    return o;
+}
+
+__global__ void __launch_bounds__(256)
+k_descriptors(const uint8_t* __restrict__ img, int H, int W, int ftzero, uint2* __restrict__ desc)
+{
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    int y = blockIdx.y;
+    size_t b = blockIdx.z;
+    if (x >= W) return;
+    desc[b * (size_t)H * W + (size_t)y * W + x] = desc_at(img + b * (size_t)H * W, x, y, H, W, ftzero);
 }
 
 int b2s_launch_descriptors(const uint8_t* img, const SgbmEff& e, uint2* desc, cudaStream_t st)
@@ -59,6 +64,35 @@ int b2s_launch_descriptors(const uint8_t* img, const SgbmEff& e, uint2* desc, cu
     k_descriptors<<<grid, 256, 0, st>>>(img, e.H, e.W, e.ftzero, desc);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
+}
+
+// Right-image descriptors for the fast cost kernel: per image row twelve u16 planes of PW elements,
+//   plane 2p   [ri]     = component p of pixel x   (p: Sobel value, lo, hi, raw value, lo, hi)
+//   plane 2p+1 [ri - 1] = the same                 (copy shifted by one element)
+// in REVERSED x order, ri = B2S_RPAD + (W - 1 - x), zero outside the image.  The operand pair (x-d, x-d-1)
+// of a packed disparity pair is then one aligned 32-bit word of one of the two copies, and the window of a
+// CTA is twelve contiguous 16-byte aligned runs: one bulk copy (TMA) each, no unpacking in the cost kernel.
+#define B2S_RPAD 8
+static inline int plane_pitch(int W) { return (W + B2S_RPAD + 328 + 7) & ~7; }
+
+__global__ void __launch_bounds__(256)
+k_descriptor_planes(const uint8_t* __restrict__ img, int H, int W, int ftzero, int PW, uint16_t* __restrict__ planes)
+{
+    const int ri = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    const size_t b = blockIdx.z;
+    if (ri >= PW) return;
+    const int x = W - 1 - (ri - B2S_RPAD);
+    uint2 o = make_uint2(0u, 0u);
+    if (x >= 0 && x < W) o = desc_at(img + b * (size_t)H * W, x, y, H, W, ftzero);
+    uint16_t* row = planes + ((b * H + y) * 12) * (size_t)PW;
+    const uint32_t v[6] = { o.x & 0xffu, (o.x >> 8) & 0xffu, (o.x >> 16) & 0xffu, o.y & 0xffu, (o.y >> 8) & 0xffu, (o.y >> 16) & 0xffu };
+#pragma unroll
+    for (int p = 0; p < 6; p++) {
+        row[(2 * p) * (size_t)PW + ri] = (uint16_t)v[p];
+        if (ri > 0) row[(2 * p + 1) * (size_t)PW + ri - 1] = (uint16_t)v[p];
+        if (ri == PW - 1) row[(2 * p + 1) * (size_t)PW + ri] = 0;
+    }
 }
 
 // ---------------------------------------------------------------------------
@@ -210,110 +244,144 @@ __device__ __forceinline__ uint32_t window_sum(uint32_t v)
     return sum;
 }
 
+// ---- mbarrier / bulk-copy helpers (shared-memory addresses as 32-bit .shared offsets) ----
+__device__ __forceinline__ void cmbar_init(unsigned bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void cmbar_arrive(unsigned bar)
+{
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void cmbar_expect_tx(unsigned bar, unsigned bytes)
+{
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cmbar_wait(unsigned bar, unsigned parity)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, 0x989680;\n\t"
+                 "@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ uint32_t lds32(unsigned addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+
+template <int MAXW> struct CostPlan {
+    static constexpr int NSTG = 4;                                        // rows in flight
+    static constexpr int NELP = (32 + 8 * MAXW + 16 + 63) / 64 * 64 + 32; // plane pitch in smem: copies land 64 B apart mod 128
+    static constexpr int STAGE = 12 * NELP * 2;
+    static constexpr int bars = NSTG * STAGE;                             // full[NSTG], empty[NSTG]
+    static constexpr int total = bars + 2 * NSTG * 8;
+};
+
 template <int BS, int MAXW, bool PAD>
 __global__ void __launch_bounds__(32 * MAXW, (MAXW == 16 && BS <= 7) ? 2 : 1)
-k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, SgbmEff e, int TR, int NELP,
+k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap tmap, SgbmEff e, int TR,
             uint16_t* __restrict__ cost, int* __restrict__ overflow_flag)
 {
-    constexpr int SW2 = BS / 2, TW = 32 - (BS - 1);
-    extern __shared__ __align__(16) unsigned char smem_c[];
+    using P = CostPlan<MAXW>;
+    constexpr int SW2 = BS / 2, TW = 32 - (BS - 1), NSTG = P::NSTG, NELP = P::NELP;
+    extern __shared__ __align__(128) unsigned char smem_c[];
+    const unsigned sm0 = (unsigned)__cvta_generic_to_shared(smem_c);
     const int Dp = e.Dp;
-    const int lane = threadIdx.x & 31, oct = threadIdx.x >> 5, nthreads = blockDim.x;
-    // smem: [2] x { LW[32] uint2 , planes[6][2][NELP] u16 }
-    const int stage_bytes = 256 + 12 * NELP * 2;
+    const int lane = threadIdx.x & 31, oct = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     const int x0 = blockIdx.x * TW, yb = blockIdx.y * TR;
-    const size_t b = blockIdx.z;
+    const unsigned b = blockIdx.z;
     const int yend = min(yb + TR, e.H);
+    const int nrows = yend - yb + 2 * SW2;                                    // rows yb-SW2 .. yend+SW2-1 enter the window
     // phase A geometry of this thread (row independent)
     const int xiA = min(max(x0 - SW2 + lane, 0), e.width1 - 1) + e.minX1;     // clamp on the cropped axis
-    const int XRM = min(max(x0 - SW2 + 31, 0), e.width1 - 1) + e.minX1 - e.minD;
-    const int e0 = XRM - (xiA - e.minD - 8 * oct);                            // first reversed element
+    const int XRM = min(max(x0 - SW2 + 31, 0), e.width1 - 1) + e.minX1 - e.minD;   // image column of reversed element 0
+    const int gbase = B2S_RPAD + (e.W - 1 - XRM);                             // its index in the plane rows
+    const int shift = gbase & 7, gal = gbase - shift;                         // bulk copies start 16-byte aligned
+    const int e0 = XRM - (xiA - e.minD - 8 * oct) + shift;                    // first element of this thread in a staged plane
     const int par = e0 & 1;
-    const int roff = 256 + (par * NELP) * 2 + ((e0 - par) >> 1) * 4;          // byte offset inside a stage buffer
-    const int pstride = NELP;                                                 // u32 words between planes (2 copies each)
+    const unsigned roff = (unsigned)((par * NELP) * 2 + ((e0 - par) >> 1) * 4);
     // phase B geometry
     const int opos = b2s_cell_pos(8 * oct, e.R, e.G, e.swz);                  // where this octet lives in the record
     const int xB = x0 + lane;
     const bool outB = lane < TW && xB < e.width1;
-    uint16_t* optr = cost + ((b * e.H + yb) * (size_t)e.width1 + min(xB, e.width1 - 1)) * Dp + opos;   // running store pointer
+    const size_t ostride = (size_t)e.width1 * Dp;
+    uint16_t* optr = cost + (((size_t)b * e.H + yb) * e.width1 + min(xB, e.width1 - 1)) * Dp + opos;   // running store pointer
     uint32_t pmask[4];
 #pragma unroll
     for (int w = 0; w < 4; w++) {
         int d0 = 8 * oct + 2 * w;
         pmask[w] = (d0 < e.D ? 0xffffu : 0u) | (d0 + 1 < e.D ? 0xffff0000u : 0u);
     }
-    // staging role of this thread: element `sel` of the reversed right row (threads beyond nel idle),
-    // threads of the last warp additionally fetch the left words
-    const int nel = 32 + Dp;
-    const int sel = threadIdx.x;                         // nel <= blockDim.x + 32: second element for the first 32 threads
-    const int xr1 = XRM - sel, xr2 = XRM - (sel + nthreads);
-    const bool st1 = sel < nel && xr1 >= 0 && xr1 < e.W, st2 = sel + nthreads < nel && xr2 >= 0 && xr2 < e.W;
-    const bool stL = oct == (nthreads >> 5) - 1;
+    const unsigned bimg = b * (unsigned)(e.H * e.W);                          // batch*H*W < 2^31 is checked on the host
+    auto left_word = [&](int r) {
+        const int yr = min(max(yb - SW2 + r, 0), e.H - 1);
+        return __ldg(descL + (bimg + (unsigned)(yr * e.W + xiA)));
+    };
+    // producer (thread 0): ONE 3-d tensor copy (TMA) per row -- box {8 elements, NELP/8, 12 planes} of the view
+    // {8, PW/8, batch*H*12} of the plane rows -> stage r % NSTG, dense [12][NELP].  Before a stage is refilled every
+    // warp must have handed it back (empty barrier of the row that used it last).
+    const int gal8 = gal >> 3;
+    auto issue = [&](int r) {
+        const int yr = min(max(yb - SW2 + r, 0), e.H - 1);
+        const unsigned st = (unsigned)(r & (NSTG - 1));
+        const unsigned full = sm0 + P::bars + st * 8, dst = sm0 + st * P::STAGE;
+        if (r >= NSTG) cmbar_wait(sm0 + P::bars + (NSTG + st) * 8, (unsigned)((r / NSTG) - 1) & 1u);
+        cmbar_expect_tx(full, (unsigned)P::STAGE);
+        const int row = (int)((b * (unsigned)e.H + (unsigned)yr) * 12u);
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                     ::"r"(dst), "l"(&tmap), "r"(0), "r"(gal8), "r"(row), "r"(full) : "memory");
+    };
 
-    // descriptor addresses as 32-bit pixel offsets from the kernel-argument pointers (batch*H*W < 2^31 is
-    // checked on the host): one IMAD.WIDE per load and nothing to keep live across the row loop
-    const unsigned bimg = (unsigned)b * (unsigned)(e.H * e.W);
-    auto stage_load = [&](int yv, uint2& w1, uint2& w2, uint2& wl) {
-        const int yr = min(max(yv, 0), e.H - 1);
-        const unsigned rb = bimg + (unsigned)(yr * e.W);
-        w1 = make_uint2(0u, 0u); w2 = make_uint2(0u, 0u); wl = make_uint2(0u, 0u);
-        if (st1) w1 = __ldg(descR + (rb + (unsigned)xr1));
-        if (st2) w2 = __ldg(descR + (rb + (unsigned)xr2));
-        if (stL) wl = __ldg(descL + (rb + (unsigned)xiA));
-    };
-    auto stage_put = [&](unsigned char* buf, int el, const uint2& w) {
-        uint16_t* planes = reinterpret_cast<uint16_t*>(buf + 256);
-        const uint32_t vals[6] = { w.x & 0xffu, (w.x >> 8) & 0xffu, (w.x >> 16) & 0xffu,
-                                   w.y & 0xffu, (w.y >> 8) & 0xffu, (w.y >> 16) & 0xffu };
-#pragma unroll
-        for (int p = 0; p < 6; p++) {
-            planes[(2 * p) * NELP + el] = (uint16_t)vals[p];
-            if (el > 0) planes[(2 * p + 1) * NELP + el - 1] = (uint16_t)vals[p];
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < NSTG; i++) {
+            cmbar_init(sm0 + P::bars + i * 8, 1);
+            cmbar_init(sm0 + P::bars + (NSTG + i) * 8, nwarps);
         }
-    };
-    auto stage_store = [&](int bufi, const uint2& w1, const uint2& w2, const uint2& wl) {
-        unsigned char* buf = smem_c + bufi * stage_bytes;
-        if (sel < nel) stage_put(buf, sel, w1);
-        if (sel + nthreads < nel) stage_put(buf, sel + nthreads, w2);
-        if (stL) reinterpret_cast<uint2*>(buf)[lane] = wl;
-    };
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+        for (int r = 0; r < NSTG - 1 && r < nrows; r++) issue(r);
 
     uint32_t acc[4] = { 0, 0, 0, 0 }, ring[BS][4], vmax = 0;
 #pragma unroll
     for (int s = 0; s < BS; s++) { ring[s][0] = ring[s][1] = ring[s][2] = ring[s][3] = 0; }
+    uint2 wl_next = left_word(0);
 
-    {   // first row
-        uint2 w1, w2, wl;
-        stage_load(yb - SW2, w1, w2, wl);
-        stage_store(0, w1, w2, wl);
-    }
-    __syncthreads();
-    int cur = 0;
-    for (int yv0 = yb - SW2; yv0 < yend + SW2; yv0 += BS) {
+    for (int r0 = 0; r0 < nrows; r0 += BS) {
 #pragma unroll
         for (int s = 0; s < BS; s++) {
-            const int yv = yv0 + s;
-            if (yv >= yend + SW2) break;                   // uniform
-            // next row's descriptors travel while this row is computed
-            uint2 nw1, nw2, nwl;
-            const bool more = yv + 1 < yend + SW2;
-            if (more) stage_load(yv + 1, nw1, nw2, nwl);
-            const unsigned char* const buf = smem_c + cur * stage_bytes;
+            const int r = r0 + s;
+            if (r >= nrows) break;                                            // uniform
+            if (threadIdx.x == 0 && r + NSTG - 1 < nrows) issue(r + NSTG - 1);   // keep NSTG-1 rows ahead
+            const uint2 wl = wl_next;
+            if (r + 1 < nrows) wl_next = left_word(r + 1);
+            const unsigned st = (unsigned)(r & (NSTG - 1));
+            cmbar_wait(sm0 + P::bars + st * 8, (unsigned)(r / NSTG) & 1u);
             // ---- phase A: pixel costs of (column, 8 disparities) --------------------------------
             uint32_t hs[4];
             {
-                const uint2 wl = reinterpret_cast<const uint2*>(buf)[lane];
-                const uint32_t* const rbase = reinterpret_cast<const uint32_t*>(buf + roff);
+                const unsigned rb = sm0 + st * P::STAGE + roff;
                 const uint32_t ug = __byte_perm(wl.x, 0, 0x4040), log = __byte_perm(wl.x, 0, 0x4141), hig = __byte_perm(wl.x, 0, 0x4242);
                 const uint32_t ur = __byte_perm(wl.y, 0, 0x4040), lor = __byte_perm(wl.y, 0, 0x4141), hir = __byte_perm(wl.y, 0, 0x4242);
                 uint32_t pc[4];
 #pragma unroll
                 for (int w = 0; w < 4; w++) {
-                    const uint32_t cg = bt2(ug, log, hig, rbase[w], rbase[pstride + w], rbase[2 * pstride + w]);
-                    const uint32_t cr = bt2(ur, lor, hir, rbase[3 * pstride + w], rbase[4 * pstride + w], rbase[5 * pstride + w]);
+                    const uint32_t cg = bt2(ug, log, hig, lds32(rb + 4 * w), lds32(rb + NELP * 4 + 4 * w), lds32(rb + 2 * NELP * 4 + 4 * w));
+                    const uint32_t cr = bt2(ur, lor, hir, lds32(rb + 3 * NELP * 4 + 4 * w), lds32(rb + 4 * NELP * 4 + 4 * w),
+                                            lds32(rb + 5 * NELP * 4 + 4 * w));
                     // (cr - bias) >> 2 == ((cr >> 2) & 0x7f) - 0x40 per half
                     pc[w] = cg + ((cr >> 2) & 0x007f007fu) - (B2S_BIAS + 0x00400040u);
                 }
+                // this warp is done with the stage: hand it back to the producer
+                __syncwarp();
+                if (lane == 0) cmbar_arrive(sm0 + P::bars + (NSTG + st) * 8);
                 // ---- phase B: box sums.  The BS columns are the next BS-1 lanes of this warp: window sum
                 // by doubling (p2 = x + x+1, p4 = p2 + p2(x+2), ...) through shuffles, no shared memory.
 #pragma unroll
@@ -327,17 +395,15 @@ k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, Sg
                 }
                 // a half can only wrap past 0xffff after first being seen >= 0x8000
                 vmax = __vimax3_u16x2(vmax, __vmaxu2(acc[0], acc[1]), __vmaxu2(acc[2], acc[3]));
-                const int yo = yv - SW2;
-                if (outB && yo >= yb) {
-                    uint4 o = make_uint4(acc[0], acc[1], acc[2], acc[3]);
-                    if (PAD) { o.x &= pmask[0]; o.y &= pmask[1]; o.z &= pmask[2]; o.w &= pmask[3]; }
-                    *reinterpret_cast<uint4*>(optr) = o;
+                if (r >= 2 * SW2) {                        // output row yb + r - 2*SW2
+                    if (outB) {
+                        uint4 o = make_uint4(acc[0], acc[1], acc[2], acc[3]);
+                        if (PAD) { o.x &= pmask[0]; o.y &= pmask[1]; o.z &= pmask[2]; o.w &= pmask[3]; }
+                        *reinterpret_cast<uint4*>(optr) = o;
+                    }
+                    optr += ostride;
                 }
-                if (yo >= yb) optr += (size_t)e.width1 * Dp;
             }
-            if (more) stage_store(cur ^ 1, nw1, nw2, nwl);
-            cur ^= 1;
-            __syncthreads();
         }
     }
     if (PAD) vmax &= (pmask[0] | pmask[1] | pmask[2] | pmask[3]);   // coarse: padded lanes never decide
@@ -346,23 +412,71 @@ k_cost_fast(const uint2* __restrict__ descL, const uint2* __restrict__ descR, Sg
     if (2 * (int)m + 3 * e.P2 > 32767) atomicOr(overflow_flag, 1);
 }
 
-template <int BS, int MAXW>
-static int launch_cost_fast(const uint2* descL, const uint2* descR, const SgbmEff& e, uint16_t* cost, int* flag, cudaStream_t st)
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
+typedef CUresult (*tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static tmap_encode_fn tmap_encoder()
 {
+    static tmap_encode_fn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) == cudaSuccess && qr == cudaDriverEntryPointSuccess)
+            fn = (tmap_encode_fn)p;
+    }
+    return fn;
+}
+
+template <int BS, int MAXW>
+static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const SgbmEff& e, uint16_t* cost, int* flag, cudaStream_t st)
+{
+    using P = CostPlan<MAXW>;
     constexpr int TW = 32 - (BS - 1);
-    const int nel = 32 + e.Dp;
-    const int NELP = (nel + 63) / 64 * 64 + 32;            // copies land 64 bytes apart modulo 128: disjoint banks
-    const size_t smem = 2 * (256 + (size_t)12 * NELP * 2);
     const int TR = 75;
     dim3 grid(b2s_cdiv(e.width1, TW), b2s_cdiv(e.H, TR), e.batch);
     const int nthreads = 32 * (e.Dp / 8);
+    const int PW = plane_pitch(e.W);
+    tmap_encode_fn enc = tmap_encoder();
+    if (!enc) { b2s_set_error("cuTensorMapEncodeTiled is not available from this driver"); return B2S_E_CUDA; }
+    CUtensorMap tmap;
+    const cuuint64_t gdim[3] = { 8, (cuuint64_t)PW / 8, (cuuint64_t)e.batch * e.H * 12 };
+    const cuuint64_t gstr[2] = { 16, (cuuint64_t)PW * 2 };
+    const cuuint32_t box[3] = { 8, (cuuint32_t)P::NELP / 8, 12 };
+    const cuuint32_t estr[3] = { 1, 1, 1 };
+    CUresult cr = enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, (void*)planesR, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                      CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) { b2s_set_error("cuTensorMapEncodeTiled failed (%d)", (int)cr); return B2S_E_CUDA; }
     if (e.D != e.Dp) {
-        if (smem > 48 * 1024) B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_cost_fast<BS, MAXW, true><<<grid, nthreads, smem, st>>>(descL, descR, e, TR, NELP, cost, flag);
+        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
+        k_cost_fast<BS, MAXW, true><<<grid, nthreads, P::total, st>>>(descL, tmap, e, TR, cost, flag);
     } else {
-        if (smem > 48 * 1024) B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_cost_fast<BS, MAXW, false><<<grid, nthreads, smem, st>>>(descL, descR, e, TR, NELP, cost, flag);
+        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
+        k_cost_fast<BS, MAXW, false><<<grid, nthreads, P::total, st>>>(descL, tmap, e, TR, cost, flag);
     }
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}
+
+// which of the two cost kernels serves a configuration (decides the format of the right descriptors)
+static bool cost_is_fast(const SgbmEff& e)
+{
+    const int bs = 2 * e.SW2 + 1;
+    return (e.Dp <= 128 && bs <= 11) || (e.Dp <= 256 && bs <= 7);
+}
+
+size_t b2s_desc_right_bytes(const SgbmEff& e)
+{
+    if (cost_is_fast(e)) return (size_t)e.batch * e.H * 12 * plane_pitch(e.W) * sizeof(uint16_t);
+    return (size_t)e.batch * e.H * e.W * sizeof(uint2);
+}
+
+int b2s_launch_descriptors_right(const uint8_t* img, const SgbmEff& e, void* desc, cudaStream_t st)
+{
+    if (!cost_is_fast(e)) return b2s_launch_descriptors(img, e, (uint2*)desc, st);
+    const int PW = plane_pitch(e.W);
+    dim3 grid(b2s_cdiv(PW, 256), e.H, e.batch);
+    k_descriptor_planes<<<grid, 256, 0, st>>>(img, e.H, e.W, e.ftzero, PW, (uint16_t*)desc);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
 }
@@ -370,10 +484,12 @@ static int launch_cost_fast(const uint2* descL, const uint2* descR, const SgbmEf
 static int b2s_launch_cost_generic(const uint2* descL, const uint2* descR, const SgbmEff& e, uint16_t* cost,
                                    int* overflow_flag, cudaStream_t st);
 
-int b2s_launch_cost(const uint2* descL, const uint2* descR, const SgbmEff& e, uint16_t* cost,
+int b2s_launch_cost(const uint2* descL, const void* descRv, const SgbmEff& e, uint16_t* cost,
                     int* overflow_flag, cudaStream_t st)
 {
     const int bs = 2 * e.SW2 + 1;
+    const uint16_t* descR = (const uint16_t*)descRv;      // planes when cost_is_fast(e)
+    if (!cost_is_fast(e)) return b2s_launch_cost_generic(descL, (const uint2*)descRv, e, cost, overflow_flag, st);
     if (e.Dp <= 128) {
         switch (bs) {
         case 1: return launch_cost_fast<1, 16>(descL, descR, e, cost, overflow_flag, st);
@@ -391,7 +507,7 @@ int b2s_launch_cost(const uint2* descL, const uint2* descR, const SgbmEff& e, ui
         case 7: return launch_cost_fast<7, 32>(descL, descR, e, cost, overflow_flag, st);
         }
     }
-    return b2s_launch_cost_generic(descL, descR, e, cost, overflow_flag, st);
+    return B2S_E_UNSUPPORTED;                              // unreachable: cost_is_fast covers exactly the cases above
 }
 
 static int b2s_launch_cost_generic(const uint2* descL, const uint2* descR, const SgbmEff& e, uint16_t* cost,
