@@ -30,32 +30,46 @@ __device__ __forceinline__ uint32_t pack_desc(int pm, int p, int pp, bool has_l,
     return (uint32_t)p | ((uint32_t)lo << 8) | ((uint32_t)hi << 16);
 }
 
-__device__ __forceinline__ uint2 desc_at(const uint8_t* base, int x, int y, int H, int W, int ftzero)
+// (Sobel value, raw value) of the pixels x0 + dir*i, i in [-1, n+1], into sv[i + 1] as g | r << 8: the pixel's own
+// two values are computed once and its neighbours' come from shared memory.  x outside the image -> 0.
+__device__ __forceinline__ void row_values(const uint8_t* base, int x0, int dir, int n, int y, int H, int W, int ftzero, uint16_t* sv)
 {
     const uint8_t* c = base + (size_t)y * W;
-    const uint8_t* n = base + (size_t)(y > 0 ? y - 1 : y) * W;
-    const uint8_t* s = base + (size_t)(y < H - 1 ? y + 1 : y) * W;
-    int g0 = sobel_clip(c, n, s, x - 1, W, ftzero);
-    int g1 = sobel_clip(c, n, s, x, W, ftzero);
-    int g2 = sobel_clip(c, n, s, x + 1, W, ftzero);
-    // raw channel: image value, but the two border columns are the constant ftzero
-    int r0 = (x - 1 <= 0) ? ftzero : c[x - 1];
-    int r1 = (x <= 0 || x >= W - 1) ? ftzero : c[x];
-    int r2 = (x + 1 >= W - 1) ? ftzero : c[min(x + 1, W - 1)];
+    const uint8_t* nn = base + (size_t)(y > 0 ? y - 1 : y) * W;
+    const uint8_t* ss = base + (size_t)(y < H - 1 ? y + 1 : y) * W;
+    for (int i = (int)threadIdx.x - 1; i <= n + 1; i += (int)blockDim.x) {
+        const int x = x0 + dir * i;
+        uint32_t v = 0;
+        if (x >= 0 && x < W) {
+            const int g = sobel_clip(c, nn, ss, x, W, ftzero);
+            const int r = (x <= 0 || x >= W - 1) ? ftzero : c[x];   // raw channel: the two border columns are the constant ftzero
+            v = (uint32_t)g | ((uint32_t)r << 8);
+        }
+        sv[i + 1] = (uint16_t)v;
+    }
+}
+
+// descriptor of pixel x from its own values and those of x-1 (vm) and x+1 (vp)
+__device__ __forceinline__ uint2 desc_from(uint32_t vm, uint32_t v, uint32_t vp, int x, int W)
+{
     uint2 o;
-    o.x = pack_desc(g0, g1, g2, x > 0, x < W - 1);
-    o.y = pack_desc(r0, r1, r2, x > 0, x < W - 1);
+    o.x = pack_desc((int)(vm & 0xffu), (int)(v & 0xffu), (int)(vp & 0xffu), x > 0, x < W - 1);
+    o.y = pack_desc((int)(vm >> 8), (int)(v >> 8), (int)(vp >> 8), x > 0, x < W - 1);
     return o;
 }
 
 __global__ void __launch_bounds__(256)
 k_descriptors(const uint8_t* __restrict__ img, int H, int W, int ftzero, uint2* __restrict__ desc)
 {
-    int x = blockIdx.x * blockDim.x + threadIdx.x;
-    int y = blockIdx.y;
-    size_t b = blockIdx.z;
+    __shared__ uint16_t sv[256 + 4];
+    const int x0 = blockIdx.x * 256;
+    const int y = blockIdx.y;
+    const size_t b = blockIdx.z;
+    row_values(img + b * (size_t)H * W, x0, 1, 256, y, H, W, ftzero, sv);
+    __syncthreads();
+    const int x = x0 + threadIdx.x;
     if (x >= W) return;
-    desc[b * (size_t)H * W + (size_t)y * W + x] = desc_at(img + b * (size_t)H * W, x, y, H, W, ftzero);
+    desc[b * (size_t)H * W + (size_t)y * W + x] = desc_from(sv[threadIdx.x], sv[threadIdx.x + 1], sv[threadIdx.x + 2], x, W);
 }
 
 int b2s_launch_descriptors(const uint8_t* img, const SgbmEff& e, uint2* desc, cudaStream_t st)
@@ -75,24 +89,39 @@ int b2s_launch_descriptors(const uint8_t* img, const SgbmEff& e, uint2* desc, cu
 #define B2S_RPAD 8
 static inline int plane_pitch(int W) { return (W + B2S_RPAD + 328 + 7) & ~7; }
 
+#define B2S_PLANE_EPB 512      // plane elements per block
 __global__ void __launch_bounds__(256)
 k_descriptor_planes(const uint8_t* __restrict__ img, int H, int W, int ftzero, int PW, uint16_t* __restrict__ planes)
 {
-    const int ri = blockIdx.x * blockDim.x + threadIdx.x;
+    // a block = 512 consecutive plane elements ri0 .. ri0+511 (x descending) of one image row
+    constexpr int N = B2S_PLANE_EPB;
+    __shared__ uint16_t sv[N + 6];
+    __shared__ uint2 sd[N + 2];
+    const int ri0 = blockIdx.x * N;
     const int y = blockIdx.y;
     const size_t b = blockIdx.z;
-    if (ri >= PW) return;
-    const int x = W - 1 - (ri - B2S_RPAD);
-    uint2 o = make_uint2(0u, 0u);
-    if (x >= 0 && x < W) o = desc_at(img + b * (size_t)H * W, x, y, H, W, ftzero);
-    uint16_t* row = planes + ((b * H + y) * 12) * (size_t)PW;
-    const uint32_t v[6] = { o.x & 0xffu, (o.x >> 8) & 0xffu, (o.x >> 16) & 0xffu, o.y & 0xffu, (o.y >> 8) & 0xffu, (o.y >> 16) & 0xffu };
-#pragma unroll
-    for (int p = 0; p < 6; p++) {
-        row[(2 * p) * (size_t)PW + ri] = (uint16_t)v[p];
-        if (ri > 0) row[(2 * p + 1) * (size_t)PW + ri - 1] = (uint16_t)v[p];
-        if (ri == PW - 1) row[(2 * p + 1) * (size_t)PW + ri] = 0;
+    const int xfirst = W - 1 - (ri0 - B2S_RPAD);
+    row_values(img + b * (size_t)H * W, xfirst, -1, N + 1, y, H, W, ftzero, sv);     // elements -1 .. N+2
+    __syncthreads();
+    for (int i = threadIdx.x; i <= N; i += 256) {                                    // element ri0+N feeds the shifted copy
+        const int x = xfirst - i;
+        // in reversed order the element before is x+1 and the one after is x-1
+        sd[i] = (x >= 0 && x < W && ri0 + i < PW) ? desc_from(sv[i + 2], sv[i + 1], sv[i], x, W) : make_uint2(0u, 0u);
     }
+    __syncthreads();
+    // thread k owns word k of all twelve plane copies: copy A = elements (2k, 2k+1), copy B = elements (2k+1, 2k+2).
+    // The top byte of a descriptor word is 0, so one PRMT builds a packed pair of u16 values.
+    const int k = threadIdx.x;
+    if (ri0 + 2 * k >= PW) return;
+    const uint2 a = sd[2 * k], m = sd[2 * k + 1], c = sd[2 * k + 2];
+    uint32_t* row = reinterpret_cast<uint32_t*>(planes + ((b * H + y) * 12) * (size_t)PW) + (ri0 >> 1) + k;
+    const size_t pw2 = (size_t)(PW >> 1);
+    row[0] = __byte_perm(a.x, m.x, 0x7430);          row[pw2] = __byte_perm(m.x, c.x, 0x7430);
+    row[2 * pw2] = __byte_perm(a.x, m.x, 0x7531);    row[3 * pw2] = __byte_perm(m.x, c.x, 0x7531);
+    row[4 * pw2] = __byte_perm(a.x, m.x, 0x7632);    row[5 * pw2] = __byte_perm(m.x, c.x, 0x7632);
+    row[6 * pw2] = __byte_perm(a.y, m.y, 0x7430);    row[7 * pw2] = __byte_perm(m.y, c.y, 0x7430);
+    row[8 * pw2] = __byte_perm(a.y, m.y, 0x7531);    row[9 * pw2] = __byte_perm(m.y, c.y, 0x7531);
+    row[10 * pw2] = __byte_perm(a.y, m.y, 0x7632);   row[11 * pw2] = __byte_perm(m.y, c.y, 0x7632);
 }
 
 // ---------------------------------------------------------------------------
@@ -433,7 +462,13 @@ static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const S
 {
     using P = CostPlan<MAXW>;
     constexpr int TW = 32 - (BS - 1);
-    const int TR = 75;
+    // rows per band: tall bands re-read fewer halo rows (BS-1 per band); shorter ones when the batch is too small
+    // to fill the machine otherwise
+    int TR = 125;
+    for (const int cand : { 125, 75, 47, 25 }) {
+        TR = cand;
+        if ((long long)b2s_cdiv(e.width1, TW) * b2s_cdiv(e.H, TR) * e.batch >= 4 * 148) break;
+    }
     dim3 grid(b2s_cdiv(e.width1, TW), b2s_cdiv(e.H, TR), e.batch);
     const int nthreads = 32 * (e.Dp / 8);
     const int PW = plane_pitch(e.W);
@@ -475,7 +510,7 @@ int b2s_launch_descriptors_right(const uint8_t* img, const SgbmEff& e, void* des
 {
     if (!cost_is_fast(e)) return b2s_launch_descriptors(img, e, (uint2*)desc, st);
     const int PW = plane_pitch(e.W);
-    dim3 grid(b2s_cdiv(PW, 256), e.H, e.batch);
+    dim3 grid(b2s_cdiv(PW, B2S_PLANE_EPB), e.H, e.batch);
     k_descriptor_planes<<<grid, 256, 0, st>>>(img, e.H, e.W, e.ftzero, PW, (uint16_t*)desc);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
