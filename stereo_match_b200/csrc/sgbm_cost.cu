@@ -304,8 +304,14 @@ __device__ __forceinline__ uint32_t lds32(unsigned addr)
     return v;
 }
 
+#ifndef B2S_COST_NSTG
+#define B2S_COST_NSTG 8
+#endif
+#ifndef B2S_COST_PRODUCER_LAST
+#define B2S_COST_PRODUCER_LAST 1
+#endif
 template <int MAXW> struct CostPlan {
-    static constexpr int NSTG = 4;                                        // rows in flight
+    static constexpr int NSTG = B2S_COST_NSTG;                            // rows in flight
     static constexpr int NELP = (32 + 8 * MAXW + 16 + 63) / 64 * 64 + 32; // plane pitch in smem: copies land 64 B apart mod 128
     static constexpr int STAGE = 12 * NELP * 2;
     static constexpr int bars = NSTG * STAGE;                             // full[NSTG], empty[NSTG]
@@ -375,7 +381,8 @@ k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    if (threadIdx.x == 0)
+    const bool producer = threadIdx.x == (B2S_COST_PRODUCER_LAST ? blockDim.x - 32 : 0u);
+    if (producer)
         for (int r = 0; r < NSTG - 1 && r < nrows; r++) issue(r);
 
     uint32_t acc[4] = { 0, 0, 0, 0 }, ring[BS][4], vmax = 0;
@@ -388,7 +395,7 @@ k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap
         for (int s = 0; s < BS; s++) {
             const int r = r0 + s;
             if (r >= nrows) break;                                            // uniform
-            if (threadIdx.x == 0 && r + NSTG - 1 < nrows) issue(r + NSTG - 1);   // keep NSTG-1 rows ahead
+            if (producer && r + NSTG - 1 < nrows) issue(r + NSTG - 1);           // keep NSTG-1 rows ahead
             const uint2 wl = wl_next;
             if (r + 1 < nrows) wl_next = left_word(r + 1);
             const unsigned st = (unsigned)(r & (NSTG - 1));
