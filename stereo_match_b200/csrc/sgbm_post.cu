@@ -134,34 +134,55 @@ k_lrcheck(SgbmEff e, int16_t* __restrict__ disp, const uint32_t* __restrict__ di
 
 // Tail of the fused WTA (sgbm_wave): record -> sub-pixel disparity -> LR check -> raw map.
 // rec.x = minS | best << 16 (best = 0xffff: rejected by the uniqueness test), rec.y = S(best-1) | S(best+1) << 16
+__device__ __forceinline__ int finish_pixel(const SgbmEff& e, const uint2 r, const uint32_t* __restrict__ keyrow, int x)
+{
+    if (x < e.minX1 || x >= e.maxX1) return e.invalid;
+    const int best = (int)(r.x >> 16);
+    if (best == 0xffff) return e.invalid;
+    const int minS = (int)(r.x & 0xffffu), sm1 = (int)(r.y & 0xffffu), sp1 = (int)(r.y >> 16);
+    int dq = best * 16;
+    if (best > 0 && best < e.D - 1) {
+        int denom2 = max(sm1 + sp1 - 2 * minS, 1);
+        dq += ((sm1 - sp1) * 16 + denom2) / (denom2 * 2);
+    }
+    const int d1 = dq + e.minD * 16;
+    return lr_consistent(e, keyrow, x, d1) ? d1 : e.invalid;
+}
+
 __global__ void __launch_bounds__(256)
 k_finish_rec(SgbmEff e, const uint2* __restrict__ rec, const uint32_t* __restrict__ disp2key, int16_t* __restrict__ disp)
 {
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= e.W) return;
     const size_t row = ((size_t)blockIdx.z * e.H + blockIdx.y) * e.W;
-    int out = e.invalid;
-    if (x >= e.minX1 && x < e.maxX1) {
-        const uint2 r = rec[row + x];
-        const int best = (int)(r.x >> 16);
-        if (best != 0xffff) {
-            const int minS = (int)(r.x & 0xffffu), sm1 = (int)(r.y & 0xffffu), sp1 = (int)(r.y >> 16);
-            int dq = best * 16;
-            if (best > 0 && best < e.D - 1) {
-                int denom2 = max(sm1 + sp1 - 2 * minS, 1);
-                dq += ((sm1 - sp1) * 16 + denom2) / (denom2 * 2);
-            }
-            const int d1 = dq + e.minD * 16;
-            if (lr_consistent(e, disp2key + row, x, d1)) out = d1;
-        }
-    }
-    disp[row + x] = (int16_t)out;
+    uint2 r = make_uint2(0xffff0000u, 0u);
+    if (x >= e.minX1 && x < e.maxX1) r = rec[row + x];
+    disp[row + x] = (int16_t)finish_pixel(e, r, disp2key + row, x);
+}
+
+// two pixels per thread: one 16-byte record load, one 32-bit store (even W)
+__global__ void __launch_bounds__(256)
+k_finish_rec_x2(SgbmEff e, const uint2* __restrict__ rec, const uint32_t* __restrict__ disp2key, int16_t* __restrict__ disp)
+{
+    const int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+    if (x >= e.W) return;
+    const size_t row = ((size_t)blockIdx.z * e.H + blockIdx.y) * e.W;
+    uint4 r = make_uint4(0xffff0000u, 0u, 0xffff0000u, 0u);
+    if (x + 1 >= e.minX1 && x < e.maxX1) r = *reinterpret_cast<const uint4*>(rec + row + x);
+    const int o0 = finish_pixel(e, make_uint2(r.x, r.y), disp2key + row, x);
+    const int o1 = finish_pixel(e, make_uint2(r.z, r.w), disp2key + row, x + 1);
+    *reinterpret_cast<uint32_t*>(disp + row + x) = ((uint32_t)o0 & 0xffffu) | ((uint32_t)o1 << 16);
 }
 
 int b2s_launch_finish_rec(const SgbmEff& e, const uint2* rec, const uint32_t* disp2key, int16_t* disp_raw, cudaStream_t st)
 {
-    dim3 grid(b2s_cdiv(e.W, 256), e.H, e.batch);
-    k_finish_rec<<<grid, 256, 0, st>>>(e, rec, disp2key, disp_raw);
+    if ((e.W & 1) == 0) {
+        dim3 grid(b2s_cdiv(e.W / 2, 256), e.H, e.batch);
+        k_finish_rec_x2<<<grid, 256, 0, st>>>(e, rec, disp2key, disp_raw);
+    } else {
+        dim3 grid(b2s_cdiv(e.W, 256), e.H, e.batch);
+        k_finish_rec<<<grid, 256, 0, st>>>(e, rec, disp2key, disp_raw);
+    }
     B2S_LAUNCH_CHECK();
     return B2S_OK;
 }
@@ -218,11 +239,49 @@ k_median3(const int16_t* __restrict__ src, int H, int W, int16_t* __restrict__ d
     dst[base + (size_t)y * W + x] = (int16_t)p4;
 }
 
+// two horizontally adjacent pixels per thread as packed s16x2 (VIMNMX.S16x2): half the exchanges, 32-bit
+// loads and stores.  Needs 4-byte aligned rows (even W).
+#define MSORT2(a, b) { uint32_t _t = __vmins2(a, b); b = __vmaxs2(a, b); a = _t; }
+__global__ void __launch_bounds__(256)
+k_median3_x2(const int16_t* __restrict__ src, int H, int W, int16_t* __restrict__ dst)
+{
+    const int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+    const int y = blockIdx.y;
+    if (x >= W) return;
+    const size_t base = (size_t)blockIdx.z * H * W;
+    const uint32_t* r[3] = { reinterpret_cast<const uint32_t*>(src + base + (size_t)max(y - 1, 0) * W),
+                             reinterpret_cast<const uint32_t*>(src + base + (size_t)y * W),
+                             reinterpret_cast<const uint32_t*>(src + base + (size_t)min(y + 1, H - 1) * W) };
+    const int k = x >> 1;
+    uint32_t p[9];
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        const uint32_t a = r[i][k];                                   // (x, x+1)
+        const uint32_t l = x >= 2 ? r[i][k - 1] : __byte_perm(a, a, 0x1010);      // (.., x-1), replicate at the border
+        const uint32_t q = x + 2 < W ? r[i][k + 1] : __byte_perm(a, a, 0x3232);   // (x+2, ..)
+        p[3 * i] = __byte_perm(l, a, 0x5432);                         // (x-1, x)
+        p[3 * i + 1] = a;
+        p[3 * i + 2] = __byte_perm(a, q, 0x5432);                     // (x+1, x+2)
+    }
+    MSORT2(p[1], p[2]) MSORT2(p[4], p[5]) MSORT2(p[7], p[8]) MSORT2(p[0], p[1]) MSORT2(p[3], p[4]) MSORT2(p[6], p[7])
+    MSORT2(p[1], p[2]) MSORT2(p[4], p[5]) MSORT2(p[7], p[8]) MSORT2(p[0], p[3]) MSORT2(p[5], p[8]) MSORT2(p[4], p[7])
+    MSORT2(p[3], p[6]) MSORT2(p[1], p[4]) MSORT2(p[2], p[5]) MSORT2(p[4], p[7]) MSORT2(p[4], p[2]) MSORT2(p[6], p[4])
+    MSORT2(p[4], p[2])
+    reinterpret_cast<uint32_t*>(dst + base + (size_t)y * W)[k] = p[4];
+}
+
 int b2s_launch_median3(const int16_t* src, int H, int W, int batch, int16_t* dst, cudaStream_t st)
 {
+    if ((W & 1) == 0 && (((uintptr_t)src | (uintptr_t)dst) & 3) == 0) {
+        dim3 grid(b2s_cdiv(W / 2, 256), H, batch);
+        k_median3_x2<<<grid, 256, 0, st>>>(src, H, W, dst);
+        B2S_LAUNCH_CHECK();
+        return B2S_OK;
+    }
     dim3 grid(b2s_cdiv(W, 256), H, batch);
     k_median3<<<grid, 256, 0, st>>>(src, H, W, dst);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
 }
+
 
