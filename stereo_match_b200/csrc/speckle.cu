@@ -75,7 +75,7 @@ k_speckle_runs(const int16_t* __restrict__ img, int H, int W, int newVal, int ma
         if (threadIdx.x == SPK_NT - 1) carry_s = s;
         if (x < W) {
             labels[rowbase + x] = valid ? (int32_t)(rowbase + s) : -1;
-            counts[rowbase + x] = 0;
+            if (valid && !connL) counts[rowbase + x] = 0;     // only run starts can become roots
         }
         __syncthreads();
         carry = carry_s;
@@ -126,6 +126,8 @@ k_speckle_count(const int16_t* __restrict__ img, int H, int W, int newVal, int m
     if (root != s) labels[s] = root;                  // every run start now points at its root
 }
 
+// Only small components change, and a small component only has short runs: the last pixel of every run
+// looks up its component size once and, if it is a speckle, clears its own run.
 __global__ void __launch_bounds__(256)
 k_speckle_apply(int16_t* img, int H, int W, int newVal, int maxDiff, int maxSize, const int32_t* __restrict__ labels,
                 const int32_t* __restrict__ counts)
@@ -135,9 +137,24 @@ k_speckle_apply(int16_t* img, int H, int W, int newVal, int maxDiff, int maxSize
     const size_t i = ((size_t)blockIdx.z * H + blockIdx.y) * W + x;
     const int v = img[i];
     if (v == newVal) return;
-    int s = labels[i];                                // run start (or, for a start, its root)
-    const int root = labels[s];                       // root of the run start (a root points at itself)
-    if (counts[root] <= maxSize) img[i] = (int16_t)newVal;
+    if (x + 1 < W) {                                  // only the last pixel of a run works
+        const int r = img[i + 1];
+        if (r != newVal && abs(v - r) <= maxDiff) return;
+    }
+    const int l = __ldg(labels + i);                  // run start (or, for a start, its root)
+    const int root = __ldg(labels + l);               // root of the run start (a root points at itself)
+    if (__ldg(counts + root) > maxSize) return;
+    // walk back to the run start: l for a non-start pixel; a start pixel has no connected left neighbour
+    int j = x;
+    int cur = v;
+    while (true) {
+        const size_t k = i - (size_t)(x - j);
+        int left = newVal;
+        if (j > 0) left = img[k - 1];
+        img[k] = (int16_t)newVal;
+        if (j == 0 || left == newVal || abs(cur - left) > maxDiff) break;
+        cur = left; j--;
+    }
 }
 
 int b2s_launch_speckles(int16_t* img, int H, int W, int batch, int newVal, int maxSize, int maxDiff,
