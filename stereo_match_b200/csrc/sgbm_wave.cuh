@@ -37,6 +37,7 @@ struct WaveArgs {
     uint32_t* disp2key;     // final pass: [batch][H][W] (cost << 16 | 0xffff - x) scatter-min keys
     unsigned long long magic;  // ceil(2^40 / (100 - uniquenessRatio)), 0 if the ratio is >= 100
     int flip;               // 0: forward sweep, 1: both axes reversed
+    int fastacc;            // S can be summed without per-direction saturation (see k_wave, FA)
     int nbands;
 };
 

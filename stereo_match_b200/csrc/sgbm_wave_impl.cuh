@@ -280,7 +280,9 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
     __syncwarp();
 }
 
-template <int R, int G, int NT, bool PAD, bool VERT, bool FINAL>
+// FA ("fast accumulate"): the host proved that S1 + the four L_r of a sweep stay below 65536, so S is summed with
+// plain adds and clamped to 32767 once (all terms are >= 0: same result as cv2's saturating add per direction)
+template <int R, int G, int NT, bool PAD, bool VERT, bool FINAL, bool FA>
 __global__ void __launch_bounds__(NT, (G == 32 ? 1 : 576 / NT))
 k_wave(SgbmEff e, WaveArgs a)
 {
@@ -513,9 +515,13 @@ k_wave(SgbmEff e, WaveArgs a)
             if ((threadIdx.x & 31) == 0) mbar_arrive(bar_addr);
 #pragma unroll
             for (int i = 0; i < R; i++) {
-                uint32_t v = __viaddmin_u16x2(Lv[0][i], Lv[1][i], 0x7fff7fffu);
-                v = __viaddmin_u16x2(v, Lv[2][i], 0x7fff7fffu);
-                Sv[i] = FINAL ? __viaddmin_u16x2(v, S1c[i], 0x7fff7fffu) : v;
+                if (FA) {
+                    Sv[i] = FINAL ? S1c[i] + Lv[0][i] + Lv[1][i] + Lv[2][i] : Lv[0][i] + Lv[1][i] + Lv[2][i];
+                } else {
+                    uint32_t v = __viaddmin_u16x2(Lv[0][i], Lv[1][i], 0x7fff7fffu);
+                    v = __viaddmin_u16x2(v, Lv[2][i], 0x7fff7fffu);
+                    Sv[i] = FINAL ? __viaddmin_u16x2(v, S1c[i], 0x7fff7fffu) : v;
+                }
             }
         } else {
 #pragma unroll
@@ -552,31 +558,39 @@ k_wave(SgbmEff e, WaveArgs a)
     }
 }
 
-template <int R, int G, int NT, bool PAD, bool VERT, bool FINAL>
+template <int R, int G, int NT, bool PAD, bool VERT, bool FINAL, bool FA>
 int launch_one(const SgbmEff& e, const WaveArgs& a, cudaStream_t st)
 {
     using P = Plan<R, G, NT, VERT, FINAL>;
     static bool configured = false;
     if (!configured) {
-        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_wave<R, G, NT, PAD, VERT, FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
+        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_wave<R, G, NT, PAD, VERT, FINAL, FA>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
         configured = true;
     }
     const int grid = e.batch * a.nbands;
-    k_wave<R, G, NT, PAD, VERT, FINAL><<<grid, NT, P::total, st>>>(e, a);
+    k_wave<R, G, NT, PAD, VERT, FINAL, FA><<<grid, NT, P::total, st>>>(e, a);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
+}
+
+template <int R, int G, bool FA>
+int launch_rgf(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
+{
+    constexpr int NT = threads_for(G);
+    const bool pad = e.D != e.Dp;
+    if (vert && !final) return pad ? launch_one<R, G, NT, true, true, false, FA>(e, a, st) : launch_one<R, G, NT, false, true, false, FA>(e, a, st);
+    if (vert && final) return pad ? launch_one<R, G, NT, true, true, true, FA>(e, a, st) : launch_one<R, G, NT, false, true, true, FA>(e, a, st);
+    if (!vert && final) return pad ? launch_one<R, G, NT, true, false, true, false>(e, a, st) : launch_one<R, G, NT, false, false, true, false>(e, a, st);
+    b2s_set_error("wave: unsupported pass combination");
+    return B2S_E_INVALID;
 }
 
 template <int R, int G>
 int launch_rg(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
 {
-    constexpr int NT = threads_for(G);
-    const bool pad = e.D != e.Dp;
-    if (vert && !final) return pad ? launch_one<R, G, NT, true, true, false>(e, a, st) : launch_one<R, G, NT, false, true, false>(e, a, st);
-    if (vert && final) return pad ? launch_one<R, G, NT, true, true, true>(e, a, st) : launch_one<R, G, NT, false, true, true>(e, a, st);
-    if (!vert && final) return pad ? launch_one<R, G, NT, true, false, true>(e, a, st) : launch_one<R, G, NT, false, false, true>(e, a, st);
-    b2s_set_error("wave: unsupported pass combination");
-    return B2S_E_INVALID;
+    // the fast-accumulate variant is only built for the widest lanes (R = 8: D = 128 / 256 / 512)
+    if (R == 8 && a.fastacc) return launch_rgf<R, G, (R == 8)>(e, a, vert, final, st);
+    return launch_rgf<R, G, false>(e, a, vert, final, st);
 }
 
 template <int G>

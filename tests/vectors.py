@@ -27,6 +27,8 @@ SGBM_VECTORS = [
     (300, 200, 0, 96, 5, 600, 2400, 1, 63, 15, 0, 0, 0),
     (420, 70, 0, 200, 3, 100, 800, 1, 63, 10, 1, 0, 0),     # G = 16, padded (Dp = 256), 5 bands
     (23, 50, 0, 16, 3, 100, 800, 1, 63, 10, 1, 0, 0),       # width1 = 7 < one staging chunk
+    (180, 50, 0, 128, 5, 600, 2400, 1, 63, 10, 1, 0, 0),    # R = 8, S summed without per-direction saturation
+    (180, 50, 0, 128, 5, 1000, 8000, 1, 63, 10, 1, 0, 0),   # R = 8, large P2: saturating accumulation
 ]
 
 

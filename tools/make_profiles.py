@@ -17,9 +17,9 @@ TAG = sys.argv[1] if len(sys.argv) > 1 else "r01"
 
 # (object file, regex on the demangled kernel name, output name)
 KERNELS = [
-    ("sgbm_wave_g8.o", r"k_wave<8, 8, 256, false, true, false>", "k_wave_R8_G8_pass1"),
-    ("sgbm_wave_g8.o", r"k_wave<8, 8, 256, false, true, true>", "k_wave_R8_G8_pass2_wta"),
-    ("sgbm_wave_g8.o", r"k_wave<4, 8, 256, false, false, true>", "k_wave_R4_G8_sgbm_last"),
+    ("sgbm_wave_g8.o", r"k_wave<8, 8, 256, false, true, false, true>", "k_wave_R8_G8_pass1"),
+    ("sgbm_wave_g8.o", r"k_wave<8, 8, 256, false, true, true, true>", "k_wave_R8_G8_pass2_wta"),
+    ("sgbm_wave_g8.o", r"k_wave<4, 8, 256, false, false, true, false>", "k_wave_R4_G8_sgbm_last"),
     ("sgbm_cost.o", r"k_cost_fast<5, 16, false>", "k_cost_fast_BS5"),
     ("sgbm_cost.o", r"k_descriptors", "k_descriptors"),
     ("sgbm_post.o", r"k_finish_rec", "k_finish_rec"),
