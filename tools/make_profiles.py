@@ -22,8 +22,9 @@ KERNELS = [
     ("sgbm_wave_g8.o", r"k_wave<4, 8, 256, false, false, true, false>", "k_wave_R4_G8_sgbm_last"),
     ("sgbm_cost.o", r"k_cost_fast<5, 16, false>", "k_cost_fast_BS5"),
     ("sgbm_cost.o", r"k_descriptors", "k_descriptors"),
-    ("sgbm_post.o", r"k_finish_rec", "k_finish_rec"),
-    ("sgbm_post.o", r"k_median3", "k_median3"),
+    ("sgbm_cost.o", r"k_descriptor_planes", "k_descriptor_planes"),
+    ("sgbm_post.o", r"k_finish_rec_x2", "k_finish_rec_x2"),
+    ("sgbm_post.o", r"k_median3_x2", "k_median3_x2"),
     ("speckle.o", r"k_speckle_runs", "k_speckle_runs"),
     ("speckle.o", r"k_speckle_merge", "k_speckle_merge"),
     ("speckle.o", r"k_speckle_count", "k_speckle_count"),
