@@ -16,6 +16,9 @@
  *                       rectified_img_cal.py:253-254, disparity_calculation.py:207-208
  *   b2s_bgr2gray    cv2.cvtColor(img, cv2.COLOR_BGR2GRAY)
  *                       disparity_calculation.py:286-287
+ *   b2s_remap_gray_u8   the two above fused (BGR in, rectified gray out)
+ *   b2s_pipeline    remap x2 -> (gray) -> StereoSGBM.compute -> reprojectImageTo3D, one call
+ *                       disparity_calculation.py:207-208, 286-289, 302
  *   b2s_median3_i16, b2s_filter_speckles
  *                   the cv2.medianBlur / cv2.filterSpeckles that StereoSGBM.compute
  *                   runs internally, exposed for stage-level parity
@@ -144,6 +147,20 @@ B2S_API int b2s_bm_compute(b2s_handle h, const uint8_t* left, const uint8_t* rig
 
 B2S_API void b2s_destroy(b2s_handle h);
 
+/* ---- the whole per-pair chain in one call ---------------------------------
+   remap (cn = 1) or remap + BGR2GRAY (cn = 3) of both raw images -> StereoSGBM.compute ->
+   reprojectImageTo3D(float(disp) * disp_scale, Q)      [skipped when xyz == NULL]
+   Replaces disparity_calculation.py:207-208, 286-289, 302 (and stereo_vision.py:126-127, 178, 209).
+   left_raw/right_raw: [batch][sH][sW][cn] uint8; maps: [H][W] float32 per view, shared by the batch;
+   rect_l/rect_r: caller scratch, [batch][H][W] uint8 each (the rectified gray pair, left for the caller);
+   disp: [batch][H][W] int16; xyz: [batch][H][W][3] float32; Q_host: 16 doubles on the HOST;
+   scratch: >= batch floats, only for handle_missing.  Everything is enqueued on `stream`. */
+B2S_API int b2s_pipeline(b2s_handle sgbm, const uint8_t* left_raw, const uint8_t* right_raw,
+                 int sH, int sW, int cn, const float* mapx_l, const float* mapy_l,
+                 const float* mapx_r, const float* mapy_r, int H, int W, int batch,
+                 uint8_t* rect_l, uint8_t* rect_r, int16_t* disp, const double* Q_host,
+                 float disp_scale, int handle_missing, float* scratch, float* xyz, void* stream);
+
 /* ---- stand-alone stages -------------------------------------------------- */
 #define B2S_DT_U8 0
 #define B2S_DT_I16 1
@@ -160,6 +177,10 @@ B2S_API int b2s_reproject(const void* disp, int dtype, int H, int W, int batch,
 B2S_API int b2s_remap_u8(const uint8_t* src, int sH, int sW, int cn, const float* mapx,
                  const float* mapy, int H, int W, int batch, uint8_t* dst, void* stream);
 B2S_API int b2s_bgr2gray(const uint8_t* bgr, size_t npixels, uint8_t* gray, void* stream);
+/* cv2.remap of a BGR image followed by cv2.cvtColor(BGR2GRAY), fused (same bytes as the two
+   calls; disparity_calculation.py:207-208 + :286-287).  src: [batch][sH][sW][3], dst: [batch][H][W] */
+B2S_API int b2s_remap_gray_u8(const uint8_t* src_bgr, int sH, int sW, const float* mapx,
+                      const float* mapy, int H, int W, int batch, uint8_t* dst_gray, void* stream);
 B2S_API int b2s_median3_i16(const int16_t* src, int H, int W, int batch, int16_t* dst, void* stream);
 /* in place; labels: device scratch of batch*H*W int32, counts likewise */
 B2S_API int b2s_filter_speckles(int16_t* img, int H, int W, int batch, int newVal,

@@ -58,6 +58,9 @@ PROTOTYPES = {
     "b2s_reproject": (_i, [_vp, _i, _i, _i, _i, C.POINTER(C.c_double), C.c_float, _i, _vp, _vp, _vp]),
     "b2s_remap_u8": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "b2s_bgr2gray": (_i, [_vp, _sz, _vp, _vp]),
+    "b2s_remap_gray_u8": (_i, [_vp, _i, _i, _vp, _vp, _i, _i, _i, _vp, _vp]),
+    "b2s_pipeline": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp,
+                          C.POINTER(C.c_double), C.c_float, _i, _vp, _vp, _vp]),
     "b2s_median3_i16": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "b2s_filter_speckles": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
 }

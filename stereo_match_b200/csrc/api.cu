@@ -364,6 +364,33 @@ extern "C" int b2s_sgbm_stage_ms(b2s_handle h, float* ms_host)
     return B2S_OK;
 }
 
+// The reference's per-pair chain as one call (disparity_calculation.py:207-208 remap, :286-287 gray,
+// :289 compute_disparity, :302 reprojectImageTo3D): every stage is enqueued on `stream`, nothing synchronises.
+extern "C" int b2s_pipeline(b2s_handle sgbm, const uint8_t* left_raw, const uint8_t* right_raw, int sH, int sW, int cn,
+                            const float* mapx_l, const float* mapy_l, const float* mapx_r, const float* mapy_r,
+                            int H, int W, int batch, uint8_t* rect_l, uint8_t* rect_r, int16_t* disp,
+                            const double* Q_host, float disp_scale, int handle_missing, float* scratch, float* xyz,
+                            void* stream)
+{
+    if (!sgbm || sgbm->kind != 0) { b2s_set_error("pipeline: bad StereoSGBM handle"); return B2S_E_INVALID; }
+    if (!rect_l || !rect_r) { b2s_set_error("pipeline: rect_l / rect_r scratch buffers are required"); return B2S_E_INVALID; }
+    if (cn != 1 && cn != 3) { b2s_set_error("pipeline: 1 or 3 channels supported, got %d", cn); return B2S_E_UNSUPPORTED; }
+    int rc;
+    if (cn == 1) {
+        if ((rc = b2s_remap_u8(left_raw, sH, sW, 1, mapx_l, mapy_l, H, W, batch, rect_l, stream))) return rc;
+        if ((rc = b2s_remap_u8(right_raw, sH, sW, 1, mapx_r, mapy_r, H, W, batch, rect_r, stream))) return rc;
+    } else {
+        if ((rc = b2s_remap_gray_u8(left_raw, sH, sW, mapx_l, mapy_l, H, W, batch, rect_l, stream))) return rc;
+        if ((rc = b2s_remap_gray_u8(right_raw, sH, sW, mapx_r, mapy_r, H, W, batch, rect_r, stream))) return rc;
+    }
+    if ((rc = b2s_sgbm_compute(sgbm, rect_l, rect_r, H, W, batch, disp, stream))) return rc;
+    if (xyz) {
+        if (!Q_host) { b2s_set_error("pipeline: Q is required when xyz is requested"); return B2S_E_INVALID; }
+        if ((rc = b2s_reproject(disp, B2S_DT_I16, H, W, batch, Q_host, disp_scale, handle_missing, scratch, xyz, stream))) return rc;
+    }
+    return B2S_OK;
+}
+
 extern "C" void b2s_destroy(b2s_handle h)
 {
     if (!h) return;

@@ -144,6 +144,52 @@ extern "C" int b2s_remap_u8(const uint8_t* src, int sH, int sW, int cn, const fl
     return B2S_OK;
 }
 
+// remap of a BGR image followed by BGR->gray, fused: the three rectified channels stay in registers
+// (each rounded to u8 exactly like cv2.remap's output) and only the gray byte is written.
+// Replaces cv2.remap (disparity_calculation.py:207-208) + cv2.cvtColor (:286-287) without the round trip
+// of the 3-channel rectified image through HBM.
+__global__ void __launch_bounds__(256)
+k_remap_gray(const uint8_t* __restrict__ src, int sH, int sW, const float* __restrict__ mapx,
+             const float* __restrict__ mapy, int H, int W, uint8_t* __restrict__ dst)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    if (x >= W) return;
+    const size_t m = (size_t)y * W + x;
+    const int sx = __float2int_rn(__fmul_rn(__ldg(mapx + m), 32.f));
+    const int sy = __float2int_rn(__fmul_rn(__ldg(mapy + m), 32.f));
+    const int ix = min(max(sx >> 5, -32768), 32767), fx = sx & 31;
+    const int iy = min(max(sy >> 5, -32768), 32767), fy = sy & 31;
+    const int w00 = min(32767, (32 - fx) * (32 - fy) * 32), w01 = fx * (32 - fy) * 32;
+    const int w10 = (32 - fx) * fy * 32, w11 = fx * fy * 32;
+    const uint8_t* s = src + (size_t)blockIdx.z * sH * sW * 3;
+    const bool x0 = ix >= 0 && ix < sW, x1 = ix + 1 >= 0 && ix + 1 < sW;
+    const bool y0 = iy >= 0 && iy < sH, y1 = iy + 1 >= 0 && iy + 1 < sH;
+    int ch[3];
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        int t00 = (y0 && x0) ? s[((size_t)iy * sW + ix) * 3 + c] : 0;
+        int t01 = (y0 && x1) ? s[((size_t)iy * sW + ix + 1) * 3 + c] : 0;
+        int t10 = (y1 && x0) ? s[((size_t)(iy + 1) * sW + ix) * 3 + c] : 0;
+        int t11 = (y1 && x1) ? s[((size_t)(iy + 1) * sW + ix + 1) * 3 + c] : 0;
+        ch[c] = (w00 * t00 + w01 * t01 + w10 * t10 + w11 * t11 + 16384) >> 15;
+    }
+    dst[(size_t)blockIdx.z * H * W + m] = (uint8_t)((3735 * ch[0] + 19235 * ch[1] + 9798 * ch[2] + 16384) >> 15);
+}
+
+extern "C" int b2s_remap_gray_u8(const uint8_t* src_bgr, int sH, int sW, const float* mapx, const float* mapy,
+                                 int H, int W, int batch, uint8_t* dst_gray, void* stream)
+{
+    if (!src_bgr || !mapx || !mapy || !dst_gray || sH <= 0 || sW <= 0 || H <= 0 || W <= 0 || batch <= 0) {
+        b2s_set_error("remap_gray: null pointer or empty image");
+        return B2S_E_INVALID;
+    }
+    dim3 grid(b2s_cdiv(W, 256), H, batch);
+    k_remap_gray<<<grid, 256, 0, (cudaStream_t)stream>>>(src_bgr, sH, sW, mapx, mapy, H, W, dst_gray);
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}
+
 // A.8
 __global__ void __launch_bounds__(256)
 k_bgr2gray(const uint8_t* __restrict__ bgr, size_t n, uint8_t* __restrict__ gray)

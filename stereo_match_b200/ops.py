@@ -140,3 +140,78 @@ def filterSpeckles(img, newVal, maxSpeckleSize, maxDiff, buf=None):
     if s.data_ptr() != img.data_ptr():
         img.copy_(s)
     return img, buf
+
+
+def remap_gray(src_bgr, map1, map2):
+    """cv2.cvtColor(cv2.remap(src_bgr, map1, map2, INTER_LINEAR), COLOR_BGR2GRAY) in one kernel
+    (disparity_calculation.py:207-208 + :286-287).  src (H,W,3) or (B,H,W,3) uint8 ->
+    (H',W') or (B,H',W') uint8, byte-identical to the two cv2 calls."""
+    s, kind = _to_device(src_bgr, "src")
+    if s.dtype != torch.uint8 or s.dim() not in (3, 4) or s.shape[-1] != 3:
+        raise error("remap_gray: src must be (H,W,3) or (B,H,W,3) uint8")
+    squeeze = s.dim() == 3
+    if squeeze:
+        s = s[None]
+    mx, _ = _to_device(map1, "map1")
+    my, _ = _to_device(map2, "map2")
+    if mx.dtype != torch.float32 or my.dtype != torch.float32 or mx.shape != my.shape or mx.dim() != 2:
+        raise error("remap_gray: map1/map2 must be float32 (H,W) arrays of the same shape")
+    B, sH, sW, _c = s.shape
+    H, W = mx.shape
+    out = torch.empty((B, H, W), dtype=torch.uint8, device=s.device)
+    with torch.cuda.device(s.device):
+        _lib.check(_lib.load().b2s_remap_gray_u8(_ptr(s), sH, sW, _ptr(mx), _ptr(my), H, W, B, _ptr(out), _stream()))
+    return _from_device(out[0] if squeeze else out, kind)
+
+
+def pipeline(matcher, left_raw, right_raw, maps_left, maps_right, Q=None, *, disp_scale=1.0 / 16.0,
+             handleMissingValues=False):
+    """The reference's per-pair chain in ONE C call (b2s_pipeline): remap both raw images (BGR input is
+    converted to gray in the same kernel) -> matcher.compute -> reprojectImageTo3D(disp * disp_scale, Q).
+    Replaces disparity_calculation.py:207-208, 286-289, 302.
+
+    left_raw/right_raw: (H,W) / (H,W,3) uint8 or batched (B,H,W,1) / (B,H,W,3); maps_*: (mapx, mapy) float32.
+    Returns (disp int16, xyz float32 or None when Q is None, rect_left, rect_right)."""
+    from .engine import StereoSGBM
+    if not isinstance(matcher, StereoSGBM):
+        raise error("pipeline: matcher must be a StereoSGBM")
+    l, kind = _to_device(left_raw, "left")
+    r, _ = _to_device(right_raw, "right")
+    if l.shape != r.shape or l.dtype != torch.uint8 or r.dtype != torch.uint8:
+        raise error("pipeline: left.size() == right.size() && left.type() == right.type() && left.depth() == CV_8U")
+    squeeze = l.dim() == 2 or (l.dim() == 3 and l.shape[-1] == 3)
+    if l.dim() == 2:
+        l, r = l[None, :, :, None], r[None, :, :, None]
+    elif l.dim() == 3:
+        l, r = l[None], r[None]
+    if l.dim() != 4 or l.shape[-1] not in (1, 3):
+        raise error("pipeline: images must be (H,W), (H,W,3), (B,H,W,1) or (B,H,W,3)")
+    B, sH, sW, cn = l.shape
+    mxl, _ = _to_device(maps_left[0], "mapx_l"); myl, _ = _to_device(maps_left[1], "mapy_l")
+    mxr, _ = _to_device(maps_right[0], "mapx_r"); myr, _ = _to_device(maps_right[1], "mapy_r")
+    for m in (mxl, myl, mxr, myr):
+        if m.dtype != torch.float32 or m.shape != mxl.shape or m.dim() != 2:
+            raise error("pipeline: the four maps must be float32 (H,W) arrays of one shape")
+    H, W = mxl.shape
+    dev = l.device
+    rl = torch.empty((B, H, W), dtype=torch.uint8, device=dev)
+    rr = torch.empty_like(rl)
+    disp = torch.empty((B, H, W), dtype=torch.int16, device=dev)
+    xyz = torch.empty((B, H, W, 3), dtype=torch.float32, device=dev) if Q is not None else None
+    scratch = torch.empty(B, dtype=torch.float32, device=dev) if handleMissingValues else None
+    Qp = None
+    if Q is not None:
+        Qh = np.ascontiguousarray(Q.detach().cpu().numpy() if isinstance(Q, torch.Tensor) else Q, dtype=np.float64)
+        if Qh.shape != (4, 4):
+            raise error("pipeline: Q.size() == Size(4,4)")
+        Qp = Qh.ctypes.data_as(C.POINTER(C.c_double))
+    matcher._push()
+    with torch.cuda.device(dev):
+        _lib.check(_lib.load().b2s_pipeline(
+            matcher._h, _ptr(l), _ptr(r), sH, sW, cn, _ptr(mxl), _ptr(myl), _ptr(mxr), _ptr(myr), H, W, B,
+            _ptr(rl), _ptr(rr), _ptr(disp), Qp, C.c_float(disp_scale), int(bool(handleMissingValues)),
+            _ptr(scratch) if scratch is not None else None, _ptr(xyz) if xyz is not None else None, _stream()))
+    outs = [disp, xyz, rl, rr]
+    if squeeze:
+        outs = [o[0] if o is not None else None for o in outs]
+    return tuple(_from_device(o, kind) if o is not None else None for o in outs)

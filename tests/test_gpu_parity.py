@@ -203,6 +203,45 @@ def test_remap_and_gray(cv2ref):
     assert np.array_equal(out[1], cv2ref.remap(batch[1], mx, my))
 
 
+def test_remap_gray_fused(cv2ref):
+    """remap of a BGR image + BGR2GRAY in one kernel == the two cv2 calls (disparity_calculation.py:207-208, 286-287)."""
+    rng = np.random.default_rng(16)
+    mx, my = cv2ref.kitti_rect_maps()
+    img3 = rng.integers(0, 256, (375, 1242, 3), dtype=np.uint8)
+    want = cv2ref.bgr2gray(cv2ref.remap(img3, mx, my))
+    assert np.array_equal(sm.remap_gray(img3, mx, my), want)
+    batch = np.stack([img3, img3[:, ::-1].copy()])
+    out = sm.remap_gray(batch, mx, my)
+    assert np.array_equal(out[0], want)
+    assert np.array_equal(out[1], cv2ref.bgr2gray(cv2ref.remap(batch[1], mx, my)))
+
+
+@pytest.mark.parametrize("cn", [1, 3])
+def test_pipeline_one_call(cv2ref, cn):
+    """b2s_pipeline: remap x2 (+ gray) -> StereoSGBM -> reprojectImageTo3D against the same chain of cv2 calls."""
+    from stereo_match_b200.synth import KITTI_Q
+    rng = np.random.default_rng(17)
+    mx, my = cv2ref.kitti_rect_maps()
+    kw = dict(minDisparity=0, numDisparities=64, blockSize=5, P1=600, P2=2400, disp12MaxDiff=1, preFilterCap=63,
+              uniquenessRatio=15, speckleWindowSize=100, speckleRange=2, mode=sm.STEREO_SGBM_MODE_HH)
+    l, r = synth_pair(1242, 375, 64, seed=5)
+    if cn == 3:
+        l = np.stack([l, np.roll(l, 1, axis=1), l[::-1]], axis=-1).copy()
+        r = np.stack([r, np.roll(r, 1, axis=1), r[::-1]], axis=-1).copy()
+    m = sm.StereoSGBM_create(**kw)
+    disp, xyz, rl, rr = sm.pipeline(m, l, r, (mx, my), (mx, my), KITTI_Q)
+    wl, wr = cv2ref.remap(l, mx, my), cv2ref.remap(r, mx, my)
+    if cn == 3:
+        wl, wr = cv2ref.bgr2gray(wl), cv2ref.bgr2gray(wr)
+    assert np.array_equal(rl, wl) and np.array_equal(rr, wr)
+    wd = cv2ref.sgbm_compute(wl, wr, **kw)
+    assert np.array_equal(disp, wd)
+    wxyz = cv2ref.reproject(wd.astype(np.float32) / 16.0, KITTI_Q)
+    assert np.array_equal(xyz.view(np.uint32), wxyz.view(np.uint32))
+    disp2, none, _, _ = sm.pipeline(m, l, r, (mx, my), (mx, my), None)
+    assert none is None and np.array_equal(disp2, wd)
+
+
 def test_compute_disparity_surface(cv2ref):
     """The reference's compute_disparity (stereo_vision.py:132-184) with settings.ini values."""
     settings = sm.parse_config_file(None)
