@@ -35,6 +35,8 @@ k_reproject(const T* __restrict__ disp, int H, int W, QMat Q, float scale, int h
     float o1 = (float)__dmul_rn((double)(float)P[1], iw);
     float o2 = (float)__dmul_rn((double)(float)P[2], iw);
     if (handle_missing && df == minv[blockIdx.z]) o2 = 10000.f;
+    // (a transposition through shared memory for fully coalesced stores was measured slower: 301 vs 270 us per
+    // 128 cfg3 pairs -- L2 already merges the three strided stores)
     float* o = xyz + i * 3;
     o[0] = o0; o[1] = o1; o[2] = o2;
 }
@@ -128,6 +130,40 @@ k_remap(const uint8_t* __restrict__ src, int sH, int sW, const float* __restrict
     }
 }
 
+// one bilinear sample with cv2's fixed-point weights (A.7); s = image base, constant-0 border
+__device__ __forceinline__ int remap_sample_c1(const uint8_t* __restrict__ s, int sH, int sW, float mxv, float myv)
+{
+    const int sx = __float2int_rn(__fmul_rn(mxv, 32.f));
+    const int sy = __float2int_rn(__fmul_rn(myv, 32.f));
+    const int ix = min(max(sx >> 5, -32768), 32767), fx = sx & 31;
+    const int iy = min(max(sy >> 5, -32768), 32767), fy = sy & 31;
+    const int w00 = min(32767, (32 - fx) * (32 - fy) * 32), w01 = fx * (32 - fy) * 32;
+    const int w10 = (32 - fx) * fy * 32, w11 = fx * fy * 32;
+    const bool x0 = ix >= 0 && ix < sW, x1 = ix + 1 >= 0 && ix + 1 < sW;
+    const bool y0 = iy >= 0 && iy < sH, y1 = iy + 1 >= 0 && iy + 1 < sH;
+    const int t00 = (y0 && x0) ? s[(size_t)iy * sW + ix] : 0;
+    const int t01 = (y0 && x1) ? s[(size_t)iy * sW + ix + 1] : 0;
+    const int t10 = (y1 && x0) ? s[(size_t)(iy + 1) * sW + ix] : 0;
+    const int t11 = (y1 && x1) ? s[(size_t)(iy + 1) * sW + ix + 1] : 0;
+    return (w00 * t00 + w01 * t01 + w10 * t10 + w11 * t11 + 16384) >> 15;
+}
+
+// gray images, even W: two pixels per thread (64-bit map loads, 16-bit store)
+__global__ void __launch_bounds__(256)
+k_remap_c1x2(const uint8_t* __restrict__ src, int sH, int sW, const float* __restrict__ mapx,
+             const float* __restrict__ mapy, int H, int W, uint8_t* __restrict__ dst)
+{
+    const int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+    const int y = blockIdx.y;
+    if (x >= W) return;
+    const size_t m = (size_t)y * W + x;
+    const float2 mxv = __ldg(reinterpret_cast<const float2*>(mapx + m));
+    const float2 myv = __ldg(reinterpret_cast<const float2*>(mapy + m));
+    const uint8_t* s = src + (size_t)blockIdx.z * sH * sW;
+    const int a = remap_sample_c1(s, sH, sW, mxv.x, myv.x), b = remap_sample_c1(s, sH, sW, mxv.y, myv.y);
+    *reinterpret_cast<uint16_t*>(dst + (size_t)blockIdx.z * H * W + m) = (uint16_t)(a | (b << 8));
+}
+
 extern "C" int b2s_remap_u8(const uint8_t* src, int sH, int sW, int cn, const float* mapx, const float* mapy,
                             int H, int W, int batch, uint8_t* dst, void* stream)
 {
@@ -137,7 +173,9 @@ extern "C" int b2s_remap_u8(const uint8_t* src, int sH, int sW, int cn, const fl
     }
     cudaStream_t st = (cudaStream_t)stream;
     dim3 grid(b2s_cdiv(W, 256), H, batch);
-    if (cn == 1) k_remap<1><<<grid, 256, 0, st>>>(src, sH, sW, mapx, mapy, H, W, dst);
+    const bool vec2 = (W & 1) == 0 && ((((uintptr_t)mapx | (uintptr_t)mapy) & 7) == 0) && (((uintptr_t)dst & 1) == 0);
+    if (cn == 1 && vec2) k_remap_c1x2<<<dim3(b2s_cdiv(W / 2, 256), H, batch), 256, 0, st>>>(src, sH, sW, mapx, mapy, H, W, dst);
+    else if (cn == 1) k_remap<1><<<grid, 256, 0, st>>>(src, sH, sW, mapx, mapy, H, W, dst);
     else if (cn == 3) k_remap<3><<<grid, 256, 0, st>>>(src, sH, sW, mapx, mapy, H, W, dst);
     else { b2s_set_error("remap: 1 or 3 channels supported, got %d", cn); return B2S_E_UNSUPPORTED; }
     B2S_LAUNCH_CHECK();
