@@ -1,5 +1,6 @@
 // sgbm_wave_impl.cuh -- the wavefront kernel template (see sgbm_wave.cuh for the design).
 #pragma once
+#include <type_traits>
 #include "sgbm_wave.cuh"
 
 namespace wave {
@@ -430,7 +431,10 @@ k_wave(SgbmEff e, WaveArgs a)
 
     // One wavefront step.  Cc/S1c: operands of this step, Cx/S1x: prefetch targets for the next one
     // (the caller alternates the two register sets, so nothing is copied).
-    auto body = [&](const int t, uint32_t (&Cc)[R], uint32_t (&Cx)[R], uint32_t (&S1c)[R], uint32_t (&S1x)[R]) {
+    // `fast` (compile-time tag): every row of this warp is strictly inside the image at this step, has a row
+    // above and stays in range for the prefetches -- all per-pixel range tests and the zero-record selects vanish.
+    auto body = [&](auto fast, const int t, uint32_t (&Cc)[R], uint32_t (&Cx)[R], uint32_t (&S1c)[R], uint32_t (&S1x)[R]) {
+        constexpr bool FAST = decltype(fast)::value;
         if (VERT && t > 0) { mbar_wait(bar_addr, phase); phase ^= 1u; }   // every warp finished step t-1's ring stores
         if (has_below) {
             // uniform: the band's last row finished `xdone` pixels in the steps before this one.  The release
@@ -440,23 +444,25 @@ k_wave(SgbmEff e, WaveArgs a)
                 publish_progress(a.progress + eitem, xdone);
         }
         const int xs = t - SKEW * g;
-        const bool act = rowact && (unsigned)xs < (unsigned)w1;
+        const bool act = FAST || (rowact && (unsigned)xs < (unsigned)w1);
         if (has_above && (t % CH) == 2 && t >= 2) {              // chunk staging (polled during step t-1)
             const int c = (t - 2) / CH + 1;
             if (c * CH < w1) stage_chunk(c);
         }
         // prefetch the next pixel's operands
         {
-            const bool actn = rowact && (unsigned)(xs + 1) < (unsigned)w1;
+            const bool actn = FAST || (rowact && (unsigned)(xs + 1) < (unsigned)w1);
+            if (!FAST) {
 #pragma unroll
-            for (int i = 0; i < R; i++) { Cx[i] = 0; }
+                for (int i = 0; i < R; i++) { Cx[i] = 0; }
+            }
             if (actn) {
                 ldg_regs_stream<R, CSB>(cptr, Cx);
                 if (FINAL) ldg_regs_stream<R, CSB>(s1ptr, S1x);
             }
             // pull the lines of a few steps ahead into L2: the register prefetch above then waits for an
             // L2 hit instead of a DRAM round trip (one step is about as long as the loaded DRAM latency)
-            if (rowact && (unsigned)(xs + 1 + PFD) < (unsigned)w1) {
+            if (FAST || (rowact && (unsigned)(xs + 1 + PFD) < (unsigned)w1)) {
                 // (permuted records: a lane's two 16-byte chunks sit in different 128-byte lines, and a
                 // prefetch touches one 32-byte sector: even lanes cover chunk 0's line, odd lanes chunk 1's)
                 prefetch_l2(cptr + PFD * xstep + pfoff);
@@ -473,7 +479,7 @@ k_wave(SgbmEff e, WaveArgs a)
 #pragma unroll
             for (int k = 0; k < 3; k++) {
                 const int xp = xs + k - 1;                       // (x-1, x, x+1) of the row above
-                const bool has_pred = rowok && (unsigned)xp < (unsigned)w1;
+                const bool has_pred = FAST || (rowok && (unsigned)xp < (unsigned)w1);
                 const unsigned src = has_pred ? rsrc[k] + ((unsigned)xp & rmask[k]) * rstr : zsrc;
                 const unsigned ms = has_pred ? msrc[k] + ((unsigned)xp & mmask) * 16 : zmin;
                 lds_regs<R, CSB>(src, Lv[k]);
@@ -547,10 +553,20 @@ k_wave(SgbmEff e, WaveArgs a)
 #pragma unroll
     for (int i = 0; i < R; i++) { C2[i] = 0; S2[i] = 0; }
     (void)Cn; (void)S1n; (void)ring1; (void)ring2; (void)ring3; (void)ringmin; (void)zero; (void)zeromin;
+    // steps at which all rows of this warp are interior (see `fast` above)
+    const int gw0 = (int)(threadIdx.x & ~31u) / G, gw3 = gw0 + 32 / G - 1;
+    const bool warp_full = VERT && (gw3 < nrows) && (gw0 > 0 || has_above);
+    const int tfast_lo = warp_full ? SKEW * gw3 + 1 : 0x7fffffff;
+    const int tfast_hi = w1 - 2 - PFD + SKEW * gw0;                   // inclusive
 #pragma unroll 1
     for (int t = 0; t < T; t += 2) {
-        body(t, C, C2, S1, S2);
-        if (t + 1 < T) body(t + 1, C2, C, S2, S1);
+        if (t >= tfast_lo && t + 1 <= tfast_hi) {
+            body(std::true_type{}, t, C, C2, S1, S2);
+            body(std::true_type{}, t + 1, C2, C, S2, S1);
+        } else {
+            body(std::false_type{}, t, C, C2, S1, S2);
+            if (t + 1 < T) body(std::false_type{}, t + 1, C2, C, S2, S1);
+        }
     }
     if (has_below) {                       // the last chunk(s) of the edge stream
         mbar_wait(bar_addr, phase);
