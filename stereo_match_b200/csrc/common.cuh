@@ -29,14 +29,18 @@ __host__ __device__ inline void b2s_dir(int k, int& dx, int& dy)
     dx = DX[k]; dy = DY[k];
 }
 
-// Position of disparity cell d inside a [Dp] record.  Natural order unless `swz`: then the 16-byte chunk c of
-// lane j (cells 16j + 8c ... for R = 8) is stored at chunk slot c*G + j, which makes the group-wide vector
-// accesses of the wavefront kernel contiguous (sgbm_wave_impl.cuh).  Whole octets move, pairs stay adjacent.
+// Position (u16 index) of disparity cell d inside a [Dp] record.  Natural order unless `swz` (R = 8: lane j of the
+// wavefront kernel owns cells 16j .. 16j+15).  Then
+//   * register i of the lane packs the cells (16j + i, 16j + 8 + i): the neighbours d-1 / d+1 of BOTH halves are the
+//     neighbouring registers, so the recurrence needs no shifted copies of L (sgbm_wave_impl.cuh, step());
+//   * registers 0-3 and 4-7 form two 16-byte chunks, and chunk c of lane j is stored at chunk slot c*G + j, which
+//     makes every group-wide vector access contiguous.
 __host__ __device__ inline int b2s_cell_pos(int d, int R, int G, int swz)
 {
     if (!swz) return d;
-    const int nch = R / 4, o = d >> 3;
-    return (((o % nch) * G + o / nch) << 3) | (d & 7);
+    (void)R;
+    const int j = d >> 4, k = d & 15, h = k >> 3, i = k & 7, c = i >> 2, w = i & 3;
+    return ((((c * G + j) << 2) + w) << 1) | h;
 }
 
 void b2s_set_error(const char* fmt, ...);

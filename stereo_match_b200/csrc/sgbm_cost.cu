@@ -124,6 +124,38 @@ k_descriptor_planes(const uint8_t* __restrict__ img, int H, int W, int ftzero, i
     row[10 * pw2] = __byte_perm(a.y, m.y, 0x7632);   row[11 * pw2] = __byte_perm(m.y, c.y, 0x7632);
 }
 
+// The same for the interleaved records (b2s_cell_pos, swz): a packed cell pair is (d, d + 8), so its right-image
+// operands are the pixels x - d and x - d - 8: six u32 planes, element ri = component(ri) | component(ri + 8) << 16.
+__global__ void __launch_bounds__(256)
+k_descriptor_planes8(const uint8_t* __restrict__ img, int H, int W, int ftzero, int PW, uint32_t* __restrict__ planes)
+{
+    constexpr int N = B2S_PLANE_EPB;
+    __shared__ uint16_t sv[N + 8 + 4];
+    __shared__ uint2 sd[N + 8];
+    const int ri0 = blockIdx.x * N;
+    const int y = blockIdx.y;
+    const size_t b = blockIdx.z;
+    const int xfirst = W - 1 - (ri0 - B2S_RPAD);
+    row_values(img + b * (size_t)H * W, xfirst, -1, N + 8, y, H, W, ftzero, sv);     // elements -1 .. N+9
+    __syncthreads();
+    for (int i = threadIdx.x; i < N + 8; i += 256) {
+        const int x = xfirst - i;
+        sd[i] = (x >= 0 && x < W && ri0 + i < PW) ? desc_from(sv[i + 2], sv[i + 1], sv[i], x, W) : make_uint2(0u, 0u);
+    }
+    __syncthreads();
+    uint32_t* row = planes + ((b * H + y) * 6) * (size_t)PW + ri0;
+#pragma unroll
+    for (int j = 0; j < N / 256; j++) {
+        const int k = threadIdx.x + 256 * j;
+        if (ri0 + k >= PW) break;
+        const uint2 a = sd[k], c = sd[k + 8];                 // the top byte of a descriptor word is 0
+        row[k] = __byte_perm(a.x, c.x, 0x7430);               row[(size_t)PW + k] = __byte_perm(a.x, c.x, 0x7531);
+        row[2 * (size_t)PW + k] = __byte_perm(a.x, c.x, 0x7632);
+        row[3 * (size_t)PW + k] = __byte_perm(a.y, c.y, 0x7430);   row[4 * (size_t)PW + k] = __byte_perm(a.y, c.y, 0x7531);
+        row[5 * (size_t)PW + k] = __byte_perm(a.y, c.y, 0x7632);
+    }
+}
+
 // ---------------------------------------------------------------------------
 // BT cost of a disparity pair (d0, d0+1) in packed u16x2, biased by 0x0100 per half so
 // that plain 32-bit adds/subs never borrow across halves.
@@ -221,7 +253,13 @@ k_cost(const uint2* __restrict__ descL, const uint2* __restrict__ descR, SgbmEff
                     int d0 = 2 * dp;
                     if (d0 >= e.D) v = 0u;
                     else if (d0 + 1 >= e.D) v = v & 0xffffu;
-                    *reinterpret_cast<uint32_t*>(out + ((size_t)yo * e.width1 + x) * e.Dp + b2s_cell_pos(d0, e.R, e.G, e.swz)) = v;
+                    uint16_t* rec = out + ((size_t)yo * e.width1 + x) * e.Dp;
+                    if (e.swz) {                      // interleaved records: d0 and d0 + 1 are not neighbours in memory
+                        rec[b2s_cell_pos(d0, e.R, e.G, 1)] = (uint16_t)(v & 0xffffu);
+                        rec[b2s_cell_pos(d0 + 1, e.R, e.G, 1)] = (uint16_t)(v >> 16);
+                    } else {
+                        *reinterpret_cast<uint32_t*>(rec + d0) = v;
+                    }
                 }
             }
         }
@@ -318,7 +356,10 @@ template <int MAXW> struct CostPlan {
     static constexpr int total = bars + 2 * NSTG * 8;
 };
 
-template <int BS, int MAXW, bool PAD>
+// P8: the records are the wavefront kernel's interleaved ones (b2s_cell_pos, swz): a packed pair is (d, d + 8), warp
+// o owns the cells {16q + 4s + w, 16q + 4s + w + 8 : w < 4} with q = o / 2, s = o % 2, and the staged planes hold one
+// u32 (value(x), value(x - 8)) per element instead of two shifted u16 copies.
+template <int BS, int MAXW, bool PAD, bool P8>
 __global__ void __launch_bounds__(32 * MAXW, (MAXW == 16 && BS <= 7) ? 2 : 1)
 k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap tmap, SgbmEff e, int TR,
             uint16_t* __restrict__ cost, int* __restrict__ overflow_flag)
@@ -337,12 +378,13 @@ k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap
     const int xiA = min(max(x0 - SW2 + lane, 0), e.width1 - 1) + e.minX1;     // clamp on the cropped axis
     const int XRM = min(max(x0 - SW2 + 31, 0), e.width1 - 1) + e.minX1 - e.minD;   // image column of reversed element 0
     const int gbase = B2S_RPAD + (e.W - 1 - XRM);                             // its index in the plane rows
-    const int shift = gbase & 7, gal = gbase - shift;                         // bulk copies start 16-byte aligned
-    const int e0 = XRM - (xiA - e.minD - 8 * oct) + shift;                    // first element of this thread in a staged plane
+    const int shift = gbase & (P8 ? 3 : 7), gal = gbase - shift;              // bulk copies start 16-byte aligned
+    const int dfirst = P8 ? 16 * (oct >> 1) + 4 * (oct & 1) : 8 * oct;        // first cell of this warp
+    const int e0 = XRM - (xiA - e.minD - dfirst) + shift;                     // first element of this thread in a staged plane
     const int par = e0 & 1;
-    const unsigned roff = (unsigned)((par * NELP) * 2 + ((e0 - par) >> 1) * 4);
+    const unsigned roff = P8 ? (unsigned)e0 * 4u : (unsigned)((par * NELP) * 2 + ((e0 - par) >> 1) * 4);
     // phase B geometry
-    const int opos = b2s_cell_pos(8 * oct, e.R, e.G, e.swz);                  // where this octet lives in the record
+    const int opos = b2s_cell_pos(dfirst, e.R, e.G, e.swz);                   // where this warp's four words live in the record
     const int xB = x0 + lane;
     const bool outB = lane < TW && xB < e.width1;
     const size_t ostride = (size_t)e.width1 * Dp;
@@ -350,8 +392,8 @@ k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap
     uint32_t pmask[4];
 #pragma unroll
     for (int w = 0; w < 4; w++) {
-        int d0 = 8 * oct + 2 * w;
-        pmask[w] = (d0 < e.D ? 0xffffu : 0u) | (d0 + 1 < e.D ? 0xffff0000u : 0u);
+        const int dlo = P8 ? dfirst + w : dfirst + 2 * w, dhi = P8 ? dlo + 8 : dlo + 1;
+        pmask[w] = (dlo < e.D ? 0xffffu : 0u) | (dhi < e.D ? 0xffff0000u : 0u);
     }
     const unsigned bimg = b * (unsigned)(e.H * e.W);                          // batch*H*W < 2^31 is checked on the host
     auto left_word = [&](int r) {
@@ -361,14 +403,15 @@ k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap
     // producer (thread 0): ONE 3-d tensor copy (TMA) per row -- box {8 elements, NELP/8, 12 planes} of the view
     // {8, PW/8, batch*H*12} of the plane rows -> stage r % NSTG, dense [12][NELP].  Before a stage is refilled every
     // warp must have handed it back (empty barrier of the row that used it last).
-    const int gal8 = gal >> 3;
+    const int gal8 = P8 ? gal >> 2 : gal >> 3;                                // in 16-byte units
+    constexpr unsigned NPL = P8 ? 6u : 12u;                                   // plane rows per image row
     auto issue = [&](int r) {
         const int yr = min(max(yb - SW2 + r, 0), e.H - 1);
         const unsigned st = (unsigned)(r & (NSTG - 1));
         const unsigned full = sm0 + P::bars + st * 8, dst = sm0 + st * P::STAGE;
         if (r >= NSTG) cmbar_wait(sm0 + P::bars + (NSTG + st) * 8, (unsigned)((r / NSTG) - 1) & 1u);
         cmbar_expect_tx(full, (unsigned)P::STAGE);
-        const int row = (int)((b * (unsigned)e.H + (unsigned)yr) * 12u);
+        const int row = (int)((b * (unsigned)e.H + (unsigned)yr) * NPL);
         asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
                      ::"r"(dst), "l"(&tmap), "r"(0), "r"(gal8), "r"(row), "r"(full) : "memory");
     };
@@ -464,7 +507,7 @@ static tmap_encode_fn tmap_encoder()
     return fn;
 }
 
-template <int BS, int MAXW>
+template <int BS, int MAXW, bool P8>
 static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const SgbmEff& e, uint16_t* cost, int* flag, cudaStream_t st)
 {
     using P = CostPlan<MAXW>;
@@ -481,23 +524,32 @@ static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const S
     const int PW = plane_pitch(e.W);
     tmap_encode_fn enc = tmap_encoder();
     if (!enc) { b2s_set_error("cuTensorMapEncodeTiled is not available from this driver"); return B2S_E_CUDA; }
+    // plane rows as a 3-d tensor of 16-byte groups: {8 u16, groups per plane row, plane rows}
     CUtensorMap tmap;
-    const cuuint64_t gdim[3] = { 8, (cuuint64_t)PW / 8, (cuuint64_t)e.batch * e.H * 12 };
-    const cuuint64_t gstr[2] = { 16, (cuuint64_t)PW * 2 };
-    const cuuint32_t box[3] = { 8, (cuuint32_t)P::NELP / 8, 12 };
+    const cuuint64_t rowu16 = P8 ? 2 * (cuuint64_t)PW : (cuuint64_t)PW, npl = P8 ? 6 : 12;
+    const cuuint64_t gdim[3] = { 8, rowu16 / 8, (cuuint64_t)e.batch * e.H * npl };
+    const cuuint64_t gstr[2] = { 16, rowu16 * 2 };
+    const cuuint32_t box[3] = { 8, (cuuint32_t)(P8 ? 2 * P::NELP : P::NELP) / 8, (cuuint32_t)npl };
     const cuuint32_t estr[3] = { 1, 1, 1 };
     CUresult cr = enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, (void*)planesR, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                       CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) { b2s_set_error("cuTensorMapEncodeTiled failed (%d)", (int)cr); return B2S_E_CUDA; }
     if (e.D != e.Dp) {
-        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
-        k_cost_fast<BS, MAXW, true><<<grid, nthreads, P::total, st>>>(descL, tmap, e, TR, cost, flag);
+        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, true, P8>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
+        k_cost_fast<BS, MAXW, true, P8><<<grid, nthreads, P::total, st>>>(descL, tmap, e, TR, cost, flag);
     } else {
-        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
-        k_cost_fast<BS, MAXW, false><<<grid, nthreads, P::total, st>>>(descL, tmap, e, TR, cost, flag);
+        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, false, P8>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
+        k_cost_fast<BS, MAXW, false, P8><<<grid, nthreads, P::total, st>>>(descL, tmap, e, TR, cost, flag);
     }
     B2S_LAUNCH_CHECK();
     return B2S_OK;
+}
+
+template <int BS, int MAXW>
+static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const SgbmEff& e, uint16_t* cost, int* flag, cudaStream_t st)
+{
+    return e.swz ? launch_cost_fast<BS, MAXW, true>(descL, planesR, e, cost, flag, st)
+                 : launch_cost_fast<BS, MAXW, false>(descL, planesR, e, cost, flag, st);
 }
 
 // which of the two cost kernels serves a configuration (decides the format of the right descriptors)
@@ -518,7 +570,8 @@ int b2s_launch_descriptors_right(const uint8_t* img, const SgbmEff& e, void* des
     if (!cost_is_fast(e)) return b2s_launch_descriptors(img, e, (uint2*)desc, st);
     const int PW = plane_pitch(e.W);
     dim3 grid(b2s_cdiv(PW, B2S_PLANE_EPB), e.H, e.batch);
-    k_descriptor_planes<<<grid, 256, 0, st>>>(img, e.H, e.W, e.ftzero, PW, (uint16_t*)desc);
+    if (e.swz) k_descriptor_planes8<<<grid, 256, 0, st>>>(img, e.H, e.W, e.ftzero, PW, (uint32_t*)desc);
+    else k_descriptor_planes<<<grid, 256, 0, st>>>(img, e.H, e.W, e.ftzero, PW, (uint16_t*)desc);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
 }

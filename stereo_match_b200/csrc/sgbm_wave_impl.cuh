@@ -113,7 +113,10 @@ __device__ __forceinline__ uint32_t half_min(uint32_t v) { return min(v & 0xffff
 // One recurrence step of one direction for this lane's 2R disparities:
 //   L(d) <- C(d) + min( L(d), min(L(d-1), L(d+1), minL + P2 - P1) + P1 ) - minL
 // L in/out; returns the packed lane-local minimum of the new L.
-template <int R, int G, bool PAD>
+// IL (interleaved lanes, R == 8 records): register i packs the cells (2R*lane + i, 2R*lane + R + i), so the
+// neighbours d-1 and d+1 of both halves are registers i-1 and i+1 and only the two end registers need a PRMT;
+// otherwise register i packs (2R*lane + 2i, 2R*lane + 2i + 1) and every register needs its shifted copy.
+template <int R, int G, bool PAD, bool IL>
 __device__ __forceinline__ uint32_t step(uint32_t (&L)[R], const uint32_t (&C)[R], int lane, uint32_t p1x2,
                                          uint32_t p2m1x2, uint32_t minx2, const uint32_t (&padm)[R])
 {
@@ -121,17 +124,26 @@ __device__ __forceinline__ uint32_t step(uint32_t (&L)[R], const uint32_t (&C)[R
     uint32_t dn = __shfl_down_sync(0xffffffffu, L[0], 1, G);
     if (lane == 0) up = 0x7fff0000u;          // L(q,-1) = 32767
     if (lane == G - 1) dn = 0x00007fffu;      // L(q, D) = 32767
-    uint32_t sh[R + 1];                       // sh[i] = (L(d-1), L(d)) for register i's low cell
-    sh[0] = __byte_perm(up, L[0], 0x5432);
-#pragma unroll
-    for (int i = 1; i < R; i++) sh[i] = __byte_perm(L[i - 1], L[i], 0x5432);
-    sh[R] = __byte_perm(L[R - 1], dn, 0x5432);
     const uint32_t dmp = minx2 + p2m1x2;      // minL + P2 - P1  (P2 > P1)
+    uint32_t m[R];
+    if (IL) {
+        // L[-1] = (cell 2R*lane - 1, cell 2R*lane + R - 1) ; L[R] = (cell 2R*lane + R, cell 2R*lane + 2R)
+        const uint32_t lm1 = __byte_perm(up, L[R - 1], 0x5432), lr = __byte_perm(L[0], dn, 0x5432);
+#pragma unroll
+        for (int i = 0; i < R; i++) m[i] = __vimin3_u16x2(i == 0 ? lm1 : L[i - 1], i == R - 1 ? lr : L[i + 1], dmp);
+    } else {
+        uint32_t sh[R + 1];                   // sh[i] = (L(d-1), L(d)) for register i's low cell
+        sh[0] = __byte_perm(up, L[0], 0x5432);
+#pragma unroll
+        for (int i = 1; i < R; i++) sh[i] = __byte_perm(L[i - 1], L[i], 0x5432);
+        sh[R] = __byte_perm(L[R - 1], dn, 0x5432);
+#pragma unroll
+        for (int i = 0; i < R; i++) m[i] = __vimin3_u16x2(sh[i], sh[i + 1], dmp);
+    }
     uint32_t mn = 0xffffffffu;
 #pragma unroll
     for (int i = 0; i < R; i++) {
-        uint32_t m = __vimin3_u16x2(sh[i], sh[i + 1], dmp);
-        uint32_t u = __viaddmin_u16x2(m, p1x2, L[i]);
+        uint32_t u = __viaddmin_u16x2(m[i], p1x2, L[i]);
         uint32_t l = C[i] + u - minx2;        // halves never borrow: u >= minL
         if (PAD) l |= padm[i];                // padded cells (d >= D) stay pinned at 0x7fff
         L[i] = l;
@@ -204,12 +216,13 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
                                     uint16_t* scr, bool act, size_t rowpix, int xreal, uint2* rec,
                                     uint32_t* disp2key)
 {
+    constexpr bool IL = CSB != 16;                                 // register i = cells (i, R + i) instead of (2i, 2i + 1)
     const int dbase = lane * 2 * R;
     uint32_t key = 0xffffffffu;
 #pragma unroll
     for (int i = 0; i < R; i++) {
-        uint32_t k0 = __byte_perm(Sv[i], 2 * i, 0x1054);          // S(lo) << 16 | cell
-        uint32_t k1 = __byte_perm(Sv[i], 2 * i + 1, 0x3254);      // S(hi) << 16 | cell
+        uint32_t k0 = __byte_perm(Sv[i], IL ? i : 2 * i, 0x1054);          // S(lo) << 16 | cell
+        uint32_t k1 = __byte_perm(Sv[i], IL ? R + i : 2 * i + 1, 0x3254);  // S(hi) << 16 | cell
         key = __vimin3_u32(key, k0, k1);
     }
     key += dbase;                                                  // cell -> disparity index
@@ -236,8 +249,8 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
             cells = 0;
 #pragma unroll
             for (int i = 0; i < R; i++) {
-                if (dbase + 2 * i < e.D) cells |= 1u << (16 - R + i);
-                if (dbase + 2 * i + 1 < e.D) cells |= 1u << (32 - R + i);
+                if (dbase + (IL ? i : 2 * i) < e.D) cells |= 1u << (16 - R + i);
+                if (dbase + (IL ? R + i : 2 * i + 1) < e.D) cells |= 1u << (32 - R + i);
             }
         }
         uint32_t excl = 0;
@@ -245,7 +258,7 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
 #pragma unroll
         for (int k = -1; k <= 1; k++) {
             int c = bl + k;
-            if (c >= 0 && c < 2 * R) excl |= 1u << ((c & 1) * 16 + 16 - R + (c >> 1));
+            if (c >= 0 && c < 2 * R) excl |= IL ? 1u << ((c / R) * 16 + 16 - R + (c % R)) : 1u << ((c & 1) * 16 + 16 - R + (c >> 1));
         }
         bad_lane = (~acc & cells & ~excl) != 0;
     } else {
@@ -254,7 +267,7 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
         for (int i = 0; i < R; i++) {
 #pragma unroll
             for (int h = 0; h < 2; h++) {
-                int d = dbase + 2 * i + h;
+                int d = dbase + (IL ? h * R + i : 2 * i + h);
                 int val = h ? (int)(Sv[i] >> 16) : (int)(Sv[i] & 0xffffu);
                 int ad = d - best;
                 if (d < e.D && (ad > 1 || ad < -1) && val * mul < thr) bad_lane = true;
@@ -344,8 +357,8 @@ k_wave(SgbmEff e, WaveArgs a)
     uint32_t padm[R];
 #pragma unroll
     for (int i = 0; i < R; i++) {
-        int d0 = lane * 2 * R + 2 * i;
-        padm[i] = PAD ? ((d0 >= e.D ? 0x7fffu : 0u) | (d0 + 1 >= e.D ? 0x7fff0000u : 0u)) : 0u;
+        const int dlo = lane * 2 * R + (SWZ ? i : 2 * i), dhi = SWZ ? dlo + R : dlo + 1;   // cells of register i
+        padm[i] = PAD ? ((dlo >= e.D ? 0x7fffu : 0u) | (dhi >= e.D ? 0x7fff0000u : 0u)) : 0u;
     }
     const uint32_t p1x2 = (uint32_t)e.P1 * 0x10001u;
     const uint32_t p2m1x2 = (uint32_t)(e.P2 - e.P1) * 0x10001u;
@@ -486,7 +499,7 @@ k_wave(SgbmEff e, WaveArgs a)
                 minv[k] = lds_u32(ms);
             }
 #pragma unroll
-            for (int k = 0; k < 3; k++) mnv[k] = step<R, G, PAD>(Lv[k], Cc, lane, p1x2, p2m1x2, minv[k], padm);
+            for (int k = 0; k < 3; k++) mnv[k] = step<R, G, PAD, SWZ>(Lv[k], Cc, lane, p1x2, p2m1x2, minv[k], padm);
             if (act) {
                 sts_regs<R, CSB>(wdst1 + (xs & 3) * (DP * 2), Lv[0]);
                 sts_regs<R, CSB>(wdst2 + (xs & 3) * (DP * 2), Lv[1]);
@@ -534,7 +547,7 @@ k_wave(SgbmEff e, WaveArgs a)
             for (int i = 0; i < R; i++) Sv[i] = FINAL ? S1c[i] : 0u;
         }
         // ---- direction 0: along the row, state in registers -----------------------------------
-        const uint32_t mn0 = step<R, G, PAD>(Lh, Cc, lane, p1x2, p2m1x2, minh, padm);
+        const uint32_t mn0 = step<R, G, PAD, SWZ>(Lh, Cc, lane, p1x2, p2m1x2, minh, padm);
 #pragma unroll
         for (int i = 0; i < R; i++) Sv[i] = __viaddmin_u16x2(Sv[i], Lh[i], 0x7fff7fffu);
         minh = (group_min_x2<G>(half_min(mn0)) & 0xffffu) * 0x10001u;

@@ -167,8 +167,9 @@ class StereoSGBM(_Matcher):
         cost, S = cost.view(shape), S.view(shape)
         if g["swizzled"]:                 # records are stored in the wavefront kernel's lane order: undo it
             d = torch.arange(g["Dp"], device="cuda")
-            o, nch = d // 8, g["R"] // 4
-            pos = ((o % nch) * g["G"] + o // nch) * 8 + d % 8
+            j, k = d // 16, d % 16        # b2s_cell_pos (common.cuh): register i packs cells (16j + i, 16j + 8 + i)
+            h, i = k // 8, k % 8
+            pos = (((i // 4) * g["G"] + j) * 4 + i % 4) * 2 + h
             cost, S = cost[..., pos], S[..., pos]
         return cost, S, g
 

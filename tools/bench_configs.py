@@ -38,7 +38,7 @@ def cpu_time(fn, reps=2):
 out = []
 cv2.setNumThreads(1)
 ONLY = sys.argv[1] if len(sys.argv) > 1 else ""
-for name, cfg, B, D in (("cfg1_sgbm_640x480_D64", CFG1, 128, 64), ("cfg4_hh_2864x1988_D256", CFG4, 4, 256)):
+for name, cfg, B, D in (("cfg1_sgbm_640x480_D64", CFG1, 128, 64), ("cfg4_hh_2864x1988_D256", CFG4, 12, 256)):
     if ONLY and ONLY not in name:
         continue
     l, r = synth_pair(cfg["w"], cfg["h"], D, seed=cfg["seed"])

@@ -20,9 +20,9 @@ KERNELS = [
     ("sgbm_wave_g8.o", r"k_wave<8, 8, 256, false, true, false, true>", "k_wave_R8_G8_pass1"),
     ("sgbm_wave_g8.o", r"k_wave<8, 8, 256, false, true, true, true>", "k_wave_R8_G8_pass2_wta"),
     ("sgbm_wave_g8.o", r"k_wave<4, 8, 256, false, false, true, false>", "k_wave_R4_G8_sgbm_last"),
-    ("sgbm_cost.o", r"k_cost_fast<5, 16, false>", "k_cost_fast_BS5"),
+    ("sgbm_cost.o", r"k_cost_fast<5, 16, false, true>", "k_cost_fast_BS5"),
     ("sgbm_cost.o", r"k_descriptors", "k_descriptors"),
-    ("sgbm_cost.o", r"k_descriptor_planes", "k_descriptor_planes"),
+    ("sgbm_cost.o", r"k_descriptor_planes8", "k_descriptor_planes8"),
     ("sgbm_post.o", r"k_finish_rec_x2", "k_finish_rec_x2"),
     ("sgbm_post.o", r"k_median3_x2", "k_median3_x2"),
     ("speckle.o", r"k_speckle_runs", "k_speckle_runs"),
