@@ -49,6 +49,7 @@ int b2s_launch_wave(const SgbmEff& e, const uint16_t* cost, uint16_t* S, uint16_
     const int mul = 100 - e.uniq;
     a.magic = mul > 0 ? ((1ull << 40) + (unsigned long long)mul - 1) / (unsigned long long)mul : 0ull;
     a.nbands = l.nbands;
+    a.zero = 0u;
     // L_r <= C + P2 and C <= blockSize^2 * (2*ftzero + 63) (Sobel channel BT cost <= 2*ftzero, raw channel <= 255 >> 2):
     // if S1 (<= 32767) plus four such terms cannot reach 65536, the packed sums never carry between the halves
     {

@@ -39,6 +39,7 @@ struct WaveArgs {
     int flip;               // 0: forward sweep, 1: both axes reversed
     int fastacc;            // S can be summed without per-direction saturation (see k_wave, FA)
     int nbands;
+    unsigned int zero;      // always 0, opaque to the compiler (see `dep` in k_wave)
 };
 
 // threads per CTA of the wavefront kernel: small CTAs keep the per-step barrier cheap and let
