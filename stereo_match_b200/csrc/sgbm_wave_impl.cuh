@@ -99,6 +99,11 @@ __device__ __forceinline__ void sts_u32(unsigned addr, uint32_t v)
 #ifndef B2S_WAVE_DEP
 #define B2S_WAVE_DEP 1
 #endif
+// pixels of the edge row between two release stores of the progress counter (each costs the publishing warp a
+// gpu-scope fence, about 1000 cycles)
+#ifndef B2S_WAVE_PUBW
+#define B2S_WAVE_PUBW 32
+#endif
 #ifndef B2S_WAVE_PFD
 #define B2S_WAVE_PFD 6
 #endif
@@ -385,9 +390,15 @@ k_wave(SgbmEff e, WaveArgs a)
         if ((int)threadIdx.x < npx)
             cp_async16(stagemin + ((c & 1) * CH + threadIdx.x) * 4, eabove_min + (size_t)(x0 + threadIdx.x) * 4);
     };
+    // thread 0 remembers the last progress value it saw: once the producer band is far ahead (the steady state of the
+    // band-major ticket order) whole stretches of chunks need no acquire load at all
+    int known = 0;
     auto wait_progress = [&](int need) {
+        if (known >= need) return;
         const int* p = a.progress + (eitem - 1);
-        while (ld_acquire(p) < need) __nanosleep(64);
+        int v;
+        while ((v = ld_acquire(p)) < need) __nanosleep(64);
+        known = v;
     };
     if (has_above) {
         if (threadIdx.x == 0) wait_progress(min(CH, w1));
@@ -456,7 +467,7 @@ k_wave(SgbmEff e, WaveArgs a)
             // uniform: the band's last row finished `xdone` pixels in the steps before this one.  The release
             // store of one thread is cumulative over the edge stores the other lanes made before they arrived.
             const int xdone = t - SKEW * gl;
-            if (xdone > 0 && ((xdone % CH) == 0 || xdone == w1) && threadIdx.x == pubthread)
+            if (xdone > 0 && ((xdone % B2S_WAVE_PUBW) == 0 || xdone == w1) && threadIdx.x == pubthread)
                 publish_progress(a.progress + eitem, xdone);
         }
         const int xs = t - SKEW * g;
