@@ -263,10 +263,17 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
         }
         uint32_t excl = 0;
         const int bl = best - dbase;
+        if (IL && R == 8) {
+            // cells bl-1 .. bl+1 of this lane as a 16-bit linear mask (bit c = cell c), then cell c -> bit 8 + c (c < 8)
+            // or 16 + c (c >= 8): bytes 0 / 1 of the linear mask become bytes 1 / 3
+            const unsigned sh = (unsigned)min(max(bl + 2, 0), 31);
+            excl = __byte_perm(((7u << sh) >> 3) & 0xffffu, 0u, 0x1404);
+        } else {
 #pragma unroll
-        for (int k = -1; k <= 1; k++) {
-            int c = bl + k;
-            if (c >= 0 && c < 2 * R) excl |= IL ? 1u << ((c / R) * 16 + 16 - R + (c % R)) : 1u << ((c & 1) * 16 + 16 - R + (c >> 1));
+            for (int k = -1; k <= 1; k++) {
+                int c = bl + k;
+                if (c >= 0 && c < 2 * R) excl |= IL ? 1u << ((c / R) * 16 + 16 - R + (c % R)) : 1u << ((c & 1) * 16 + 16 - R + (c >> 1));
+            }
         }
         bad_lane = (~acc & cells & ~excl) != 0;
     } else {
@@ -460,19 +467,23 @@ k_wave(SgbmEff e, WaveArgs a)
     // (the caller alternates the two register sets, so nothing is copied).
     // `fast` (compile-time tag): every row of this warp is strictly inside the image at this step, has a row
     // above and stays in range for the prefetches -- all per-pixel range tests and the zero-record selects vanish.
-    auto body = [&](auto fast, const int t, uint32_t (&Cc)[R], uint32_t (&Cx)[R], uint32_t (&S1c)[R], uint32_t (&S1x)[R]) {
+    // `odd` (compile-time tag): parity of t.  The rare events of the band pipeline happen at fixed residues of t mod CH
+    // (CH is 4 or 8) and of (t - 2*gl) mod B2S_WAVE_PUBW, so each body only carries the tests of its own parity.
+    auto body = [&](auto fast, auto odd, const int t, uint32_t (&Cc)[R], uint32_t (&Cx)[R], uint32_t (&S1c)[R], uint32_t (&S1x)[R]) {
         constexpr bool FAST = decltype(fast)::value;
+        constexpr bool ODD = decltype(odd)::value;
         if (VERT && t > 0) { mbar_wait(bar_addr, phase); phase ^= 1u; }   // every warp finished step t-1's ring stores
-        if (has_below) {
+        if (!ODD && has_below) {
             // uniform: the band's last row finished `xdone` pixels in the steps before this one.  The release
             // store of one thread is cumulative over the edge stores the other lanes made before they arrived.
+            // (xdone == w1 is only reached after the loop, see the end of the kernel.)
             const int xdone = t - SKEW * gl;
-            if (xdone > 0 && ((xdone % B2S_WAVE_PUBW) == 0 || xdone == w1) && threadIdx.x == pubthread)
+            if (xdone > 0 && (xdone % B2S_WAVE_PUBW) == 0 && threadIdx.x == pubthread)
                 publish_progress(a.progress + eitem, xdone);
         }
         const int xs = t - SKEW * g;
         const bool act = FAST || (rowact && (unsigned)xs < (unsigned)w1);
-        if (has_above && (t % CH) == 2 && t >= 2) {              // chunk staging (polled during step t-1)
+        if (!ODD && has_above && (t % CH) == 2 && t >= 2) {      // chunk staging (polled during step t-1)
             const int c = (t - 2) / CH + 1;
             if (c * CH < w1) stage_chunk(c);
         }
@@ -547,8 +558,8 @@ k_wave(SgbmEff e, WaveArgs a)
                 }
             }
             if (has_above) {
-                if ((t % CH) == CH - 2) cp_async_wait_all();
-                if ((t % CH) == 1 && threadIdx.x == 0) {
+                if (!ODD && (t % CH) == CH - 2) cp_async_wait_all();
+                if (ODD && (t % CH) == 1 && threadIdx.x == 0) {
                     const int c = t / CH + 1;
                     if (c * CH < w1) wait_progress(min((c + 1) * CH, w1));
                 }
@@ -598,11 +609,11 @@ k_wave(SgbmEff e, WaveArgs a)
 #pragma unroll 1
     for (int t = 0; t < T; t += 2) {
         if (t >= tfast_lo && t + 1 <= tfast_hi) {
-            body(std::true_type{}, t, C, C2, S1, S2);
-            body(std::true_type{}, t + 1, C2, C, S2, S1);
+            body(std::true_type{}, std::false_type{}, t, C, C2, S1, S2);
+            body(std::true_type{}, std::true_type{}, t + 1, C2, C, S2, S1);
         } else {
-            body(std::false_type{}, t, C, C2, S1, S2);
-            if (t + 1 < T) body(std::false_type{}, t + 1, C2, C, S2, S1);
+            body(std::false_type{}, std::false_type{}, t, C, C2, S1, S2);
+            if (t + 1 < T) body(std::false_type{}, std::true_type{}, t + 1, C2, C, S2, S1);
         }
     }
     if (has_below) {                       // the last chunk(s) of the edge stream
