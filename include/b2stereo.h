@@ -59,7 +59,7 @@ extern "C" {
 #define B2S_MODE_SGBM 0
 #define B2S_MODE_HH 1
 #define B2S_MODE_SGBM_3WAY 2 /* unsupported */
-#define B2S_MODE_HH4 3       /* unsupported */
+#define B2S_MODE_HH4 3       /* 4 paths: -> , <- , down, up (with cv2 4.13.0's bottom-row rule) */
 
 /* matcher parameters exactly as cv2.StereoSGBM_create receives them (raw, before
    cv2's silent fallbacks -- those are applied inside) */
@@ -97,7 +97,7 @@ typedef struct b2s_sgbm_geometry {
     int32_t Dp;                   /* padded disparity stride of the cost volumes */
     int32_t invalid;              /* (minDisparity-1)*16 */
     int32_t P1, P2, ftzero, uniquenessRatio, disp12MaxDiff; /* effective values */
-    int32_t ndirs;                /* 5 (MODE_SGBM) or 8 (MODE_HH) */
+    int32_t ndirs;                /* 5 (MODE_SGBM), 8 (MODE_HH) or 4 (MODE_HH4) */
     int32_t R, G;                 /* Dp = 2*R*G: G lanes per pixel, R packed registers per lane */
     int32_t swizzled;             /* 1: cell d of a [Dp] record sits at ((o % (R/4))*G + o/(R/4))*8 + d%8, o = d/8 */
 } b2s_sgbm_geometry;

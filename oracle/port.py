@@ -79,6 +79,28 @@ def sgbm_compute(left, right, want_volumes=False, **kw):
     return (disp, Cv, Sv, raw) if want_volumes else disp
 
 
+def sgbm_hsum(left, right, **kw):
+    """Stage tap: horizontal window sums hs[H][width1][D] int32."""
+    left = np.ascontiguousarray(left, np.uint8)
+    right = np.ascontiguousarray(right, np.uint8)
+    H, W = left.shape
+    p = sgbm_params(**kw)
+    w1 = sgbm_geometry(W, **kw)["width1"]
+    out = np.empty((H, w1, p.numDisparities), np.int32)
+    if lib().orc_sgbm_hsum(_p(left), _p(right), H, W, C.byref(p), _p(out)) != 0:
+        raise ValueError("oracle: empty computed area")
+    return out
+
+
+def sgbm_finish(S, W, **kw):
+    """Stage tap: S volume -> final disparity (WTA, LR check, median, speckle filter)."""
+    S = np.ascontiguousarray(S, np.int16)
+    p = sgbm_params(**kw)
+    disp = np.empty((S.shape[0], W), np.int16)
+    lib().orc_sgbm_finish(_p(S), S.shape[0], int(W), C.byref(p), _p(disp))
+    return disp
+
+
 def sgbm_path(Cvol, P1, P2, k):
     """L_r of direction k (0..7, order of DIRS in stereo_oracle.c) from an int16 C volume."""
     Cvol = np.ascontiguousarray(Cvol, np.int16)

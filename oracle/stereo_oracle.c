@@ -107,8 +107,7 @@ static eff_t effective(const orc_sgbm_params* p, int W)
 /* SURVEY.md A.1 + A.2: C[y][x][d] = i16(P2 + block sum of BT cost).   */
 /* Cvol must hold H*width1*D int16.                                    */
 /* ------------------------------------------------------------------ */
-static void cost_volume(const uint8_t* L, const uint8_t* R, int H, int W,
-                        const eff_t* e, int16_t* Cvol)
+static int32_t* hsum_volume(const uint8_t* L, const uint8_t* R, int H, int W, const eff_t* e)
 {
     const int D = e->D, w1 = e->width1;
     size_t plane = (size_t)H * W;
@@ -147,6 +146,15 @@ static void cost_volume(const uint8_t* L, const uint8_t* R, int H, int W,
                 hrow[(size_t)x * D + d] = s;
             }
     }
+    free(pix); free(buf);
+    return hs;
+}
+
+static void cost_volume(const uint8_t* L, const uint8_t* R, int H, int W,
+                        const eff_t* e, int16_t* Cvol)
+{
+    int32_t* hs = hsum_volume(L, R, H, W, e);
+    size_t rowsz = (size_t)e->width1 * e->D;
     for (int y = 0; y < H; y++) {
         int16_t* crow = Cvol + (size_t)y * rowsz;
         for (size_t i = 0; i < rowsz; i++) {
@@ -156,7 +164,7 @@ static void cost_volume(const uint8_t* L, const uint8_t* R, int H, int W,
             crow[i] = wrap16(s);
         }
     }
-    free(hs); free(pix); free(buf);
+    free(hs);
 }
 
 /* ------------------------------------------------------------------ */
@@ -301,7 +309,13 @@ ORC_API int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, i
                              const orc_sgbm_params* p, int16_t* disp,
                              int16_t* Cout, int16_t* Sout, int16_t* raw)
 {
-    if (p->mode != 0 && p->mode != 1) return -1;
+    /* direction sets (indices into DIRS): MODE_SGBM 5 paths, MODE_HH 8, MODE_HH4 the two horizontal and the
+       two vertical ones (probed against cv2 4.13.0, tests/test_oracle_vs_cv2.py) */
+    unsigned dirmask;
+    if (p->mode == 0) dirmask = 0x1f;
+    else if (p->mode == 1) dirmask = 0xff;
+    else if (p->mode == 3) dirmask = 0x55;
+    else return -1;
     eff_t e = effective(p, W);
     size_t n = (size_t)H * W;
     /* cv2 4.13.0 (stereosgbm.cpp:511) raises cv2.error unless
@@ -312,9 +326,15 @@ ORC_API int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, i
     int16_t* Cvol = (int16_t*)malloc(vol * sizeof(int16_t));
     int32_t* Ssum = (int32_t*)calloc(vol, sizeof(int32_t));
     cost_volume(left, right, H, W, &e, Cvol);
-    int ndirs = p->mode == 1 ? 8 : 5;
-    for (int k = 0; k < ndirs; k++)
-        aggregate_dir(Cvol, H, e.width1, e.D, e.P1, e.P2, DIRS[k][0], DIRS[k][1], Ssum, NULL);
+    if (p->mode == 3) {
+        /* cv2 4.13.0 MODE_HH4: the rows whose vertical window reaches below the image (y > 0, y + SH2 >= H) are
+           never filled, C stays at its initial value P2 (found by probing: blockSize 1 matches the plain
+           4-direction sum, every larger block only with this rule) */
+        for (int y = imax(1, H - e.SH2); y < H; y++)
+            for (size_t i = 0; i < (size_t)e.width1 * e.D; i++) Cvol[(size_t)y * e.width1 * e.D + i] = wrap16(e.P2);
+    }
+    for (int k = 0; k < 8; k++)
+        if (dirmask >> k & 1) aggregate_dir(Cvol, H, e.width1, e.D, e.P1, e.P2, DIRS[k][0], DIRS[k][1], Ssum, NULL);
     int16_t* S = (int16_t*)malloc(vol * sizeof(int16_t));
     for (size_t i = 0; i < vol; i++) S[i] = sat16(Ssum[i]);
     int16_t* tmp = (int16_t*)malloc(n * sizeof(int16_t));
@@ -326,6 +346,31 @@ ORC_API int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, i
     if (Cout) memcpy(Cout, Cvol, vol * sizeof(int16_t));
     if (Sout) memcpy(Sout, S, vol * sizeof(int16_t));
     free(tmp); free(S); free(Ssum); free(Cvol);
+    return 0;
+}
+
+/* stage taps for probing cv2 variants: horizontal window sums hs[H][width1][D] (int32, A.2) ... */
+ORC_API int orc_sgbm_hsum(const uint8_t* left, const uint8_t* right, int H, int W, const orc_sgbm_params* p, int32_t* out)
+{
+    eff_t e = effective(p, W);
+    if (e.width1 <= 0) return -1;
+    int32_t* hs = hsum_volume(left, right, H, W, &e);
+    memcpy(out, hs, (size_t)H * e.width1 * e.D * sizeof(int32_t));
+    free(hs);
+    return 0;
+}
+
+/* ... and everything behind the aggregation: S[H][width1][D] -> final disparity (A.3 - A.5) */
+ORC_API int orc_sgbm_finish(const int16_t* S, int H, int W, const orc_sgbm_params* p, int16_t* disp)
+{
+    eff_t e = effective(p, W);
+    size_t n = (size_t)H * W;
+    int16_t* tmp = (int16_t*)malloc(n * sizeof(int16_t));
+    wta_rows(S, H, W, &e, tmp);
+    orc_median3_i16(tmp, H, W, disp);
+    if (p->speckleWindowSize > 0)
+        orc_filter_speckles(disp, H, W, e.INVALID, p->speckleWindowSize, 16 * p->speckleRange);
+    free(tmp);
     return 0;
 }
 

@@ -46,14 +46,21 @@ struct b2s_matcher {
     bool ev_valid = false;
 };
 
+// zeroes the last `n16` uint4 of every pair's slab (slabs `pitch16` uint4 apart): MODE_HH4's bottom cost rows
+__global__ void k_zero_tail(uint4* p, size_t pitch16, size_t n16)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n16) p[(size_t)blockIdx.y * pitch16 + i] = make_uint4(0u, 0u, 0u, 0u);
+}
+
 static size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 
 // ---- SGBM parameter rules -----------------------------------
 static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, SgbmEff& e)
 {
     if (p.numDisparities <= 0) { b2s_set_error("StereoSGBM: numDisparities must be positive"); return B2S_E_INVALID; }
-    if (p.mode != B2S_MODE_SGBM && p.mode != B2S_MODE_HH) {
-        b2s_set_error("StereoSGBM: mode %d (MODE_SGBM_3WAY / MODE_HH4) is not supported by this engine", p.mode);
+    if (p.mode != B2S_MODE_SGBM && p.mode != B2S_MODE_HH && p.mode != B2S_MODE_HH4) {
+        b2s_set_error("StereoSGBM: mode %d (MODE_SGBM_3WAY) is not supported by this engine", p.mode);
         return B2S_E_UNSUPPORTED;
     }
     e.H = H; e.W = W; e.batch = batch;
@@ -71,7 +78,7 @@ static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, Sgb
     e.maxX1 = W + (e.minD < 0 ? e.minD : 0);
     e.width1 = e.maxX1 - e.minX1;
     e.invalid = (e.minD - 1) * 16;
-    e.ndirs = p.mode == B2S_MODE_HH ? 8 : 5;
+    e.ndirs = p.mode == B2S_MODE_HH ? 8 : (p.mode == B2S_MODE_HH4 ? 4 : 5);
     // cv2 4.13.0 stereosgbm.cpp:511 raises cv2.error on this condition
     if (!(W - maxD > e.SW2)) {
         b2s_set_error("StereoSGBM: Your input images are too small for your window size and max disparity "
@@ -231,6 +238,17 @@ extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t
     if ((rc = b2s_launch_descriptors_right(right, e, descR, st))) return rc;
     B2S_MARK(1);
     if ((rc = b2s_launch_cost(descL, descR, e, cost, h->flag, st))) return rc;
+    if (e.ndirs == 4 && e.SW2 > 0 && H > 1) {
+        // cv2 4.13.0's MODE_HH4 never fills the block cost of the rows whose window reaches below the image (its
+        // copy of the row loop has no branch for them): C stays at P2 there, i.e. raw cost 0 (probed against cv2,
+        // tests/test_oracle_vs_cv2.py::test_hh4).  Rows y >= max(1, H - SW2) of every pair:
+        const int y0 = H - e.SW2 > 1 ? H - e.SW2 : 1;
+        const size_t rowb = (size_t)e.width1 * e.Dp * sizeof(uint16_t);
+        const size_t n16 = (size_t)(H - y0) * rowb / 16;           // Dp is a multiple of 32 cells: whole uint4s
+        dim3 grid((unsigned)b2s_cdiv((long long)n16, 256), (unsigned)batch);
+        k_zero_tail<<<grid, 256, 0, st>>>(reinterpret_cast<uint4*>(cost + (size_t)y0 * e.width1 * e.Dp), (size_t)H * rowb / 16, n16);
+        B2S_LAUNCH_CHECK();
+    }
     B2S_MARK(2);
     uint16_t* Sfull = S;
     if (uses_wave(e)) {
@@ -240,7 +258,7 @@ extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t
         B2S_MARK(3);
         if ((rc = b2s_launch_finish_rec(e, (const uint2*)(ws + l.rec), key, raw, st))) return rc;
     } else {
-        for (int k = 0; k < e.ndirs; k++)
+        for (int k = 0; k < (e.ndirs == 4 ? 8 : e.ndirs); k += (e.ndirs == 4 ? 2 : 1))    // MODE_HH4: -> , down, <- , up
             if ((rc = b2s_launch_aggregate(cost, S, e, k, k == 0, st))) return rc;
         B2S_MARK(3);
         if ((rc = b2s_launch_wta(S, e, raw, key, st))) return rc;

@@ -14,7 +14,7 @@ struct SgbmEff {
     int P1, P2, uniq, lrmax, ftzero;
     int minX1, maxX1, width1;
     int invalid;              // (minD-1)*16
-    int ndirs;                // 5 or 8
+    int ndirs;                // 5 (MODE_SGBM), 8 (MODE_HH) or 4 (MODE_HH4)
     int G;                    // lanes per pixel in the aggregation/WTA kernels (8, 16 or 32)
     int R;                    // packed u16x2 registers per lane: Dp = 2*R*G
     int swz;                  // 1: [Dp] records of the cost/S volumes use the permuted cell order of b2s_cell_pos

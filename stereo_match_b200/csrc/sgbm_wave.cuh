@@ -6,6 +6,7 @@
 //   pass 2 (flipped sweep) : directions  <- , up-left,   up,   up-right     S = S1 + ..., then
 //                            winner-take-all + uniqueness + disp2 scatter fused on the registers
 //   MODE_SGBM              : pass 1, then a horizontal-only flipped sweep (<-) with the same WTA
+//   MODE_HH4               : both sweeps without their diagonal directions (-> , down | <- , up)
 //
 // so the cost volume is read once per pass and S is written once and read once: 10 B per cost
 // cell of HBM traffic including the cost kernel's write (the reference algorithm's own 8 B plus
@@ -39,6 +40,7 @@ struct WaveArgs {
     int flip;               // 0: forward sweep, 1: both axes reversed
     int fastacc;            // S can be summed without per-direction saturation (see k_wave, FA)
     int nbands;
+    int diag;               // 1: the sweeps carry the two diagonal directions (MODE_SGBM / MODE_HH), 0: MODE_HH4
     unsigned int zero;      // always 0, opaque to the compiler (see `dep` in k_wave)
 };
 

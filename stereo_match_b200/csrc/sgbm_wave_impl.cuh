@@ -311,7 +311,9 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
 
 // FA ("fast accumulate"): the host proved that S1 + the four L_r of a sweep stay below 65536, so S is summed with
 // plain adds and clamped to 32767 once (all terms are >= 0: same result as cv2's saturating add per direction)
-template <int R, int G, int NT, bool PAD, bool VERT, bool FINAL, bool FA>
+// DIAG = false (MODE_HH4): only the straight vertical direction comes from the row above; the two diagonal
+// slots of the rings and of the edge stream stay unused.
+template <int R, int G, int NT, bool PAD, bool VERT, bool FINAL, bool FA, bool DIAG = true>
 __global__ void __launch_bounds__(NT, (G == 32 ? 1 : 576 / NT))
 k_wave(SgbmEff e, WaveArgs a)
 {
@@ -526,6 +528,12 @@ k_wave(SgbmEff e, WaveArgs a)
             uint32_t Lv[3][R], minv[3], mnv[3];
 #pragma unroll
             for (int k = 0; k < 3; k++) {
+                if (!DIAG && k != 1) {
+#pragma unroll
+                    for (int i = 0; i < R; i++) Lv[k][i] = 0u;
+                    minv[k] = 0u; mnv[k] = 0u;
+                    continue;
+                }
                 const int xp = xs + k - 1;                       // (x-1, x, x+1) of the row above
                 const bool has_pred = FAST || (rowok && (unsigned)xp < (unsigned)w1);
                 const unsigned src = has_pred ? rsrc[k] + ((unsigned)xp & rmask[k]) * rstr : zsrc;
@@ -534,20 +542,21 @@ k_wave(SgbmEff e, WaveArgs a)
                 minv[k] = lds_u32(ms);
             }
 #pragma unroll
-            for (int k = 0; k < 3; k++) mnv[k] = step<R, G, PAD, SWZ>(Lv[k], Cc, lane, p1x2, p2m1x2, minv[k], padm);
+            for (int k = 0; k < 3; k++)
+                if (DIAG || k == 1) mnv[k] = step<R, G, PAD, SWZ>(Lv[k], Cc, lane, p1x2, p2m1x2, minv[k], padm);
             if (act) {
-                sts_regs<R, CSB>(wdst1 + (xs & 3) * (DP * 2), Lv[0]);
+                if (DIAG) sts_regs<R, CSB>(wdst1 + (xs & 3) * (DP * 2), Lv[0]);
                 sts_regs<R, CSB>(wdst2 + (xs & 3) * (DP * 2), Lv[1]);
-                sts_regs<R, CSB>(wdst3 + (xs & 1) * (DP * 2), Lv[2]);
+                if (DIAG) sts_regs<R, CSB>(wdst3 + (xs & 1) * (DP * 2), Lv[2]);
                 if (edgerow) {
-                    st_regs<R, CSB>(eptr, Lv[0]);
+                    if (DIAG) st_regs<R, CSB>(eptr, Lv[0]);
                     st_regs<R, CSB>(eptr + DP, Lv[1]);
-                    st_regs<R, CSB>(eptr + 2 * DP, Lv[2]);
+                    if (DIAG) st_regs<R, CSB>(eptr + 2 * DP, Lv[2]);
                 }
             }
             eptr += 3 * DP;
             const uint32_t r12 = group_min_x2<G>(half_min(mnv[0]) | (half_min(mnv[1]) << 16));
-            const uint32_t r3 = group_min_x2<G>(half_min(mnv[2]));
+            const uint32_t r3 = DIAG ? group_min_x2<G>(half_min(mnv[2])) : 0u;
             if (act && lane == 0) {
                 const uint32_t m1 = (r12 & 0xffffu) * 0x10001u, m2 = (r12 >> 16) * 0x10001u, m3 = (r3 & 0xffffu) * 0x10001u;
                 const unsigned md = wmin + (xs & 3) * 16;
@@ -622,17 +631,17 @@ k_wave(SgbmEff e, WaveArgs a)
     }
 }
 
-template <int R, int G, int NT, bool PAD, bool VERT, bool FINAL, bool FA>
+template <int R, int G, int NT, bool PAD, bool VERT, bool FINAL, bool FA, bool DIAG = true>
 int launch_one(const SgbmEff& e, const WaveArgs& a, cudaStream_t st)
 {
     using P = Plan<R, G, NT, VERT, FINAL>;
     static bool configured = false;
     if (!configured) {
-        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_wave<R, G, NT, PAD, VERT, FINAL, FA>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
+        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_wave<R, G, NT, PAD, VERT, FINAL, FA, DIAG>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
         configured = true;
     }
     const int grid = e.batch * a.nbands;
-    k_wave<R, G, NT, PAD, VERT, FINAL, FA><<<grid, NT, P::total, st>>>(e, a);
+    k_wave<R, G, NT, PAD, VERT, FINAL, FA, DIAG><<<grid, NT, P::total, st>>>(e, a);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
 }
@@ -642,6 +651,11 @@ int launch_rgf(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStr
 {
     constexpr int NT = threads_for(G);
     const bool pad = e.D != e.Dp;
+    if (vert && !a.diag) {      // MODE_HH4 (built without the fast-accumulate variant)
+        if (FA) return launch_rgf<R, G, false>(e, a, vert, final, st);
+        if (!final) return pad ? launch_one<R, G, NT, true, true, false, false, false>(e, a, st) : launch_one<R, G, NT, false, true, false, false, false>(e, a, st);
+        return pad ? launch_one<R, G, NT, true, true, true, false, false>(e, a, st) : launch_one<R, G, NT, false, true, true, false, false>(e, a, st);
+    }
     if (vert && !final) return pad ? launch_one<R, G, NT, true, true, false, FA>(e, a, st) : launch_one<R, G, NT, false, true, false, FA>(e, a, st);
     if (vert && final) return pad ? launch_one<R, G, NT, true, true, true, FA>(e, a, st) : launch_one<R, G, NT, false, true, true, FA>(e, a, st);
     if (!vert && final) return pad ? launch_one<R, G, NT, true, false, true, false>(e, a, st) : launch_one<R, G, NT, false, false, true, false>(e, a, st);

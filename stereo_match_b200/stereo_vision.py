@@ -16,7 +16,7 @@ from ._lib import error  # noqa: F401  (re-exported)
 def parse_config_file(settings_file):
     """ini -> settings dict, defaults and key handling as disparity_calculation.py:75-128.
 
-    One key is added for this engine: `sgbm_mode` ("SGBM" or "HH", default "SGBM").  The
+    One key is added for this engine: `sgbm_mode` ("SGBM", "HH" or "HH4", default "SGBM").  The
     reference's own `mode` key is the phone orientation, not the matcher mode, and is kept
     as such.
     """
@@ -38,7 +38,7 @@ def parse_config_file(settings_file):
     return settings
 
 
-_MODES = {'SGBM': engine.STEREO_SGBM_MODE_SGBM, 'HH': engine.STEREO_SGBM_MODE_HH}
+_MODES = {'SGBM': engine.STEREO_SGBM_MODE_SGBM, 'HH': engine.STEREO_SGBM_MODE_HH, 'HH4': engine.STEREO_SGBM_MODE_HH4}
 
 
 def create_left_matcher(disparity_settings, method="SGBM"):
@@ -49,7 +49,7 @@ def create_left_matcher(disparity_settings, method="SGBM"):
         mode = disparity_settings.get('sgbm_mode', 'SGBM')
         if isinstance(mode, str):
             if mode.upper() not in _MODES:
-                raise error("sgbm_mode must be SGBM or HH, got %r" % mode)
+                raise error("sgbm_mode must be SGBM, HH or HH4, got %r" % mode)
             mode = _MODES[mode.upper()]
         return engine.StereoSGBM_create(minDisparity=disparity_settings['min_disparity'],
                                         numDisparities=disparity_settings['num_disparities'],

@@ -20,7 +20,7 @@ from stereo_match_b200.synth import synth_pair, KITTI_Q                # noqa: E
 assert cv2.__version__ == "4.13.0", cv2.__version__
 
 out = {}
-for i in (0, 1, 3, 5, 6, 7, 11, 13):
+for i in (0, 1, 3, 5, 6, 7, 11, 13, 26, 27, 30):          # 26.. : MODE_HH4
     v = SGBM_VECTORS[i]
     l, r = sgbm_pair(i, v)
     out["sgbm%d_l" % i], out["sgbm%d_r" % i] = l, r

@@ -29,6 +29,17 @@ SGBM_VECTORS = [
     (23, 50, 0, 16, 3, 100, 800, 1, 63, 10, 1, 0, 0),       # width1 = 7 < one staging chunk
     (180, 50, 0, 128, 5, 600, 2400, 1, 63, 10, 1, 0, 0),    # R = 8, S summed without per-direction saturation
     (180, 50, 0, 128, 5, 1000, 8000, 1, 63, 10, 1, 0, 0),   # R = 8, large P2: saturating accumulation
+    # MODE_HH4 (-> , <- , down, up; cv2 4.13.0 leaves the block cost of the last blockSize/2 rows at zero)
+    (150, 90, 0, 48, 5, 100, 400, 1, 63, 10, 3, 0, 0),
+    (131, 77, 4, 32, 9, 100, 1000, 1, 0, 5, 3, 50, 2),
+    (200, 120, -8, 64, 3, 72, 288, 2, 63, 0, 3, 0, 0),
+    (300, 200, 0, 96, 5, 600, 2400, 1, 63, 15, 3, 60, 2),   # 7 bands, R = 6
+    (40, 3, 0, 16, 5, 600, 2400, 1, 63, 15, 3, 0, 0),       # H smaller than the block: rows 1.. have zero cost
+    (60, 1, 0, 16, 5, 600, 2400, 1, 63, 15, 3, 0, 0),       # one row
+    (150, 90, 0, 40, 1, 50, 200, 1, 63, 15, 3, 0, 0),       # blockSize 1: no zeroed rows, padded D
+    (180, 50, 0, 128, 5, 600, 2400, 1, 63, 10, 3, 0, 0),    # R = 8 (permuted records)
+    (330, 40, 0, 272, 3, 72, 288, 1, 63, 10, 3, 0, 0),      # 32-lane kernels
+    (640, 24, 0, 528, 3, 72, 288, 1, 63, 10, 3, 0, 0),      # D > 512: per-direction kernels
 ]
 
 
