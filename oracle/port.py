@@ -58,10 +58,11 @@ def sgbm_geometry(W, **kw):
 
 
 def sgbm_compute(left, right, want_volumes=False, **kw):
-    """Returns disp (H,W) int16; with want_volumes also (C, S, raw)."""
+    """Returns disp (H,W) int16; with want_volumes also (C, S, raw).  Images: (H,W) gray or (H,W,3)."""
     left = np.ascontiguousarray(left, np.uint8)
     right = np.ascontiguousarray(right, np.uint8)
-    H, W = left.shape
+    H, W = left.shape[:2]
+    cn = 1 if left.ndim == 2 else left.shape[2]
     p = sgbm_params(**kw)
     disp = np.empty((H, W), np.int16)
     Cv = Sv = raw = None
@@ -71,11 +72,11 @@ def sgbm_compute(left, right, want_volumes=False, **kw):
         Cv = np.zeros((H, w1, p.numDisparities), np.int16)
         Sv = np.zeros_like(Cv)
         raw = np.empty((H, W), np.int16)
-    rc = lib().orc_sgbm_compute(_p(left), _p(right), H, W, C.byref(p), _p(disp), _p(Cv), _p(Sv), _p(raw))
+    rc = lib().orc_sgbm_compute_cn(_p(left), _p(right), H, W, cn, C.byref(p), _p(disp), _p(Cv), _p(Sv), _p(raw))
     if rc == -2:
         raise ValueError("oracle: cv2.error -- width - (minDisparity + numDisparities) > SADWindowSize/2")
     if rc != 0:
-        raise ValueError("oracle: unsupported SGBM mode")
+        raise ValueError("oracle: unsupported SGBM mode / channel count / tap")
     return (disp, Cv, Sv, raw) if want_volumes else disp
 
 
@@ -99,6 +100,15 @@ def sgbm_finish(S, W, **kw):
     disp = np.empty((S.shape[0], W), np.int16)
     lib().orc_sgbm_finish(_p(S), S.shape[0], int(W), C.byref(p), _p(disp))
     return disp
+
+
+def sgbm_wta(S, W, **kw):
+    """Stage tap: S volume -> raw disparity rows (before the median)."""
+    S = np.ascontiguousarray(S, np.int16)
+    p = sgbm_params(**kw)
+    raw = np.empty((S.shape[0], W), np.int16)
+    lib().orc_sgbm_wta(_p(S), S.shape[0], int(W), C.byref(p), _p(raw))
+    return raw
 
 
 def sgbm_path(Cvol, P1, P2, k):

@@ -107,34 +107,47 @@ static eff_t effective(const orc_sgbm_params* p, int W)
 /* SURVEY.md A.1 + A.2: C[y][x][d] = i16(P2 + block sum of BT cost).   */
 /* Cvol must hold H*width1*D int16.                                    */
 /* ------------------------------------------------------------------ */
-static int32_t* hsum_volume(const uint8_t* L, const uint8_t* R, int H, int W, const eff_t* e)
+/* cn = 1 (gray) or 3 (interleaved colour, any order): every colour channel contributes its own Sobel and raw
+   channel, each raw one shifted by 2 on its own (probed against cv2 4.13.0 with 3-channel input) */
+static int32_t* hsum_volume(const uint8_t* L, const uint8_t* R, int H, int W, int cn, const eff_t* e)
 {
     const int D = e->D, w1 = e->width1;
     size_t plane = (size_t)H * W;
-    uint8_t* buf = (uint8_t*)malloc(plane * 12);
-    uint8_t *g1 = buf, *r1 = buf + plane, *g2 = buf + 2 * plane, *r2 = buf + 3 * plane;
-    uint8_t *lo[4], *hi[4];
-    for (int k = 0; k < 4; k++) { lo[k] = buf + (4 + 2 * k) * plane; hi[k] = buf + (5 + 2 * k) * plane; }
-    descriptors(L, H, W, e->ftzero, g1, r1);
-    descriptors(R, H, W, e->ftzero, g2, r2);
-    uint8_t* pl[4] = { g1, r1, g2, r2 };
-    for (int k = 0; k < 4; k++)
-        for (int y = 0; y < H; y++)
-            halfpix(pl[k] + (size_t)y * W, W, lo[k] + (size_t)y * W, hi[k] + (size_t)y * W);
+    uint8_t* buf = (uint8_t*)malloc(plane * 12 * cn);
+    uint8_t* chan = (uint8_t*)malloc(plane * 2);
+    for (int c = 0; c < cn; c++) {
+        uint8_t* b = buf + plane * 12 * c;
+        uint8_t *g1 = b, *r1 = b + plane, *g2 = b + 2 * plane, *r2 = b + 3 * plane;
+        for (size_t i = 0; i < plane; i++) { chan[i] = L[i * cn + c]; chan[plane + i] = R[i * cn + c]; }
+        descriptors(chan, H, W, e->ftzero, g1, r1);
+        descriptors(chan + plane, H, W, e->ftzero, g2, r2);
+        uint8_t* pl[4] = { g1, r1, g2, r2 };
+        for (int k = 0; k < 4; k++)
+            for (int y = 0; y < H; y++)
+                halfpix(pl[k] + (size_t)y * W, W, b + (4 + 2 * k) * plane + (size_t)y * W, b + (5 + 2 * k) * plane + (size_t)y * W);
+    }
+    free(chan);
 
     /* pix[y][x][d], then horizontal sums hs[y][x][d] (clamp on cropped axis) */
     size_t rowsz = (size_t)w1 * D;
-    uint16_t* pix = (uint16_t*)malloc(rowsz * sizeof(uint16_t));
+    uint32_t* pix = (uint32_t*)malloc(rowsz * sizeof(uint32_t));
     int32_t* hs = (int32_t*)malloc((size_t)H * rowsz * sizeof(int32_t));
     for (int y = 0; y < H; y++) {
         size_t o = (size_t)y * W;
-        for (int x = 0; x < w1; x++) {
-            int xi = x + e->minX1;
-            for (int d = 0; d < D; d++) {
-                int xr = xi - (d + e->minD);
-                int cg = bt(g1[o + xi], g2[o + xr], lo[0][o + xi], hi[0][o + xi], lo[2][o + xr], hi[2][o + xr]);
-                int cr = bt(r1[o + xi], r2[o + xr], lo[1][o + xi], hi[1][o + xi], lo[3][o + xr], hi[3][o + xr]);
-                pix[(size_t)x * D + d] = (uint16_t)(cg + (cr >> 2));
+        memset(pix, 0, rowsz * sizeof(uint32_t));
+        for (int c = 0; c < cn; c++) {
+            const uint8_t* b = buf + plane * 12 * c;
+            const uint8_t *g1 = b, *r1 = b + plane, *g2 = b + 2 * plane, *r2 = b + 3 * plane;
+            const uint8_t *lo[4], *hi[4];
+            for (int k = 0; k < 4; k++) { lo[k] = b + (4 + 2 * k) * plane; hi[k] = b + (5 + 2 * k) * plane; }
+            for (int x = 0; x < w1; x++) {
+                int xi = x + e->minX1;
+                for (int d = 0; d < D; d++) {
+                    int xr = xi - (d + e->minD);
+                    int cg = bt(g1[o + xi], g2[o + xr], lo[0][o + xi], hi[0][o + xi], lo[2][o + xr], hi[2][o + xr]);
+                    int cr = bt(r1[o + xi], r2[o + xr], lo[1][o + xi], hi[1][o + xi], lo[3][o + xr], hi[3][o + xr]);
+                    pix[(size_t)x * D + d] += (uint32_t)(cg + (cr >> 2));
+                }
             }
         }
         int32_t* hrow = hs + (size_t)y * rowsz;
@@ -142,7 +155,7 @@ static int32_t* hsum_volume(const uint8_t* L, const uint8_t* R, int H, int W, co
             for (int d = 0; d < D; d++) {
                 int s = 0;
                 for (int k = -e->SW2; k <= e->SW2; k++)
-                    s += pix[(size_t)iclamp(x + k, 0, w1 - 1) * D + d];
+                    s += (int)pix[(size_t)iclamp(x + k, 0, w1 - 1) * D + d];
                 hrow[(size_t)x * D + d] = s;
             }
     }
@@ -150,10 +163,10 @@ static int32_t* hsum_volume(const uint8_t* L, const uint8_t* R, int H, int W, co
     return hs;
 }
 
-static void cost_volume(const uint8_t* L, const uint8_t* R, int H, int W,
+static void cost_volume(const uint8_t* L, const uint8_t* R, int H, int W, int cn,
                         const eff_t* e, int16_t* Cvol)
 {
-    int32_t* hs = hsum_volume(L, R, H, W, e);
+    int32_t* hs = hsum_volume(L, R, H, W, cn, e);
     size_t rowsz = (size_t)e->width1 * e->D;
     for (int y = 0; y < H; y++) {
         int16_t* crow = Cvol + (size_t)y * rowsz;
@@ -217,7 +230,8 @@ static const int DIRS[8][2] = {
 /* ------------------------------------------------------------------ */
 /* WTA + uniqueness + disp2 + sub-pixel + LR check.     */
 /* ------------------------------------------------------------------ */
-static void wta_rows(const int16_t* S, int H, int W, const eff_t* e, int16_t* disp)
+/* le != 0: MODE_SGBM_3WAY's uniqueness rule (rejects on equality too, and not at all for ratio 0) */
+static void wta_rows_ex(const int16_t* S, int H, int W, const eff_t* e, int le, int16_t* disp)
 {
     const int D = e->D, w1 = e->width1, INV = e->INVALID;
     int16_t* disp2 = (int16_t*)malloc(W * sizeof(int16_t));
@@ -230,8 +244,10 @@ static void wta_rows(const int16_t* S, int H, int W, const eff_t* e, int16_t* di
             int best = 0, minS = Sp[0];
             for (int d = 1; d < D; d++) if (Sp[d] < minS) { minS = Sp[d]; best = d; }
             int d;
-            for (d = 0; d < D; d++)
-                if (Sp[d] * (100 - e->uniq) < minS * 100 && abs(best - d) > 1) break;
+            for (d = 0; d < D; d++) {
+                int lhs = Sp[d] * (100 - e->uniq), rhs = minS * 100;
+                if ((le ? (e->uniq > 0 && lhs <= rhs) : lhs < rhs) && abs(best - d) > 1) break;
+            }
             if (d < D) continue;
             int x2 = x + e->minX1 - best - e->minD;
             if (disp2cost[x2] > minS) { disp2cost[x2] = minS; disp2[x2] = (int16_t)(best + e->minD); }
@@ -300,53 +316,116 @@ ORC_API void orc_filter_speckles(int16_t* img, int H, int W, int newVal, int max
     free(count); free(parent);
 }
 
+static void wta_rows(const int16_t* S, int H, int W, const eff_t* e, int16_t* disp) { wta_rows_ex(S, H, W, e, 0, disp); }
+
 /* ------------------------------------------------------------------ */
-/* StereoSGBM.compute (single-channel).  Optional outputs (may be NULL) */
-/*   Cout, Sout : H*width1*D int16 ; raw : H*W int16 (before median)   */
+/* MODE_SGBM_3WAY of cv2 4.13.0 (probed, tests/test_oracle_vs_cv2.py): the image is cut into 4 fixed stripes   */
+/* of sz = ceil(H/4) rows; stripe st starts ov = blockSize/2 + 1 + ceil(0.1*sz) rows early (clamped to the     */
+/* image), restarts the vertical block sum and the downward path there, sums the paths -> , down, <- and runs */
+/* the winner-take-all with the `<=` uniqueness rule.  Each stripe writes row y at buffer row (st ? 0 : ov) +  */
+/* y - s0 of a buffer preset to INVALID, and output row i is buffer row ov + i % sz of stripe i / sz (identity */
+/* unless the early start was clamped: then rows shift, as in cv2).                                             */
+/* hs: horizontal sums [H][width1][D]; raw: H*W before the median.                                              */
+/* ------------------------------------------------------------------ */
+static void sgbm_3way(const int32_t* hs, int H, int W, const eff_t* e, int16_t* raw)
+{
+    const int sz = (H + 3) / 4, ov = e->SH2 + 1 + (sz + 9) / 10;       /* ceil(0.1*sz) */
+    const size_t rowsz = (size_t)e->width1 * e->D;
+    int16_t* buf = (int16_t*)malloc((size_t)4 * (sz + ov) * W * sizeof(int16_t));
+    for (size_t i = 0; i < (size_t)4 * (sz + ov) * W; i++) buf[i] = (int16_t)e->INVALID;
+    for (int st = 0; st < 4; st++) {
+        int s0 = imax(imin(st * sz - ov, H), 0), s1 = imin((st + 1) * sz, H), hst = s1 - s0;
+        if (hst <= 0) continue;
+        int16_t* Cv = (int16_t*)malloc((size_t)hst * rowsz * sizeof(int16_t));
+        int32_t* Ssum = (int32_t*)calloc((size_t)hst * rowsz, sizeof(int32_t));
+        for (int y = s0; y < s1; y++)
+            for (size_t i = 0; i < rowsz; i++) {
+                int v = e->P2;
+                for (int k = -e->SH2; k <= e->SH2; k++) v += hs[(size_t)iclamp(y + k, s0, H - 1) * rowsz + i];
+                Cv[(size_t)(y - s0) * rowsz + i] = wrap16(v);
+            }
+        aggregate_dir(Cv, hst, e->width1, e->D, e->P1, e->P2, 1, 0, Ssum, NULL);
+        aggregate_dir(Cv, hst, e->width1, e->D, e->P1, e->P2, 0, 1, Ssum, NULL);
+        aggregate_dir(Cv, hst, e->width1, e->D, e->P1, e->P2, -1, 0, Ssum, NULL);
+        int16_t* S = Cv;                                                /* reuse */
+        for (size_t i = 0; i < (size_t)hst * rowsz; i++) S[i] = sat16(Ssum[i]);
+        int16_t* r = (int16_t*)malloc((size_t)hst * W * sizeof(int16_t));
+        wta_rows_ex(S, hst, W, e, 1, r);
+        for (int y = s0; y < s1; y++) {
+            int idx = (st == 0 ? ov : 0) + y - s0;
+            if (idx < sz + ov) memcpy(buf + ((size_t)st * (sz + ov) + idx) * W, r + (size_t)(y - s0) * W, W * sizeof(int16_t));
+        }
+        free(r); free(Ssum); free(Cv);
+    }
+    for (int i = 0; i < H; i++)
+        memcpy(raw + (size_t)i * W, buf + ((size_t)(i / sz) * (sz + ov) + ov + i % sz) * W, W * sizeof(int16_t));
+    free(buf);
+}
+
+/* ------------------------------------------------------------------ */
+/* StereoSGBM.compute, cn = 1 or 3 interleaved channels.  Optional outputs (may be NULL) */
+/*   Cout, Sout : H*width1*D int16 (not for MODE_SGBM_3WAY) ; raw : H*W int16 (before median)   */
 /* returns 0, -1 for unsupported mode, -2 where cv2 raises cv2.error.   */
 /* ------------------------------------------------------------------ */
-ORC_API int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, int W,
-                             const orc_sgbm_params* p, int16_t* disp,
-                             int16_t* Cout, int16_t* Sout, int16_t* raw)
+ORC_API int orc_sgbm_compute_cn(const uint8_t* left, const uint8_t* right, int H, int W, int cn,
+                                const orc_sgbm_params* p, int16_t* disp,
+                                int16_t* Cout, int16_t* Sout, int16_t* raw)
 {
     /* direction sets (indices into DIRS): MODE_SGBM 5 paths, MODE_HH 8, MODE_HH4 the two horizontal and the
        two vertical ones (probed against cv2 4.13.0, tests/test_oracle_vs_cv2.py) */
     unsigned dirmask;
     if (p->mode == 0) dirmask = 0x1f;
     else if (p->mode == 1) dirmask = 0xff;
+    else if (p->mode == 2) dirmask = 0;
     else if (p->mode == 3) dirmask = 0x55;
     else return -1;
+    if (cn != 1 && cn != 3) return -1;
     eff_t e = effective(p, W);
     size_t n = (size_t)H * W;
     /* cv2 4.13.0 (stereosgbm.cpp:511) raises cv2.error unless
        width - (minDisparity + numDisparities) > SADWindowSize/2 */
     if (!(W - e.maxD > e.SW2)) return -2;
     if (e.width1 <= 0) { for (size_t i = 0; i < n; i++) disp[i] = (int16_t)e.INVALID; return 0; }
-    size_t vol = (size_t)H * e.width1 * e.D;
-    int16_t* Cvol = (int16_t*)malloc(vol * sizeof(int16_t));
-    int32_t* Ssum = (int32_t*)calloc(vol, sizeof(int32_t));
-    cost_volume(left, right, H, W, &e, Cvol);
-    if (p->mode == 3) {
-        /* cv2 4.13.0 MODE_HH4: the rows whose vertical window reaches below the image (y > 0, y + SH2 >= H) are
-           never filled, C stays at its initial value P2 (found by probing: blockSize 1 matches the plain
-           4-direction sum, every larger block only with this rule) */
-        for (int y = imax(1, H - e.SH2); y < H; y++)
-            for (size_t i = 0; i < (size_t)e.width1 * e.D; i++) Cvol[(size_t)y * e.width1 * e.D + i] = wrap16(e.P2);
-    }
-    for (int k = 0; k < 8; k++)
-        if (dirmask >> k & 1) aggregate_dir(Cvol, H, e.width1, e.D, e.P1, e.P2, DIRS[k][0], DIRS[k][1], Ssum, NULL);
-    int16_t* S = (int16_t*)malloc(vol * sizeof(int16_t));
-    for (size_t i = 0; i < vol; i++) S[i] = sat16(Ssum[i]);
     int16_t* tmp = (int16_t*)malloc(n * sizeof(int16_t));
-    wta_rows(S, H, W, &e, tmp);
+    if (p->mode == 2) {
+        if (Cout || Sout) { free(tmp); return -1; }
+        int32_t* hs = hsum_volume(left, right, H, W, cn, &e);
+        sgbm_3way(hs, H, W, &e, tmp);
+        free(hs);
+    } else {
+        size_t vol = (size_t)H * e.width1 * e.D;
+        int16_t* Cvol = (int16_t*)malloc(vol * sizeof(int16_t));
+        int32_t* Ssum = (int32_t*)calloc(vol, sizeof(int32_t));
+        cost_volume(left, right, H, W, cn, &e, Cvol);
+        if (p->mode == 3) {
+            /* cv2 4.13.0 MODE_HH4: the rows whose vertical window reaches below the image (y > 0, y + SH2 >= H) are
+               never filled, C stays at its initial value P2 (found by probing: blockSize 1 matches the plain
+               4-direction sum, every larger block only with this rule) */
+            for (int y = imax(1, H - e.SH2); y < H; y++)
+                for (size_t i = 0; i < (size_t)e.width1 * e.D; i++) Cvol[(size_t)y * e.width1 * e.D + i] = wrap16(e.P2);
+        }
+        for (int k = 0; k < 8; k++)
+            if (dirmask >> k & 1) aggregate_dir(Cvol, H, e.width1, e.D, e.P1, e.P2, DIRS[k][0], DIRS[k][1], Ssum, NULL);
+        int16_t* S = (int16_t*)malloc(vol * sizeof(int16_t));
+        for (size_t i = 0; i < vol; i++) S[i] = sat16(Ssum[i]);
+        wta_rows(S, H, W, &e, tmp);
+        if (Cout) memcpy(Cout, Cvol, vol * sizeof(int16_t));
+        if (Sout) memcpy(Sout, S, vol * sizeof(int16_t));
+        free(S); free(Ssum); free(Cvol);
+    }
     if (raw) memcpy(raw, tmp, n * sizeof(int16_t));
     orc_median3_i16(tmp, H, W, disp);
     if (p->speckleWindowSize > 0)
         orc_filter_speckles(disp, H, W, e.INVALID, p->speckleWindowSize, 16 * p->speckleRange);
-    if (Cout) memcpy(Cout, Cvol, vol * sizeof(int16_t));
-    if (Sout) memcpy(Sout, S, vol * sizeof(int16_t));
-    free(tmp); free(S); free(Ssum); free(Cvol);
+    free(tmp);
     return 0;
+}
+
+ORC_API int orc_sgbm_compute(const uint8_t* left, const uint8_t* right, int H, int W,
+                             const orc_sgbm_params* p, int16_t* disp,
+                             int16_t* Cout, int16_t* Sout, int16_t* raw)
+{
+    return orc_sgbm_compute_cn(left, right, H, W, 1, p, disp, Cout, Sout, raw);
 }
 
 /* stage taps for probing cv2 variants: horizontal window sums hs[H][width1][D] (int32, A.2) ... */
@@ -354,7 +433,7 @@ ORC_API int orc_sgbm_hsum(const uint8_t* left, const uint8_t* right, int H, int 
 {
     eff_t e = effective(p, W);
     if (e.width1 <= 0) return -1;
-    int32_t* hs = hsum_volume(left, right, H, W, &e);
+    int32_t* hs = hsum_volume(left, right, H, W, 1, &e);
     memcpy(out, hs, (size_t)H * e.width1 * e.D * sizeof(int32_t));
     free(hs);
     return 0;
@@ -371,6 +450,14 @@ ORC_API int orc_sgbm_finish(const int16_t* S, int H, int W, const orc_sgbm_param
     if (p->speckleWindowSize > 0)
         orc_filter_speckles(disp, H, W, e.INVALID, p->speckleWindowSize, 16 * p->speckleRange);
     free(tmp);
+    return 0;
+}
+
+/* ... or only A.3 (winner-take-all, uniqueness, sub-pixel, LR check), before the median */
+ORC_API int orc_sgbm_wta(const int16_t* S, int H, int W, const orc_sgbm_params* p, int16_t* raw)
+{
+    eff_t e = effective(p, W);
+    wta_rows(S, H, W, &e, raw);
     return 0;
 }
 
