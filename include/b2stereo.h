@@ -58,7 +58,7 @@ extern "C" {
 /* cv2.STEREO_SGBM_MODE_* */
 #define B2S_MODE_SGBM 0
 #define B2S_MODE_HH 1
-#define B2S_MODE_SGBM_3WAY 2 /* unsupported */
+#define B2S_MODE_SGBM_3WAY 2 /* 3 paths (-> , down, <-) over cv2's four fixed image stripes */
 #define B2S_MODE_HH4 3       /* 4 paths: -> , <- , down, up (with cv2 4.13.0's bottom-row rule) */
 
 /* matcher parameters exactly as cv2.StereoSGBM_create receives them (raw, before
@@ -97,7 +97,7 @@ typedef struct b2s_sgbm_geometry {
     int32_t Dp;                   /* padded disparity stride of the cost volumes */
     int32_t invalid;              /* (minDisparity-1)*16 */
     int32_t P1, P2, ftzero, uniquenessRatio, disp12MaxDiff; /* effective values */
-    int32_t ndirs;                /* 5 (MODE_SGBM), 8 (MODE_HH) or 4 (MODE_HH4) */
+    int32_t ndirs;                /* 5 (MODE_SGBM), 8 (MODE_HH), 4 (MODE_HH4) or 3 (MODE_SGBM_3WAY) */
     int32_t R, G;                 /* Dp = 2*R*G: G lanes per pixel, R packed registers per lane */
     int32_t swizzled;             /* 1: cell d of a [Dp] record sits at ((o % (R/4))*G + o/(R/4))*8 + d%8, o = d/8 */
 } b2s_sgbm_geometry;
@@ -116,6 +116,10 @@ B2S_API size_t b2s_sgbm_workspace_bytes(b2s_handle h, int H, int W, int batch);
 /* left/right: [batch][H][W] uint8 ; disp: [batch][H][W] int16 (Q4 fixed point) */
 B2S_API int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t* right,
                      int H, int W, int batch, int16_t* disp, void* stream);
+/* same with cn = 1 or 3 interleaved channels per pixel ([batch][H][W][cn]): cv2.StereoSGBM.compute on colour images
+   (reference: try_try.py:69-81) sums the matching cost of the three channels */
+B2S_API int b2s_sgbm_compute_cn(b2s_handle h, const uint8_t* left, const uint8_t* right,
+                     int H, int W, int cn, int batch, int16_t* disp, void* stream);
 /* stage taps for parity tests: copies the last compute's volumes (device to device, on
    `stream`) into caller buffers of `elems` uint16 each (either may be NULL); layout
    [batch][H][width1][Dp] (cell order inside a record: see b2s_sgbm_geometry.swizzled).  cost = raw block cost (cv2's C minus P2, padded cells 0);

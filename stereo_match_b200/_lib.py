@@ -47,6 +47,7 @@ PROTOTYPES = {
     "b2s_sgbm_get_geometry": (_i, [_vp, _i, C.POINTER(SgbmGeometry)]),
     "b2s_sgbm_workspace_bytes": (_sz, [_vp, _i, _i, _i]),
     "b2s_sgbm_compute": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
+    "b2s_sgbm_compute_cn": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "b2s_sgbm_keep_volumes": (_i, [_vp, _i]),
     "b2s_sgbm_debug_volumes": (_i, [_vp, _vp, _vp, _sz, _vp]),
     "b2s_sgbm_overflow_flag": (_i, [_vp, C.POINTER(_i)]),

@@ -59,9 +59,9 @@ static size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, SgbmEff& e)
 {
     if (p.numDisparities <= 0) { b2s_set_error("StereoSGBM: numDisparities must be positive"); return B2S_E_INVALID; }
-    if (p.mode != B2S_MODE_SGBM && p.mode != B2S_MODE_HH && p.mode != B2S_MODE_HH4) {
-        b2s_set_error("StereoSGBM: mode %d (MODE_SGBM_3WAY) is not supported by this engine", p.mode);
-        return B2S_E_UNSUPPORTED;
+    if (p.mode < B2S_MODE_SGBM || p.mode > B2S_MODE_HH4) {
+        b2s_set_error("StereoSGBM: unknown mode %d", p.mode);
+        return B2S_E_INVALID;
     }
     e.H = H; e.W = W; e.batch = batch;
     e.minD = p.minDisparity; e.D = p.numDisparities;
@@ -78,7 +78,8 @@ static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, Sgb
     e.maxX1 = W + (e.minD < 0 ? e.minD : 0);
     e.width1 = e.maxX1 - e.minX1;
     e.invalid = (e.minD - 1) * 16;
-    e.ndirs = p.mode == B2S_MODE_HH ? 8 : (p.mode == B2S_MODE_HH4 ? 4 : 5);
+    e.ndirs = p.mode == B2S_MODE_HH ? 8 : (p.mode == B2S_MODE_HH4 ? 4 : (p.mode == B2S_MODE_SGBM_3WAY ? 3 : 5));
+    e.cn = 1; e.Hsrc = H; e.nst = 1; e.sz = e.ov = 0; e.uqle = 0;
     // cv2 4.13.0 stereosgbm.cpp:511 raises cv2.error on this condition
     if (!(W - maxD > e.SW2)) {
         b2s_set_error("StereoSGBM: Your input images are too small for your window size and max disparity "
@@ -103,25 +104,47 @@ static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, Sgb
     return B2S_OK;
 }
 
-struct SgbmLayout { size_t descL, descR, cost, S, Sdbg, raw, key, rec, edge, labels, counts, total; };
+// The geometry of the cost / S volumes: the image itself, or, for MODE_SGBM_3WAY, cv2's four fixed stripes as
+// independent "stripe images" (batch * 4 of them, each stripe_sz + stripe_overlap rows; SgbmEff).
+static SgbmEff volume_geometry(const SgbmEff& e, int cn)
+{
+    SgbmEff v = e;
+    v.cn = cn;
+    if (e.ndirs == 3) {
+        v.nst = 4;
+        v.sz = (e.H + 3) / 4;
+        v.ov = e.SW2 + 1 + (v.sz + 9) / 10;                 // SADWindowSize/2 + 1 + ceil(0.1 * stripe_sz)
+        v.H = v.sz + v.ov < e.H ? v.sz + v.ov : e.H;
+        v.batch = e.batch * 4;
+        v.uqle = e.uniq > 0 ? 1 : 0;
+    }
+    return v;
+}
+
+struct SgbmLayout { size_t planar, descL, descR, cost, S, Sdbg, raw, rawv, key, rec, edge, labels, counts, total; };
 
 static bool uses_wave(const SgbmEff& e) { return e.R <= 8; }
 
-static SgbmLayout sgbm_layout(const SgbmEff& e, bool speckle, bool keep_volumes)
+// e: the images (batch pairs of H rows); v: volume_geometry(e, cn)
+static SgbmLayout sgbm_layout(const SgbmEff& e, const SgbmEff& v, bool speckle, bool keep_volumes)
 {
     SgbmLayout l;
-    const size_t npix = (size_t)e.batch * e.H * e.W;
-    const size_t vol = e.width1 > 0 ? (size_t)e.batch * e.H * e.width1 * e.Dp * sizeof(uint16_t) : 0;
+    const size_t npix = (size_t)e.batch * e.H * e.W, npixv = (size_t)v.batch * v.H * v.W;
+    const size_t vol = v.width1 > 0 ? (size_t)v.batch * v.H * v.width1 * v.Dp * sizeof(uint16_t) : 0;
+    SgbmEff ed = e;
+    ed.batch = e.batch * v.cn;                               // one gray image per colour channel
     size_t o = 0;
-    l.descL = o; o += align_up(npix * sizeof(uint2));
-    l.descR = o; o += align_up(b2s_desc_right_bytes(e));
+    l.planar = o; o += v.cn > 1 ? 2 * align_up(npix * v.cn) : 0;
+    l.descL = o; o += align_up(npix * v.cn * sizeof(uint2));
+    l.descR = o; o += align_up(b2s_desc_right_bytes(ed));
     l.cost = o; o += align_up(vol);
     l.S = o; o += align_up(vol);
     l.Sdbg = o; o += (keep_volumes && uses_wave(e)) ? align_up(vol) : 0;
     l.raw = o; o += align_up(npix * sizeof(int16_t));
-    l.key = o; o += align_up(npix * sizeof(uint32_t));
-    l.rec = o; o += uses_wave(e) ? align_up(npix * sizeof(uint2)) : 0;
-    l.edge = o; o += (uses_wave(e) && e.width1 > 0) ? align_up(b2s_wave_edge_bytes(e)) : 0;
+    l.rawv = o; o += v.nst > 1 ? align_up(npixv * sizeof(int16_t)) : 0;
+    l.key = o; o += align_up(npixv * sizeof(uint32_t));
+    l.rec = o; o += uses_wave(e) ? align_up(npixv * sizeof(uint2)) : 0;
+    l.edge = o; o += (uses_wave(e) && v.width1 > 0) ? align_up(b2s_wave_edge_bytes(v)) : 0;
     l.labels = o; o += speckle ? align_up(npix * sizeof(int32_t)) : 0;
     l.counts = o; o += speckle ? align_up(npix * sizeof(int32_t)) : 0;
     l.total = o;
@@ -192,7 +215,7 @@ extern "C" size_t b2s_sgbm_workspace_bytes(b2s_handle h, int H, int W, int batch
     if (!h || h->kind != 0) return 0;
     SgbmEff e;
     if (sgbm_effective(h->sp, H, W, batch, e)) return 0;
-    return sgbm_layout(e, h->sp.speckleWindowSize > 0, h->keep_volumes).total;
+    return sgbm_layout(e, volume_geometry(e, 1), h->sp.speckleWindowSize > 0, h->keep_volumes).total;
 }
 
 __global__ void k_fill16(int16_t* p, size_t n, int16_t v)
@@ -201,15 +224,32 @@ __global__ void k_fill16(int16_t* p, size_t n, int16_t v)
     if (i < n) p[i] = v;
 }
 
-extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t* right, int H, int W, int batch,
-                                int16_t* disp, void* stream)
+// interleaved colour images [n][3] -> three gray planes per image [n / (H*W)][3][H*W]
+__global__ void k_split3(const uint8_t* __restrict__ src, size_t npix, size_t plane, uint8_t* __restrict__ dst)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    const size_t b = i / plane, o = i - b * plane;
+    const uint8_t* p = src + 3 * i;
+    uint8_t* d = dst + b * 3 * plane + o;
+    d[0] = p[0]; d[plane] = p[1]; d[2 * plane] = p[2];
+}
+
+extern "C" int b2s_sgbm_compute_cn(b2s_handle h, const uint8_t* left, const uint8_t* right, int H, int W, int cn, int batch,
+                                   int16_t* disp, void* stream)
 {
     if (!h || h->kind != 0) { b2s_set_error("sgbm_compute: bad handle"); return B2S_E_INVALID; }
+    if (cn != 1 && cn != 3) { b2s_set_error("StereoSGBM: images must have 1 or 3 channels (got %d)", cn); return B2S_E_INVALID; }
     int rc = check_images("StereoSGBM", left, right, disp, H, W, batch);
     if (rc) return rc;
     SgbmEff e;
     rc = sgbm_effective(h->sp, H, W, batch, e);
     if (rc) return rc;
+    const SgbmEff v = volume_geometry(e, cn);          // the cost / S volumes (stripe images for MODE_SGBM_3WAY)
+    if ((long long)batch * cn * H * W >= (1ll << 31) || (long long)v.batch * v.H * W >= (1ll << 31)) {
+        b2s_set_error("StereoSGBM: batch*channels*H*W must be < 2^31");
+        return B2S_E_UNSUPPORTED;
+    }
     cudaStream_t st = (cudaStream_t)stream;
     const size_t npix = (size_t)batch * H * W;
     h->last_cost = h->last_S = nullptr;
@@ -219,7 +259,7 @@ extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t
         return B2S_OK;
     }
     const bool speckle = h->sp.speckleWindowSize > 0;
-    const SgbmLayout l = sgbm_layout(e, speckle, h->keep_volumes);
+    const SgbmLayout l = sgbm_layout(e, v, speckle, h->keep_volumes);
     rc = ensure_ws(h, l.total, st);
     if (rc) return rc;
     char* ws = (char*)h->ws;
@@ -228,20 +268,32 @@ extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t
     uint16_t* cost = (uint16_t*)(ws + l.cost);
     uint16_t* S = (uint16_t*)(ws + l.S);
     int16_t* raw = (int16_t*)(ws + l.raw);
+    int16_t* rawv = v.nst > 1 ? (int16_t*)(ws + l.rawv) : raw;     // per-stripe rows before they are put together
     uint32_t* key = (uint32_t*)(ws + l.key);
 
     B2S_CUDA_CHECK(cudaMemsetAsync(h->flag, 0, sizeof(int), st));
     h->ev_valid = false;
 #define B2S_MARK(i) do { if (h->timing) B2S_CUDA_CHECK(cudaEventRecord(h->ev[i], st)); } while (0)
     B2S_MARK(0);
-    if ((rc = b2s_launch_descriptors(left, e, descL, st))) return rc;
-    if ((rc = b2s_launch_descriptors_right(right, e, descR, st))) return rc;
+    SgbmEff ed = e;                              // descriptors: every colour channel is a gray image of its own
+    ed.batch = batch * cn;
+    if (cn == 3) {
+        uint8_t* pl = (uint8_t*)(ws + l.planar);
+        uint8_t* pr = pl + align_up(npix * 3);
+        k_split3<<<b2s_cdiv((long long)npix, 256), 256, 0, st>>>(left, npix, (size_t)H * W, pl);
+        B2S_LAUNCH_CHECK();
+        k_split3<<<b2s_cdiv((long long)npix, 256), 256, 0, st>>>(right, npix, (size_t)H * W, pr);
+        B2S_LAUNCH_CHECK();
+        left = pl; right = pr;
+    }
+    if ((rc = b2s_launch_descriptors(left, ed, descL, st))) return rc;
+    if ((rc = b2s_launch_descriptors_right(right, ed, descR, st))) return rc;
     B2S_MARK(1);
-    if ((rc = b2s_launch_cost(descL, descR, e, cost, h->flag, st))) return rc;
+    if ((rc = b2s_launch_cost(descL, descR, v, cost, h->flag, st))) return rc;
     if (e.ndirs == 4 && e.SW2 > 0 && H > 1) {
         // cv2 4.13.0's MODE_HH4 never fills the block cost of the rows whose window reaches below the image (its
         // copy of the row loop has no branch for them): C stays at P2 there, i.e. raw cost 0 (probed against cv2,
-        // tests/test_oracle_vs_cv2.py::test_hh4).  Rows y >= max(1, H - SW2) of every pair:
+        // tests/test_oracle_vs_cv2.py).  Rows y >= max(1, H - SW2) of every pair:
         const int y0 = H - e.SW2 > 1 ? H - e.SW2 : 1;
         const size_t rowb = (size_t)e.width1 * e.Dp * sizeof(uint16_t);
         const size_t n16 = (size_t)(H - y0) * rowb / 16;           // Dp is a multiple of 32 cells: whole uint4s
@@ -254,15 +306,19 @@ extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t
     if (uses_wave(e)) {
         // two fused sweeps; the second one ends in the winner-take-all (stage 2 = both sweeps)
         Sfull = h->keep_volumes ? (uint16_t*)(ws + l.Sdbg) : nullptr;
-        if ((rc = b2s_launch_wave(e, cost, S, Sfull, ws + l.edge, (uint2*)(ws + l.rec), key, st))) return rc;
+        if ((rc = b2s_launch_wave(v, cost, S, Sfull, ws + l.edge, (uint2*)(ws + l.rec), key, st))) return rc;
         B2S_MARK(3);
-        if ((rc = b2s_launch_finish_rec(e, (const uint2*)(ws + l.rec), key, raw, st))) return rc;
+        if ((rc = b2s_launch_finish_rec(v, (const uint2*)(ws + l.rec), key, rawv, st))) return rc;
     } else {
-        for (int k = 0; k < (e.ndirs == 4 ? 8 : e.ndirs); k += (e.ndirs == 4 ? 2 : 1))    // MODE_HH4: -> , down, <- , up
-            if ((rc = b2s_launch_aggregate(cost, S, e, k, k == 0, st))) return rc;
+        // one launch per direction (table of b2s_dir): MODE_SGBM 0-4, MODE_HH 0-7, MODE_HH4 -> , down, <- , up,
+        // MODE_SGBM_3WAY -> , down, <-
+        const int last = e.ndirs == 4 ? 6 : (e.ndirs == 3 ? 4 : e.ndirs - 1), stepk = (e.ndirs == 4 || e.ndirs == 3) ? 2 : 1;
+        for (int k = 0; k <= last; k += stepk)
+            if ((rc = b2s_launch_aggregate(cost, S, v, k, k == 0, st))) return rc;
         B2S_MARK(3);
-        if ((rc = b2s_launch_wta(S, e, raw, key, st))) return rc;
+        if ((rc = b2s_launch_wta(S, v, rawv, key, st))) return rc;
     }
+    if (v.nst > 1 && (rc = b2s_launch_assemble_stripes(v, rawv, raw, st))) return rc;
     B2S_MARK(4);
     if ((rc = b2s_launch_median3(raw, H, W, batch, disp, st))) return rc;
     B2S_MARK(5);
@@ -275,8 +331,14 @@ extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t
 #undef B2S_MARK
     h->ev_valid = h->timing;
     h->last_cost = cost; h->last_S = Sfull; h->last_stream = st;
-    h->last_elems = (size_t)batch * H * e.width1 * e.Dp;
+    h->last_elems = (size_t)v.batch * v.H * v.width1 * v.Dp;
     return B2S_OK;
+}
+
+extern "C" int b2s_sgbm_compute(b2s_handle h, const uint8_t* left, const uint8_t* right, int H, int W, int batch,
+                                int16_t* disp, void* stream)
+{
+    return b2s_sgbm_compute_cn(h, left, right, H, W, 1, batch, disp, stream);
 }
 
 extern "C" int b2s_sgbm_debug_volumes(b2s_handle h, uint16_t* cost_out, uint16_t* S_out, size_t elems, void* stream)

@@ -18,7 +18,23 @@ struct SgbmEff {
     int G;                    // lanes per pixel in the aggregation/WTA kernels (8, 16 or 32)
     int R;                    // packed u16x2 registers per lane: Dp = 2*R*G
     int swz;                  // 1: [Dp] records of the cost/S volumes use the permuted cell order of b2s_cell_pos
+    // --- where the cost kernels read their descriptors (defaults: cn = 1, Hsrc = H, nst = 1) ---
+    int cn;                   // colour channels of the input (1 or 3): the descriptor arrays hold (pairs * cn) gray
+                              // images, channel c of pair p at index p * cn + c; the BT costs of the channels add up
+    int Hsrc;                 // rows of the source images
+    int nst, sz, ov;          // MODE_SGBM_3WAY: the volumes hold batch = pairs * nst "stripe images" of H rows; stripe
+                              // st of a pair starts at source row b2s_stripe_start() and clamps its block sum there
+    int uqle;                 // 1: the uniqueness test rejects on equality as well (MODE_SGBM_3WAY)
 };
+
+// first source row of stripe st (cv2 4.13.0 computeDisparity3WAY: range.start * stripe_sz - stripe_overlap, clamped)
+__host__ __device__ inline int b2s_stripe_start(const SgbmEff& e, int st)
+{
+    if (e.nst == 1) return 0;
+    int s = st * e.sz - e.ov;
+    s = s < e.Hsrc ? s : e.Hsrc;
+    return s > 0 ? s : 0;
+}
 
 // aggregation direction table (step from predecessor to pixel), same order as the
 // oracle's DIRS: -> , down-right, down, down-left, <- , up-right, up, up-left
@@ -73,6 +89,8 @@ int b2s_launch_aggregate(const uint16_t* cost, uint16_t* S, const SgbmEff& e, in
 int b2s_launch_wta(const uint16_t* S, const SgbmEff& e, int16_t* disp_raw, uint32_t* disp2key,
                    cudaStream_t st);
 int b2s_launch_finish_rec(const SgbmEff& e, const uint2* rec, const uint32_t* disp2key, int16_t* disp_raw, cudaStream_t st);
+// MODE_SGBM_3WAY: rows of the stripe images (v = volume geometry) -> rows of the image, cv2's buffer offsets included
+int b2s_launch_assemble_stripes(const SgbmEff& v, const int16_t* raw_stripes, int16_t* raw, cudaStream_t st);
 int b2s_launch_median3(const int16_t* src, int H, int W, int batch, int16_t* dst, cudaStream_t st);
 int b2s_launch_speckles(int16_t* img, int H, int W, int batch, int newVal, int maxSize, int maxDiff,
                         int32_t* labels, int32_t* counts, cudaStream_t st);

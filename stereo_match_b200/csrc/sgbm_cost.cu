@@ -198,8 +198,12 @@ k_cost(const uint2* __restrict__ descL, const uint2* __restrict__ descR, SgbmEff
     const int yb = blockIdx.y * TR;
     const size_t b = blockIdx.z;
     const int yend = min(yb + TR, e.H);
-    const uint2* dL = descL + b * (size_t)e.H * e.W;
-    const uint2* dR = descR + b * (size_t)e.H * e.W;
+    // source images of this (stripe) image: channel c of pair bsrc, rows from s0 on
+    const size_t bsrc = b / e.nst;
+    const int s0 = b2s_stripe_start(e, (int)(b % e.nst));
+    const size_t plane = (size_t)e.Hsrc * e.W;
+    const uint2* dL = descL + bsrc * e.cn * plane;
+    const uint2* dR = descR + bsrc * e.cn * plane;
     uint16_t* out = cost + b * (size_t)e.H * e.width1 * e.Dp;
     const int nitems = TW * DP2;
 
@@ -211,7 +215,7 @@ k_cost(const uint2* __restrict__ descL, const uint2* __restrict__ descR, SgbmEff
 
     int slot = 0;
     for (int yv = yb - e.SW2; yv < yend + e.SW2; yv++) {
-        const int yr = min(max(yv, 0), e.H - 1);
+        const int yr = min(s0 + max(yv, 0), e.Hsrc - 1);     // clamped at the stripe's first row and at the image's last
         __syncthreads();                           // previous row's pix fully consumed
         for (int it = threadIdx.x; it < PW * DP2; it += COST_NT) {
             int xh = it / DP2, dp = it - xh * DP2;
@@ -220,15 +224,17 @@ k_cost(const uint2* __restrict__ descL, const uint2* __restrict__ descR, SgbmEff
             int d0 = 2 * dp;
             uint32_t pc = 0;
             if (d0 < e.D) {
-                const uint2* rowL = dL + (size_t)yr * e.W;
-                const uint2* rowR = dR + (size_t)yr * e.W;
-                uint2 wl = __ldg(rowL + xi);
-                int xr = xi - d0 - e.minD;
-                uint2 wa = __ldg(rowR + xr);
-                uint2 wb = (d0 + 1 < e.D) ? __ldg(rowR + xr - 1) : wa;
-                uint32_t cg = bt_pair(wl.x, wa.x, wb.x);
-                uint32_t cr = bt_pair(wl.y, wa.y, wb.y);
-                pc = cg + ((cr >> 2) & 0x003f003fu);
+                for (int c = 0; c < e.cn; c++) {
+                    const uint2* rowL = dL + c * plane + (size_t)yr * e.W;
+                    const uint2* rowR = dR + c * plane + (size_t)yr * e.W;
+                    uint2 wl = __ldg(rowL + xi);
+                    int xr = xi - d0 - e.minD;
+                    uint2 wa = __ldg(rowR + xr);
+                    uint2 wb = (d0 + 1 < e.D) ? __ldg(rowR + xr - 1) : wa;
+                    uint32_t cg = bt_pair(wl.x, wa.x, wb.x);
+                    uint32_t cr = bt_pair(wl.y, wa.y, wb.y);
+                    pc += cg + ((cr >> 2) & 0x003f003fu);
+                }
             }
             pix[it] = pc;
         }
@@ -359,7 +365,9 @@ template <int MAXW> struct CostPlan {
 // P8: the records are the wavefront kernel's interleaved ones (b2s_cell_pos, swz): a packed pair is (d, d + 8), warp
 // o owns the cells {16q + 4s + w, 16q + 4s + w + 8 : w < 4} with q = o / 2, s = o % 2, and the staged planes hold one
 // u32 (value(x), value(x - 8)) per element instead of two shifted u16 copies.
-template <int BS, int MAXW, bool PAD, bool P8>
+// CN colour channels: the ring carries one stage per (row, channel), the BT costs of the channels add up before the
+// box sum.  Stripe images (MODE_SGBM_3WAY, e.nst > 1) read their rows from the pair's source image, see SgbmEff.
+template <int BS, int MAXW, bool PAD, bool P8, int CN>
 __global__ void __launch_bounds__(32 * MAXW, (MAXW == 16 && BS <= 7) ? 2 : 1)
 k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap tmap, SgbmEff e, int TR,
             uint16_t* __restrict__ cost, int* __restrict__ overflow_flag)
@@ -395,23 +403,29 @@ k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap
         const int dlo = P8 ? dfirst + w : dfirst + 2 * w, dhi = P8 ? dlo + 8 : dlo + 1;
         pmask[w] = (dlo < e.D ? 0xffffu : 0u) | (dhi < e.D ? 0xffff0000u : 0u);
     }
-    const unsigned bimg = b * (unsigned)(e.H * e.W);                          // batch*H*W < 2^31 is checked on the host
-    auto left_word = [&](int r) {
-        const int yr = min(max(yb - SW2 + r, 0), e.H - 1);
-        return __ldg(descL + (bimg + (unsigned)(yr * e.W + xiA)));
+    const unsigned bsrc = b / (unsigned)e.nst;
+    const int s0 = b2s_stripe_start(e, (int)(b % (unsigned)e.nst));
+    const unsigned plane = (unsigned)(e.Hsrc * e.W);
+    const unsigned bimg = bsrc * CN * plane;                                  // pairs*cn*H*W < 2^31 is checked on the host
+    const int nitems = nrows * CN;                                            // ring items: (row, channel)
+    auto src_row = [&](int r) { return min(s0 + max(yb - SW2 + r, 0), e.Hsrc - 1); };   // clamped at the stripe's first row
+    auto left_word = [&](int q) {
+        const int r = q / CN, c = q - r * CN;
+        return __ldg(descL + (bimg + (unsigned)c * plane + (unsigned)(src_row(r) * e.W + xiA)));
     };
     // producer (thread 0): ONE 3-d tensor copy (TMA) per row -- box {8 elements, NELP/8, 12 planes} of the view
     // {8, PW/8, batch*H*12} of the plane rows -> stage r % NSTG, dense [12][NELP].  Before a stage is refilled every
     // warp must have handed it back (empty barrier of the row that used it last).
     const int gal8 = P8 ? gal >> 2 : gal >> 3;                                // in 16-byte units
     constexpr unsigned NPL = P8 ? 6u : 12u;                                   // plane rows per image row
-    auto issue = [&](int r) {
-        const int yr = min(max(yb - SW2 + r, 0), e.H - 1);
-        const unsigned st = (unsigned)(r & (NSTG - 1));
+    auto issue = [&](int q) {
+        const int r = q / CN, c = q - r * CN;
+        const int yr = src_row(r);
+        const unsigned st = (unsigned)(q & (NSTG - 1));
         const unsigned full = sm0 + P::bars + st * 8, dst = sm0 + st * P::STAGE;
-        if (r >= NSTG) cmbar_wait(sm0 + P::bars + (NSTG + st) * 8, (unsigned)((r / NSTG) - 1) & 1u);
+        if (q >= NSTG) cmbar_wait(sm0 + P::bars + (NSTG + st) * 8, (unsigned)((q / NSTG) - 1) & 1u);
         cmbar_expect_tx(full, (unsigned)P::STAGE);
-        const int row = (int)((b * (unsigned)e.H + (unsigned)yr) * NPL);
+        const int row = (int)(((bsrc * CN + (unsigned)c) * (unsigned)e.Hsrc + (unsigned)yr) * NPL);
         asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
                      ::"r"(dst), "l"(&tmap), "r"(0), "r"(gal8), "r"(row), "r"(full) : "memory");
     };
@@ -426,7 +440,7 @@ k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap
     __syncthreads();
     const bool producer = threadIdx.x == (B2S_COST_PRODUCER_LAST ? blockDim.x - 32 : 0u);
     if (producer)
-        for (int r = 0; r < NSTG - 1 && r < nrows; r++) issue(r);
+        for (int q = 0; q < NSTG - 1 && q < nitems; q++) issue(q);
 
     uint32_t acc[4] = { 0, 0, 0, 0 }, ring[BS][4], vmax = 0;
 #pragma unroll
@@ -438,34 +452,35 @@ k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap
         for (int s = 0; s < BS; s++) {
             const int r = r0 + s;
             if (r >= nrows) break;                                            // uniform
-            if (producer && r + NSTG - 1 < nrows) issue(r + NSTG - 1);           // keep NSTG-1 rows ahead
-            const uint2 wl = wl_next;
-            if (r + 1 < nrows) wl_next = left_word(r + 1);
-            const unsigned st = (unsigned)(r & (NSTG - 1));
-            cmbar_wait(sm0 + P::bars + st * 8, (unsigned)(r / NSTG) & 1u);
-            // ---- phase A: pixel costs of (column, 8 disparities) --------------------------------
-            uint32_t hs[4];
-            {
+            // ---- phase A: pixel costs of (column, 8 disparities), summed over the colour channels ----
+            uint32_t hs[4], pc[4] = { 0, 0, 0, 0 };
+#pragma unroll
+            for (int c = 0; c < CN; c++) {
+                const int q = r * CN + c;
+                if (producer && q + NSTG - 1 < nitems) issue(q + NSTG - 1);      // keep NSTG-1 items ahead
+                const uint2 wl = wl_next;
+                if (q + 1 < nitems) wl_next = left_word(q + 1);
+                const unsigned st = (unsigned)(q & (NSTG - 1));
+                cmbar_wait(sm0 + P::bars + st * 8, (unsigned)(q / NSTG) & 1u);
                 const unsigned rb = sm0 + st * P::STAGE + roff;
                 const uint32_t ug = __byte_perm(wl.x, 0, 0x4040), log = __byte_perm(wl.x, 0, 0x4141), hig = __byte_perm(wl.x, 0, 0x4242);
                 const uint32_t ur = __byte_perm(wl.y, 0, 0x4040), lor = __byte_perm(wl.y, 0, 0x4141), hir = __byte_perm(wl.y, 0, 0x4242);
-                uint32_t pc[4];
 #pragma unroll
                 for (int w = 0; w < 4; w++) {
                     const uint32_t cg = bt2(ug, log, hig, lds32(rb + 4 * w), lds32(rb + NELP * 4 + 4 * w), lds32(rb + 2 * NELP * 4 + 4 * w));
                     const uint32_t cr = bt2(ur, lor, hir, lds32(rb + 3 * NELP * 4 + 4 * w), lds32(rb + 4 * NELP * 4 + 4 * w),
                                             lds32(rb + 5 * NELP * 4 + 4 * w));
                     // (cr - bias) >> 2 == ((cr >> 2) & 0x7f) - 0x40 per half
-                    pc[w] = cg + ((cr >> 2) & 0x007f007fu) - (B2S_BIAS + 0x00400040u);
+                    pc[w] += cg + ((cr >> 2) & 0x007f007fu) - (B2S_BIAS + 0x00400040u);
                 }
                 // this warp is done with the stage: hand it back to the producer
                 __syncwarp();
                 if (lane == 0) cmbar_arrive(sm0 + P::bars + (NSTG + st) * 8);
-                // ---- phase B: box sums.  The BS columns are the next BS-1 lanes of this warp: window sum
-                // by doubling (p2 = x + x+1, p4 = p2 + p2(x+2), ...) through shuffles, no shared memory.
-#pragma unroll
-                for (int w = 0; w < 4; w++) hs[w] = window_sum<BS>(pc[w]);
             }
+            // ---- phase B: box sums.  The BS columns are the next BS-1 lanes of this warp: window sum
+            // by doubling (p2 = x + x+1, p4 = p2 + p2(x+2), ...) through shuffles, no shared memory.
+#pragma unroll
+            for (int w = 0; w < 4; w++) hs[w] = window_sum<BS>(pc[w]);
             {
 #pragma unroll
                 for (int w = 0; w < 4; w++) {
@@ -507,7 +522,7 @@ static tmap_encode_fn tmap_encoder()
     return fn;
 }
 
-template <int BS, int MAXW, bool P8>
+template <int BS, int MAXW, bool P8, int CN>
 static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const SgbmEff& e, uint16_t* cost, int* flag, cudaStream_t st)
 {
     using P = CostPlan<MAXW>;
@@ -527,7 +542,7 @@ static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const S
     // plane rows as a 3-d tensor of 16-byte groups: {8 u16, groups per plane row, plane rows}
     CUtensorMap tmap;
     const cuuint64_t rowu16 = P8 ? 2 * (cuuint64_t)PW : (cuuint64_t)PW, npl = P8 ? 6 : 12;
-    const cuuint64_t gdim[3] = { 8, rowu16 / 8, (cuuint64_t)e.batch * e.H * npl };
+    const cuuint64_t gdim[3] = { 8, rowu16 / 8, (cuuint64_t)(e.batch / e.nst) * CN * e.Hsrc * npl };   // the source images
     const cuuint64_t gstr[2] = { 16, rowu16 * 2 };
     const cuuint32_t box[3] = { 8, (cuuint32_t)(P8 ? 2 * P::NELP : P::NELP) / 8, (cuuint32_t)npl };
     const cuuint32_t estr[3] = { 1, 1, 1 };
@@ -535,11 +550,11 @@ static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const S
                       CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) { b2s_set_error("cuTensorMapEncodeTiled failed (%d)", (int)cr); return B2S_E_CUDA; }
     if (e.D != e.Dp) {
-        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, true, P8>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
-        k_cost_fast<BS, MAXW, true, P8><<<grid, nthreads, P::total, st>>>(descL, tmap, e, TR, cost, flag);
+        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, true, P8, CN>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
+        k_cost_fast<BS, MAXW, true, P8, CN><<<grid, nthreads, P::total, st>>>(descL, tmap, e, TR, cost, flag);
     } else {
-        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, false, P8>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
-        k_cost_fast<BS, MAXW, false, P8><<<grid, nthreads, P::total, st>>>(descL, tmap, e, TR, cost, flag);
+        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast<BS, MAXW, false, P8, CN>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
+        k_cost_fast<BS, MAXW, false, P8, CN><<<grid, nthreads, P::total, st>>>(descL, tmap, e, TR, cost, flag);
     }
     B2S_LAUNCH_CHECK();
     return B2S_OK;
@@ -548,8 +563,11 @@ static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const S
 template <int BS, int MAXW>
 static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const SgbmEff& e, uint16_t* cost, int* flag, cudaStream_t st)
 {
-    return e.swz ? launch_cost_fast<BS, MAXW, true>(descL, planesR, e, cost, flag, st)
-                 : launch_cost_fast<BS, MAXW, false>(descL, planesR, e, cost, flag, st);
+    if (e.cn == 3)
+        return e.swz ? launch_cost_fast<BS, MAXW, true, 3>(descL, planesR, e, cost, flag, st)
+                     : launch_cost_fast<BS, MAXW, false, 3>(descL, planesR, e, cost, flag, st);
+    return e.swz ? launch_cost_fast<BS, MAXW, true, 1>(descL, planesR, e, cost, flag, st)
+                 : launch_cost_fast<BS, MAXW, false, 1>(descL, planesR, e, cost, flag, st);
 }
 
 // which of the two cost kernels serves a configuration (decides the format of the right descriptors)

@@ -62,7 +62,7 @@ k_wta(const uint16_t* __restrict__ S, SgbmEff e, int16_t* __restrict__ disp, uin
     const int minS = (int)(key >> 16);
 
     // uniqueness + neighbours of the winner
-    const int thr = minS * 100;
+    const int thr = minS * 100 + e.uqle;       // uqle (MODE_SGBM_3WAY): reject on equality too
     const int mul = 100 - e.uniq;
     uint32_t bad = 0, sm1 = 0, sp1 = 0;
 #pragma unroll
@@ -183,6 +183,32 @@ int b2s_launch_finish_rec(const SgbmEff& e, const uint2* rec, const uint32_t* di
         dim3 grid(b2s_cdiv(e.W, 256), e.H, e.batch);
         k_finish_rec<<<grid, 256, 0, st>>>(e, rec, disp2key, disp_raw);
     }
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}
+
+// MODE_SGBM_3WAY (cv2 4.13.0 computeDisparity3WAY): stripe st writes its source row y to row (st ? 0 : ov) + y - s0 of a
+// buffer of sz + ov rows preset to INVALID, and image row i is copied from row ov + i % sz of stripe i / sz.  Unless the
+// early start of a stripe was clamped at the image top (tiny images) that is the stripe's own row i.
+__global__ void __launch_bounds__(256)
+k_assemble_stripes(SgbmEff v, const int16_t* __restrict__ src, int16_t* __restrict__ dst)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= v.W) return;
+    const int i = blockIdx.y, b = blockIdx.z;
+    const int st = i / v.sz;
+    const int s0 = b2s_stripe_start(v, st);
+    const int s1 = min((st + 1) * v.sz, v.Hsrc);
+    const int y = s0 + v.ov + (i - st * v.sz) - (st == 0 ? v.ov : 0);
+    int val = v.invalid;
+    if (y >= s0 && y < s1 && y - s0 < v.H) val = src[(((size_t)b * v.nst + st) * v.H + (y - s0)) * v.W + x];
+    dst[((size_t)b * v.Hsrc + i) * v.W + x] = (int16_t)val;
+}
+
+int b2s_launch_assemble_stripes(const SgbmEff& v, const int16_t* raw_stripes, int16_t* raw, cudaStream_t st)
+{
+    dim3 grid(b2s_cdiv(v.W, 256), v.Hsrc, v.batch / v.nst);
+    k_assemble_stripes<<<grid, 256, 0, st>>>(v, raw_stripes, raw);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
 }

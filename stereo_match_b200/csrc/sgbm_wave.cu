@@ -49,18 +49,18 @@ int b2s_launch_wave(const SgbmEff& e, const uint16_t* cost, uint16_t* S, uint16_
     const int mul = 100 - e.uniq;
     a.magic = mul > 0 ? ((1ull << 40) + (unsigned long long)mul - 1) / (unsigned long long)mul : 0ull;
     a.nbands = l.nbands;
-    a.diag = e.ndirs == 4 ? 0 : 1;
+    a.diag = (e.ndirs == 4 || e.ndirs == 3) ? 0 : 1;
     a.zero = 0u;
     // L_r <= C + P2 and C <= blockSize^2 * (2*ftzero + 63) (Sobel channel BT cost <= 2*ftzero, raw channel <= 255 >> 2):
     // if S1 (<= 32767) plus four such terms cannot reach 65536, the packed sums never carry between the halves
     {
         const long long bs = 2 * e.SW2 + 1;
-        const long long lmax = bs * bs * (2LL * e.ftzero + 63) + e.P2;
+        const long long lmax = bs * bs * (2LL * e.ftzero + 63) * e.cn + e.P2;     // cn colour channels add up
         a.fastacc = (4 * lmax <= 32768) ? 1 : 0;
     }
     int rc;
     B2S_CUDA_CHECK(cudaMemsetAsync(disp2key, 0xff, (size_t)e.batch * e.H * e.W * sizeof(uint32_t), st));
-    // pass 1: -> , down-right, down, down-left (MODE_HH4: -> , down)
+    // pass 1: -> , down-right, down, down-left (MODE_HH4, MODE_SGBM_3WAY: -> , down)
     B2S_CUDA_CHECK(cudaMemsetAsync(a.progress, 0, (items + 1) * sizeof(int), st));
     a.flip = 0;
     if ((rc = launch_pass(e, a, 1, 0, st))) return rc;
@@ -69,7 +69,7 @@ int b2s_launch_wave(const SgbmEff& e, const uint16_t* cost, uint16_t* S, uint16_
     if (e.ndirs == 8 || e.ndirs == 4) {   // MODE_HH: the mirrored sweep adds <- , up-left, up, up-right (MODE_HH4: <- , up)
         B2S_CUDA_CHECK(cudaMemsetAsync(a.progress, 0, (items + 1) * sizeof(int), st));
         rc = launch_pass(e, a, 1, 1, st);
-    } else {                     // MODE_SGBM: only <-
+    } else {                     // MODE_SGBM, MODE_SGBM_3WAY: only <-
         rc = launch_pass(e, a, 0, 1, st);
     }
     return rc;

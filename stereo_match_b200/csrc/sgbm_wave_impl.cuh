@@ -244,7 +244,8 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
     bool bad_lane = false;
     if (mul > 0) {
         // S * mul < minS * 100  <=>  S < T,  T = ceil(minS * 100 / mul)   (exact magic division)
-        const unsigned a = (unsigned)(minS * 100 + mul - 1);
+        // (MODE_SGBM_3WAY, e.uqle: S * mul <= minS * 100  <=>  S < floor(minS * 100 / mul) + 1)
+        const unsigned a = (unsigned)(minS * 100 + mul - 1 + e.uqle);
         unsigned T = (unsigned)(((unsigned long long)a * magic) >> 40);
         T = min(T, 0x8000u);
         const uint32_t K = (0x8000u - T) * 0x10001u;               // S + K has bit 15 set  <=>  S >= T
@@ -277,7 +278,7 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
         }
         bad_lane = (~acc & cells & ~excl) != 0;
     } else {
-        const int thr = minS * 100;
+        const int thr = minS * 100 + e.uqle;
 #pragma unroll
         for (int i = 0; i < R; i++) {
 #pragma unroll

@@ -80,19 +80,24 @@ class _Matcher:
             pass
 
     def _check_pair(self, who, left, right):
+        """-> (left, right) as [B, H, W] or [B, H, W, 3] uint8 device tensors, kind, squeeze, channels.
+        Shapes: (H, W) gray, (H, W, 3) colour (what cv2 takes), (B, H, W) gray batch, (B, H, W, 3) colour batch."""
         l, kind = _to_device(left, "left")
         r, _ = _to_device(right, "right")
         if l.shape != r.shape or l.dtype != r.dtype or l.dtype != torch.uint8:
             raise error("%s: left.size() == right.size() && left.type() == right.type() && left.depth() == CV_8U" % who)
-        if l.dim() == 3 and l.shape[2] == 3 and l.shape[1] != 3:
-            raise error("%s: 3-channel input is not supported by this engine; convert with cvtColor first" % who, _lib.E_UNSUPPORTED)
-        if l.dim() == 2:
+        cn = 1
+        if l.dim() == 4 and l.shape[3] == 3:
+            cn, squeeze = 3, False
+        elif l.dim() == 3 and l.shape[2] == 3 and l.shape[1] != 3:
+            l, r, cn, squeeze = l[None], r[None], 3, True
+        elif l.dim() == 2:
             l, r, squeeze = l[None], r[None], True
         elif l.dim() == 3:
             squeeze = False
         else:
-            raise error("%s: images must be (H, W) or (B, H, W) uint8" % who)
-        return l, r, kind, squeeze
+            raise error("%s: images must be (H, W), (H, W, 3), (B, H, W) or (B, H, W, 3) uint8" % who)
+        return l.contiguous(), r.contiguous(), kind, squeeze, cn
 
 
 class StereoSGBM(_Matcher):
@@ -110,11 +115,11 @@ class StereoSGBM(_Matcher):
         _lib.check(_lib.load().b2s_sgbm_set_params(self._h, C.byref(self._p)))
 
     def compute(self, left, right, disparity=None):
-        l, r, kind, squeeze = self._check_pair("StereoSGBM", left, right)
-        B, H, W = l.shape
+        l, r, kind, squeeze, cn = self._check_pair("StereoSGBM", left, right)
+        B, H, W = l.shape[:3]
         out = torch.empty((B, H, W), dtype=torch.int16, device=l.device)
         with torch.cuda.device(l.device):
-            _lib.check(_lib.load().b2s_sgbm_compute(self._h, _ptr(l), _ptr(r), H, W, B, _ptr(out), _stream()))
+            _lib.check(_lib.load().b2s_sgbm_compute_cn(self._h, _ptr(l), _ptr(r), H, W, cn, B, _ptr(out), _stream()))
         if squeeze:
             out = out[0]
         res = _from_device(out, kind)

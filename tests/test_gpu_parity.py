@@ -10,7 +10,8 @@ import torch
 
 import stereo_match_b200 as sm
 from stereo_match_b200.synth import synth_pair, KITTI_Q
-from vectors import (SGBM_VECTORS, SGBM_ERROR_VECTORS, SGBM_UNPINNED_VECTORS, BM_VECTORS, sgbm_kwargs, sgbm_pair)
+from vectors import (SGBM_VECTORS, SGBM_ERROR_VECTORS, SGBM_UNPINNED_VECTORS, SGBM_COLOR_VECTORS, BM_VECTORS, sgbm_kwargs,
+                     sgbm_pair, color_pair)
 
 pytestmark = pytest.mark.gpu
 
@@ -29,6 +30,25 @@ def test_sgbm_matches_oracle(i, v, port, cv2ref):
     got = m.compute(l, r)
     assert got.dtype == np.int16 and got.shape == l.shape
     assert np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
+
+
+@pytest.mark.parametrize("i,seed", SGBM_COLOR_VECTORS)
+def test_sgbm_color_matches_oracle(i, seed, port):
+    """3-channel input (reference: try_try.py:69-81), every mode, against the restatement and live cv2."""
+    import cv2
+    v = SGBM_VECTORS[i]
+    kw = sgbm_kwargs(v)
+    l, r = color_pair(v[0], v[1], max(v[2] + v[3], 8), seed)
+    want = port.sgbm_compute(l, r, **kw)
+    assert np.array_equal(want, cv2.StereoSGBM_create(**kw).compute(l, r)), "oracle port disagrees with cv2"
+    got = sm.StereoSGBM_create(**kw).compute(l, r)
+    assert got.shape == l.shape[:2] and np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
+    if i in (0, 26):            # a colour batch equals its singles
+        L = torch.from_numpy(np.stack([l, l[::-1].copy()])).cuda()
+        R = torch.from_numpy(np.stack([r, r[::-1].copy()])).cuda()
+        out = sm.StereoSGBM_create(**kw).compute(L, R)
+        assert np.array_equal(out[0].cpu().numpy(), want)
+        assert np.array_equal(out[1].cpu().numpy(), port.sgbm_compute(l[::-1].copy(), r[::-1].copy(), **kw))
 
 
 @pytest.mark.parametrize("i", [1, 7, 11, 13, 15, 27, 29, 33])      # 27.. : MODE_HH4 (zeroed bottom cost rows)
@@ -91,8 +111,10 @@ def test_sgbm_bad_inputs():
         m.compute(l, r[:, :-1])
     with pytest.raises(sm.error, match="CV_8U"):
         m.compute(l.astype(np.int16), r.astype(np.int16))
+    with pytest.raises(sm.error, match="unknown mode"):
+        sm.StereoSGBM_create(numDisparities=16, mode=4).compute(l, r)
     with pytest.raises(sm.error):
-        sm.StereoSGBM_create(numDisparities=16, mode=sm.STEREO_SGBM_MODE_SGBM_3WAY).compute(l, r)
+        m.compute(np.dstack([l] * 4), np.dstack([r] * 4))     # 4 channels
 
 
 @pytest.mark.parametrize("v", SGBM_UNPINNED_VECTORS, ids=_ids(SGBM_UNPINNED_VECTORS))

@@ -5,7 +5,8 @@ import os
 import numpy as np
 import pytest
 
-from vectors import SGBM_VECTORS, SGBM_ERROR_VECTORS, BM_VECTORS, sgbm_kwargs, sgbm_pair
+from vectors import (SGBM_VECTORS, SGBM_ERROR_VECTORS, SGBM_COLOR_VECTORS, BM_VECTORS, sgbm_kwargs, sgbm_pair,
+                     color_pair)
 from stereo_match_b200.synth import synth_pair, KITTI_Q
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cv2_4_13_0.npz")
@@ -25,6 +26,18 @@ def test_sgbm_port_equals_cv2(i, v, port, cv2ref):
     l, r = sgbm_pair(i, v)
     kw = sgbm_kwargs(v)
     got, want = port.sgbm_compute(l, r, **kw), cv2ref.sgbm_compute(l, r, **kw)
+    assert np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
+
+
+@pytest.mark.parametrize("i,seed", SGBM_COLOR_VECTORS)
+def test_sgbm_port_equals_cv2_color(i, seed, port):
+    """3-channel input: every colour channel contributes its own Sobel and raw BT cost."""
+    import cv2
+    v = SGBM_VECTORS[i]
+    kw = sgbm_kwargs(v)
+    l, r = color_pair(v[0], v[1], max(v[2] + v[3], 8), seed)
+    want = cv2.StereoSGBM_create(**kw).compute(l, r)
+    got = port.sgbm_compute(l, r, **kw)
     assert np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
 
 
@@ -95,6 +108,14 @@ def test_golden_sgbm(port, gold):
         assert v == SGBM_VECTORS[i]
         got = port.sgbm_compute(gold["sgbm%d_l" % i], gold["sgbm%d_r" % i], **sgbm_kwargs(v))
         assert np.array_equal(got, gold["sgbm%d_d" % i]), "golden sgbm vector %d" % i
+
+
+def test_golden_sgbm_color(port, gold):
+    ids = sorted(int(k[5:-2]) for k in gold.files if k.startswith("color") and k.endswith("_d"))
+    assert len(ids) >= 4
+    for i in ids:
+        got = port.sgbm_compute(gold["color%d_l" % i], gold["color%d_r" % i], **sgbm_kwargs(SGBM_VECTORS[i]))
+        assert np.array_equal(got, gold["color%d_d" % i]), "golden colour vector %d" % i
 
 
 def test_golden_bm(port, gold):

@@ -40,7 +40,39 @@ SGBM_VECTORS = [
     (180, 50, 0, 128, 5, 600, 2400, 1, 63, 10, 3, 0, 0),    # R = 8 (permuted records)
     (330, 40, 0, 272, 3, 72, 288, 1, 63, 10, 3, 0, 0),      # 32-lane kernels
     (640, 24, 0, 528, 3, 72, 288, 1, 63, 10, 3, 0, 0),      # D > 512: per-direction kernels
+    # MODE_SGBM_3WAY (-> , down, <- inside 4 fixed stripes that restart the block sum and the downward path;
+    # uniqueness test with <=)
+    (300, 200, 0, 64, 5, 100, 400, 1, 63, 10, 2, 0, 0),
+    (150, 90, 0, 48, 5, 100, 400, 1, 63, 0, 2, 40, 2),      # uniquenessRatio 0: no uniqueness test at all
+    (131, 77, 4, 32, 9, 100, 1000, 1, 0, 5, 2, 0, 0),
+    (200, 121, -8, 64, 3, 72, 288, 2, 63, 15, 2, 40, 2),
+    (40, 3, 0, 16, 5, 600, 2400, 1, 63, 15, 2, 0, 0),       # stripes of one row: clamped starts shift cv2's rows
+    (60, 1, 0, 16, 5, 600, 2400, 1, 63, 15, 2, 0, 0),
+    (120, 7, 0, 16, 3, 100, 400, 1, 63, 10, 2, 0, 0),
+    (120, 12, 0, 16, 5, 100, 400, 1, 63, 10, 2, 0, 0),
+    (100, 25, 0, 16, 9, 100, 400, 1, 63, 10, 2, 0, 0),
+    (150, 90, 0, 24, 1, 8, 32, 1, 63, 15, 2, 0, 0),         # equality cases of the uniqueness test
+    (150, 90, 0, 48, 5, 0, 0, 0, 0, -1, 2, 0, 0),           # every silent fallback
+    (180, 50, 0, 128, 5, 600, 2400, 1, 63, 10, 2, 0, 0),    # R = 8
+    (330, 40, 0, 272, 3, 72, 288, 1, 63, 10, 2, 0, 0),      # 32-lane kernels
+    (640, 24, 0, 528, 3, 72, 288, 1, 63, 10, 2, 0, 0),      # D > 512: per-direction kernels
+    (150, 90, 0, 40, 13, 20, 80, 1, 31, 15, 2, 0, 0),       # blockSize 13: generic cost kernel
 ]
+
+# 3-channel input (reference: try_try.py:69-81): (index into SGBM_VECTORS whose parameters are used, seed)
+SGBM_COLOR_VECTORS = [(0, 1), (1, 2), (3, 3), (4, 4), (5, 5), (8, 6), (12, 7), (22, 8), (24, 9), (26, 10), (27, 11), (36, 12),
+                      (37, 13), (40, 14), (47, 15), (46, 16)]
+
+
+def color_pair(w, h, maxd, seed):
+    """Correlated colour channels: one synthetic pair plus per-channel mixtures of two others."""
+    import numpy as np
+    a, b, c = (synth_pair(w, h, maxd, seed=1000 + 3 * seed + k) for k in range(3))
+
+    def mix(k):
+        return [a[k], np.clip(a[k] * 0.8 + b[k] * 0.2, 0, 255).astype(np.uint8),
+                np.clip(a[k] * 0.7 + c[k] * 0.3, 0, 255).astype(np.uint8)]
+    return np.stack(mix(0), -1), np.stack(mix(1), -1)
 
 
 # cv2 4.13.0 raises cv2.error for these (width - maxD <= blockSize/2, stereosgbm.cpp:511)
