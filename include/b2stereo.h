@@ -19,6 +19,8 @@
  *   b2s_remap_gray_u8   the two above fused (BGR in, rectified gray out)
  *   b2s_pipeline    remap x2 -> (gray) -> StereoSGBM.compute -> reprojectImageTo3D, one call
  *                       disparity_calculation.py:207-208, 286-289, 302
+ *   b2s_compact_points  points_3d[mask], colors[mask] in front of io_functions.write_ply
+ *                       disparity_calculation.py:309-321, try_try.py:91-94
  *   b2s_median3_i16, b2s_filter_speckles
  *                   the cv2.medianBlur / cv2.filterSpeckles that StereoSGBM.compute
  *                   runs internally, exposed for stage-level parity
@@ -185,6 +187,15 @@ B2S_API int b2s_bgr2gray(const uint8_t* bgr, size_t npixels, uint8_t* gray, void
    calls; disparity_calculation.py:207-208 + :286-287).  src: [batch][sH][sW][3], dst: [batch][H][W] */
 B2S_API int b2s_remap_gray_u8(const uint8_t* src_bgr, int sH, int sW, const float* mapx,
                       const float* mapy, int H, int W, int batch, uint8_t* dst_gray, void* stream);
+/* Point cloud behind reprojectImageTo3D (disparity_calculation.py:309-321, try_try.py:91-94): keeps the pixels with
+   lo < disp < hi in row-major order (numpy's points_3d[mask]), their colours as RGB bytes from the BGR image (bgr and
+   rgb may both be NULL), NaN / inf coordinates replaced by 0.  Images of a batch are packed one after the other:
+   offsets[b] .. offsets[b+1] are the vertices of image b (device array of batch + 1 int64; offsets[batch] = total).
+   verts / rgb must hold batch*H*W vertices (worst case); scratch: b2s_compact_points_scratch_bytes bytes. */
+B2S_API size_t b2s_compact_points_scratch_bytes(int H, int W, int batch);
+B2S_API int b2s_compact_points(const float* xyz, const void* disp, int disp_dtype, double lo, double hi,
+                       const uint8_t* bgr, int H, int W, int batch, float* verts, uint8_t* rgb,
+                       long long* offsets, void* scratch, void* stream);
 B2S_API int b2s_median3_i16(const int16_t* src, int H, int W, int batch, int16_t* dst, void* stream);
 /* in place; labels: device scratch of batch*H*W int32, counts likewise */
 B2S_API int b2s_filter_speckles(int16_t* img, int H, int W, int batch, int newVal,

@@ -62,6 +62,8 @@ PROTOTYPES = {
     "b2s_remap_gray_u8": (_i, [_vp, _i, _i, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "b2s_pipeline": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp,
                           C.POINTER(C.c_double), C.c_float, _i, _vp, _vp, _vp]),
+    "b2s_compact_points_scratch_bytes": (_sz, [_i, _i, _i]),
+    "b2s_compact_points": (_i, [_vp, _vp, _i, C.c_double, C.c_double, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "b2s_median3_i16": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "b2s_filter_speckles": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
 }

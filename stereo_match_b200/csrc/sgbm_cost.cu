@@ -408,7 +408,8 @@ k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap
     const unsigned plane = (unsigned)(e.Hsrc * e.W);
     const unsigned bimg = bsrc * CN * plane;                                  // pairs*cn*H*W < 2^31 is checked on the host
     const int nitems = nrows * CN;                                            // ring items: (row, channel)
-    auto src_row = [&](int r) { return min(s0 + max(yb - SW2 + r, 0), e.Hsrc - 1); };   // clamped at the stripe's first row
+    const int rbase = yb - SW2 + s0, rlast = e.Hsrc - 1;
+    auto src_row = [&](int r) { return min(max(rbase + r, s0), rlast); };    // clamped at the stripe's first row and the image's last
     auto left_word = [&](int q) {
         const int r = q / CN, c = q - r * CN;
         return __ldg(descL + (bimg + (unsigned)c * plane + (unsigned)(src_row(r) * e.W + xiA)));

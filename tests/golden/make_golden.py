@@ -69,6 +69,20 @@ for size, diff in ((0, 0), (10, 16), (100, 32)):
 out["med_in"] = d16
 out["med_out"] = cv2.medianBlur(d16, 3)
 
+# PLY bytes from the reference's own writer (io_functions.py:28-44), imported from /root/reference in this container
+import importlib.util   # noqa: E402
+import tempfile         # noqa: E402
+spec = importlib.util.spec_from_file_location("ref_io_functions", "/root/reference/io_functions.py")
+ref_io = importlib.util.module_from_spec(spec)
+spec.loader.exec_module(ref_io)
+pv = (rng.standard_normal((37, 3)) * 100).astype(np.float32)
+pv[3, 1] = 0.0
+pc = rng.integers(0, 256, (37, 3), dtype=np.uint8)
+with tempfile.TemporaryDirectory() as td:
+    ref_io.write_ply(os.path.join(td, "a.ply"), pv, pc)
+    out["ply_bytes"] = np.frombuffer(open(os.path.join(td, "a.ply"), "rb").read(), np.uint8)
+out["ply_verts"], out["ply_colors"] = pv, pc
+
 path = os.path.join(HERE, "cv2_4_13_0.npz")
 np.savez_compressed(path, **out)
 print(path, os.path.getsize(path), "bytes,", len(out), "arrays")

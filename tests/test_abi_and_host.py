@@ -149,3 +149,12 @@ def test_two_rank_sharding_gloo(tmp_path):
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr[-2000:]
     assert '{"ok": true}' in r.stdout, r.stdout + r.stderr[-2000:]
+
+
+def test_write_ply_matches_reference_writer(tmp_path):
+    """Bytes of io_functions.write_ply (reference, run here by tests/golden/make_golden.py) for the same vertices."""
+    import stereo_match_b200 as sm
+    g = np.load(os.path.join(ROOT, "tests", "golden", "cv2_4_13_0.npz"))
+    fn = tmp_path / "cloud.ply"
+    sm.write_ply(str(fn), g["ply_verts"], g["ply_colors"])
+    assert fn.read_bytes() == g["ply_bytes"].tobytes()

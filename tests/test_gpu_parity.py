@@ -317,3 +317,50 @@ def test_filter_speckles_stress(seed, cv2ref):
         for k in range(len(imgs)):
             want = cv2ref.filter_speckles(imgs[k], -16, size, diff)
             assert np.array_equal(got[k].cpu().numpy(), want), (k, size, diff, int((got[k].cpu().numpy() != want).sum()))
+
+
+def _cloud_numpy(disp, xyz, bgr, lo, hi):
+    """disparity_calculation.py:309-321 restated with numpy's own boolean-mask indexing."""
+    mask = np.logical_and(disp < hi, disp > lo)
+    pts = xyz[mask].copy()
+    pts[np.isnan(pts)] = 0
+    pts[np.isinf(pts)] = 0
+    return pts, (bgr[..., ::-1][mask] if bgr is not None else None)
+
+
+@pytest.mark.parametrize("dtype", [np.int16, np.float32, np.uint8, np.int32])
+def test_point_cloud_matches_numpy_mask(dtype):
+    rng = np.random.default_rng(11)
+    H, W = 53, 1031                                    # not a multiple of the block size, several blocks
+    disp = rng.integers(-16, 40, (H, W)).astype(dtype) if dtype != np.uint8 else rng.integers(0, 40, (H, W)).astype(dtype)
+    xyz = rng.standard_normal((H, W, 3)).astype(np.float32)
+    xyz[rng.random((H, W)) < 0.05] = np.inf
+    xyz[rng.random((H, W)) < 0.05, 1] = np.nan
+    xyz[rng.random((H, W)) < 0.05, 2] = -np.inf
+    bgr = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+    for lo, hi in ((10, 20), (-np.inf, np.inf), (100, 200), (float(disp.min()), np.inf)):
+        wp, wc = _cloud_numpy(disp, xyz, bgr, lo, hi)
+        gp, gc = sm.point_cloud(disp, xyz, bgr, lo, hi)
+        assert gp.shape == wp.shape and np.array_equal(gp.view(np.uint32), wp.view(np.uint32))
+        assert np.array_equal(gc, wc)
+    gp, gc = sm.point_cloud(disp, xyz, None, 10, 20)
+    assert gc is None and np.array_equal(gp.view(np.uint32), _cloud_numpy(disp, xyz, None, 10, 20)[0].view(np.uint32))
+
+
+def test_point_cloud_batch_and_chain(cv2ref):
+    """Batch offsets; and the reference's tail (compute -> reprojectImageTo3D -> mask -> PLY vertices) on the GPU."""
+    pairs = [synth_pair(160, 60, 32, seed=s) for s in range(3)]
+    L = torch.from_numpy(np.stack([p[0] for p in pairs])).cuda()
+    R = torch.from_numpy(np.stack([p[1] for p in pairs])).cuda()
+    m = sm.StereoSGBM_create(minDisparity=0, numDisparities=32, blockSize=5, P1=600, P2=2400, disp12MaxDiff=1,
+                             uniquenessRatio=10, speckleWindowSize=50, speckleRange=2, preFilterCap=63)
+    disp = m.compute(L, R)
+    xyz = sm.reprojectImageTo3D(disp, KITTI_Q)
+    bgr = torch.stack([L, R, L], -1).contiguous()
+    verts, cols, offs = sm.point_cloud(disp, xyz, bgr, lo=100, hi=300)
+    offs = offs.cpu().numpy()
+    assert offs[0] == 0 and offs[-1] == verts.shape[0]
+    for b in range(3):
+        wp, wc = _cloud_numpy(disp[b].cpu().numpy(), xyz[b].cpu().numpy(), bgr[b].cpu().numpy(), 100, 300)
+        assert np.array_equal(verts[offs[b]:offs[b + 1]].cpu().numpy().view(np.uint32), wp.view(np.uint32))
+        assert np.array_equal(cols[offs[b]:offs[b + 1]].cpu().numpy(), wc)
