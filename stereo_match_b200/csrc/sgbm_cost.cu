@@ -406,10 +406,12 @@ k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap
     const unsigned bsrc = b / (unsigned)e.nst;
     const int s0 = b2s_stripe_start(e, (int)(b % (unsigned)e.nst));
     const unsigned plane = (unsigned)(e.Hsrc * e.W);
-    const unsigned bimg = bsrc * CN * plane;                                  // pairs*cn*H*W < 2^31 is checked on the host
+    // the stripe's first row is folded into the bases, so rows are clamped to [0, hrel] like those of a whole image
+    const unsigned bimg = bsrc * CN * plane + (unsigned)(s0 * e.W);           // pairs*cn*H*W < 2^31 is checked on the host
+    const unsigned rowbase = bsrc * CN * (unsigned)e.Hsrc + (unsigned)s0;
+    const int hrel = e.Hsrc - 1 - s0;
     const int nitems = nrows * CN;                                            // ring items: (row, channel)
-    const int rbase = yb - SW2 + s0, rlast = e.Hsrc - 1;
-    auto src_row = [&](int r) { return min(max(rbase + r, s0), rlast); };    // clamped at the stripe's first row and the image's last
+    auto src_row = [&](int r) { return min(max(yb - SW2 + r, 0), hrel); };    // relative to the stripe's first row
     auto left_word = [&](int q) {
         const int r = q / CN, c = q - r * CN;
         return __ldg(descL + (bimg + (unsigned)c * plane + (unsigned)(src_row(r) * e.W + xiA)));
@@ -426,7 +428,7 @@ k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap
         const unsigned full = sm0 + P::bars + st * 8, dst = sm0 + st * P::STAGE;
         if (q >= NSTG) cmbar_wait(sm0 + P::bars + (NSTG + st) * 8, (unsigned)((q / NSTG) - 1) & 1u);
         cmbar_expect_tx(full, (unsigned)P::STAGE);
-        const int row = (int)(((bsrc * CN + (unsigned)c) * (unsigned)e.Hsrc + (unsigned)yr) * NPL);
+        const int row = (int)((rowbase + (unsigned)(c * e.Hsrc + yr)) * NPL);
         asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
                      ::"r"(dst), "l"(&tmap), "r"(0), "r"(gal8), "r"(row), "r"(full) : "memory");
     };
