@@ -70,3 +70,30 @@ def test_cfg4_hh_middlebury_fullres(cv2ref):
     assert np.array_equal(m.compute(l, r), got)                # idempotent on a reused handle
     want = cv2ref.sgbm_compute(l, r, **CFG4["kw"])
     assert np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
+
+
+@pytest.mark.parametrize("mode", [2, 3])
+def test_cfg3_shape_other_modes(mode):
+    """MODE_SGBM_3WAY (4 stripes of 94 rows + 13 rows of overlap) and MODE_HH4 at the KITTI shape, gray and colour,
+    against live cv2 (which runs these two modes in parallel: about a second each)."""
+    import cv2
+    from vectors import color_pair
+    kw = dict(CFG3["kw"], mode=mode)
+    l, r = synth_pair(CFG3["w"], CFG3["h"], 128, seed=7)
+    m = sm.StereoSGBM_create(**kw)
+    got = m.compute(l, r)
+    want = cv2.StereoSGBM_create(**kw).compute(l, r)
+    assert np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
+    lc, rc = color_pair(CFG3["w"], CFG3["h"], 128, seed=21)
+    kwc = dict(kw, blockSize=3)                                   # colour costs are 3x: stay inside the int16 domain
+    mc = sm.StereoSGBM_create(**kwc)
+    gotc = mc.compute(lc, rc)
+    assert not mc.overflowed()
+    wantc = cv2.StereoSGBM_create(**kwc).compute(lc, rc)
+    assert np.array_equal(gotc, wantc), "%d pixels differ (colour)" % (gotc != wantc).sum()
+    # a batch of colour pairs equals its singles
+    L = torch.from_numpy(np.stack([lc, lc[:, ::-1].copy()])).cuda()
+    R = torch.from_numpy(np.stack([rc, rc[:, ::-1].copy()])).cuda()
+    out = mc.compute(L, R)
+    assert np.array_equal(out[0].cpu().numpy(), wantc)
+    assert np.array_equal(out[1].cpu().numpy(), cv2.StereoSGBM_create(**kwc).compute(lc[:, ::-1].copy(), rc[:, ::-1].copy()))
