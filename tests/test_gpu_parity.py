@@ -364,3 +364,16 @@ def test_point_cloud_batch_and_chain(cv2ref):
         wp, wc = _cloud_numpy(disp[b].cpu().numpy(), xyz[b].cpu().numpy(), bgr[b].cpu().numpy(), 100, 300)
         assert np.array_equal(verts[offs[b]:offs[b + 1]].cpu().numpy().view(np.uint32), wp.view(np.uint32))
         assert np.array_equal(cols[offs[b]:offs[b + 1]].cpu().numpy(), wc)
+
+
+@pytest.mark.parametrize("seed", range(80))
+def test_sgbm_random_sweep(seed):
+    """Seeded random parameter / size / mode / channel combinations against live cv2 (tests/random_cases.py)."""
+    import cv2
+    from random_cases import random_case
+    kw, l, r = random_case(seed)
+    want = cv2.StereoSGBM_create(**kw).compute(l, r)
+    m = sm.StereoSGBM_create(**kw)
+    got = m.compute(l, r)
+    assert not m.overflowed(), "case left the guaranteed domain: %r" % (kw,)
+    assert np.array_equal(got, want), "%d pixels differ for %r %r" % ((got != want).sum(), kw, l.shape)

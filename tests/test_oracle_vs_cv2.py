@@ -137,3 +137,14 @@ def test_golden_stages(port, gold):
     for size, diff in ((0, 0), (10, 16), (100, 32)):
         assert np.array_equal(port.filter_speckles(gold["sp_in"], -16, size, diff), gold["sp_out_%d_%d" % (size, diff)])
     assert np.array_equal(port.median3(gold["med_in"]), gold["med_out"])
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_sgbm_port_random_sweep(seed, port):
+    """Seeded random parameter / size / mode / channel combinations inside the guaranteed-parity domain."""
+    import cv2
+    from random_cases import random_case
+    kw, l, r = random_case(seed)
+    want = cv2.StereoSGBM_create(**kw).compute(l, r)
+    got = port.sgbm_compute(l, r, **kw)
+    assert np.array_equal(got, want), "%d pixels differ for %r %r" % ((got != want).sum(), kw, l.shape)
