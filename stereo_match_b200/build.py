@@ -8,7 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_obj")
 LIB = os.path.join(HERE, "libb2stereo.so")
-SOURCES = ["api.cu", "sgbm_cost.cu", "sgbm_agg.cu", "sgbm_wave.cu", "sgbm_wave_g8.cu", "sgbm_wave_g16.cu", "sgbm_wave_g32.cu", "sgbm_post.cu", "speckle.cu", "bm.cu", "geom.cu", "cloud.cu"]
+SOURCES = ["api.cu", "sgbm_cost.cu", "sgbm_agg.cu", "sgbm_wave.cu", "sgbm_wave_g8.cu", "sgbm_wave_g8s.cu", "sgbm_wave_g16.cu", "sgbm_wave_g32.cu", "sgbm_post.cu", "speckle.cu", "bm.cu", "geom.cu", "cloud.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "--fmad=false",            # reprojection must not contract fp64 mul+add (bitwise parity)
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "-Xptxas", "-v"]
@@ -30,7 +30,7 @@ def _stale(target, deps):
 
 def build(force=False, verbose=False):
     global OBJ, LIB
-    extra = os.environ.get("B2S_NVCC_EXTRA", "").split()      # A/B builds: e.g. -DB2S_WAVE_NT8=256
+    extra = os.environ.get("B2S_NVCC_EXTRA", "").split()      # A/B builds: e.g. -DB2S_WAVE_PFD=10
     if extra:
         tag = "".join(c if c.isalnum() else "_" for c in "".join(extra))
         OBJ, LIB = os.path.join(HERE, "_obj" + tag), os.path.join(HERE, "libb2stereo%s.so" % tag)

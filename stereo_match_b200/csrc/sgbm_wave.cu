@@ -1,7 +1,17 @@
 // sgbm_wave.cu -- host side of the fused wavefront aggregation (see sgbm_wave.cuh).
 #include "sgbm_wave.cuh"
 
-int b2s_wave_rows_per_band(const SgbmEff& e) { return wave::threads_for(e.G) / e.G; }
+int b2s_wave_threads(const SgbmEff& e)
+{
+    if (e.G != 8) return 256;
+    // the 8-path sweeps with the widest lanes run a little faster in 16-row bands (see sgbm_wave.cuh); otherwise take
+    // 16-row bands only where 32-row bands would compute at least 5 % more rows (short images: the 3WAY stripes)
+    if (e.ndirs == 8 && e.R == 8) return 128;
+    const int r32 = (e.H + 31) / 32 * 32, r16 = (e.H + 15) / 16 * 16;
+    return (20 * r32 >= 21 * r16) ? 128 : 256;
+}
+
+int b2s_wave_rows_per_band(const SgbmEff& e) { return b2s_wave_threads(e) / e.G; }
 
 static size_t al256(size_t v) { return (v + 255) / 256 * 256; }
 
@@ -24,7 +34,7 @@ size_t b2s_wave_edge_bytes(const SgbmEff& e) { return edge_layout(e).total; }
 static int launch_pass(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
 {
     switch (e.G) {
-    case 8: return b2s_launch_wave_g8(e, a, vert, final, st);
+    case 8: return b2s_wave_threads(e) == 128 ? b2s_launch_wave_g8s(e, a, vert, final, st) : b2s_launch_wave_g8(e, a, vert, final, st);
     case 16: return b2s_launch_wave_g16(e, a, vert, final, st);
     case 32: return b2s_launch_wave_g32(e, a, vert, final, st);
     }

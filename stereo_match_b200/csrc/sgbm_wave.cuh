@@ -44,16 +44,17 @@ struct WaveArgs {
     unsigned int zero;      // always 0, opaque to the compiler (see `dep` in k_wave)
 };
 
-// threads per CTA of the wavefront kernel: small CTAs keep the per-step barrier cheap and let
-// several independent bands share an SM
-#ifndef B2S_WAVE_NT8
-#define B2S_WAVE_NT8 256
-#endif
-namespace wave { constexpr int threads_for(int G) { return G == 8 ? B2S_WAVE_NT8 : 256; } }
+// Threads per CTA of the wavefront kernel (a CTA owns threads / G rows): small CTAs keep the per-step barrier cheap
+// and let several independent bands share an SM.  With G = 8 lanes per pixel both 256 (32 rows) and 128 (16 rows) are
+// built; measured on the B200 per 128 KITTI-shape pairs: MODE_HH 19.36 / 19.05 ms, MODE_HH4 14.68 / 15.11,
+// MODE_SGBM_3WAY (stripe images of 107 rows: 128 / 112 rows computed) 13.16 / 12.38, MODE_SGBM 640x480 D = 64
+// 10.12 / 10.36 ms per step; 64 threads: 29.8 ms (four times the edge traffic).
+int b2s_wave_threads(const SgbmEff& e);
 int b2s_wave_rows_per_band(const SgbmEff& e);
 size_t b2s_wave_edge_bytes(const SgbmEff& e);       // edge + edge_min + progress + ticket
 int b2s_launch_wave(const SgbmEff& e, const uint16_t* cost, uint16_t* S, uint16_t* S_dbg, void* edge_ws,
                     uint2* rec, uint32_t* disp2key, cudaStream_t st);
-int b2s_launch_wave_g8(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st);
+int b2s_launch_wave_g8(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st);        // 256 threads
+int b2s_launch_wave_g8s(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st);       // 128 threads
 int b2s_launch_wave_g16(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st);
 int b2s_launch_wave_g32(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st);

@@ -2,5 +2,5 @@
 #include "sgbm_wave_impl.cuh"
 int b2s_launch_wave_g8(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
 {
-    return wave::launch_g<8>(e, a, vert, final, st);
+    return wave::launch_g<8, 256>(e, a, vert, final, st);
 }

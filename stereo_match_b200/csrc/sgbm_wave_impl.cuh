@@ -647,13 +647,12 @@ int launch_one(const SgbmEff& e, const WaveArgs& a, cudaStream_t st)
     return B2S_OK;
 }
 
-template <int R, int G, bool FA>
+template <int R, int G, int NT, bool FA>
 int launch_rgf(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
 {
-    constexpr int NT = threads_for(G);
     const bool pad = e.D != e.Dp;
     if (vert && !a.diag) {      // MODE_HH4 (built without the fast-accumulate variant)
-        if (FA) return launch_rgf<R, G, false>(e, a, vert, final, st);
+        if (FA) return launch_rgf<R, G, NT, false>(e, a, vert, final, st);
         if (!final) return pad ? launch_one<R, G, NT, true, true, false, false, false>(e, a, st) : launch_one<R, G, NT, false, true, false, false, false>(e, a, st);
         return pad ? launch_one<R, G, NT, true, true, true, false, false>(e, a, st) : launch_one<R, G, NT, false, true, true, false, false>(e, a, st);
     }
@@ -664,22 +663,23 @@ int launch_rgf(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStr
     return B2S_E_INVALID;
 }
 
-template <int R, int G>
+template <int R, int G, int NT>
 int launch_rg(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
 {
     // the fast-accumulate variant is only built for the widest lanes (R = 8: D = 128 / 256 / 512)
-    if (R == 8 && a.fastacc) return launch_rgf<R, G, (R == 8)>(e, a, vert, final, st);
-    return launch_rgf<R, G, false>(e, a, vert, final, st);
+    if (R == 8 && a.fastacc) return launch_rgf<R, G, NT, (R == 8)>(e, a, vert, final, st);
+    return launch_rgf<R, G, NT, false>(e, a, vert, final, st);
 }
 
-template <int G>
+// NT threads per CTA = NT / G rows per band (b2s_wave_threads picks it on the host)
+template <int G, int NT>
 int launch_g(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
 {
     switch (e.R) {
-    case 2: return launch_rg<2, G>(e, a, vert, final, st);
-    case 4: return launch_rg<4, G>(e, a, vert, final, st);
-    case 6: return launch_rg<6, G>(e, a, vert, final, st);
-    case 8: return launch_rg<8, G>(e, a, vert, final, st);
+    case 2: return launch_rg<2, G, NT>(e, a, vert, final, st);
+    case 4: return launch_rg<4, G, NT>(e, a, vert, final, st);
+    case 6: return launch_rg<6, G, NT>(e, a, vert, final, st);
+    case 8: return launch_rg<8, G, NT>(e, a, vert, final, st);
     }
     b2s_set_error("wave: no kernel for R=%d G=%d", e.R, G);
     return B2S_E_UNSUPPORTED;
