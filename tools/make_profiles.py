@@ -17,8 +17,8 @@ TAG = sys.argv[1] if len(sys.argv) > 1 else "r01"
 
 # (object file, regex on the demangled kernel name, output name)
 KERNELS = [
-    ("sgbm_wave_g8.o", r"k_wave<8, 8, 256, false, true, false, true, true>", "k_wave_R8_G8_pass1"),
-    ("sgbm_wave_g8.o", r"k_wave<8, 8, 256, false, true, true, true, true>", "k_wave_R8_G8_pass2_wta"),
+    ("sgbm_wave_g8.o", r"k_wave<8, 8, 128, false, true, false, true, true>", "k_wave_R8_G8_pass1"),
+    ("sgbm_wave_g8.o", r"k_wave<8, 8, 128, false, true, true, true, true>", "k_wave_R8_G8_pass2_wta"),
     ("sgbm_wave_g8.o", r"k_wave<4, 8, 256, false, false, true, false, true>", "k_wave_R4_G8_sgbm_last"),
     ("sgbm_wave_g8.o", r"k_wave<8, 8, 256, false, true, true, false, false>", "k_wave_R8_G8_hh4_pass2_wta"),
     ("sgbm_cost.o", r"k_cost_fast<5, 16, false, true, 1>", "k_cost_fast_BS5"),
