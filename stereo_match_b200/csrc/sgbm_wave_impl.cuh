@@ -651,10 +651,9 @@ template <int R, int G, int NT, bool FA>
 int launch_rgf(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
 {
     const bool pad = e.D != e.Dp;
-    if (vert && !a.diag) {      // MODE_HH4 (built without the fast-accumulate variant)
-        if (FA) return launch_rgf<R, G, NT, false>(e, a, vert, final, st);
-        if (!final) return pad ? launch_one<R, G, NT, true, true, false, false, false>(e, a, st) : launch_one<R, G, NT, false, true, false, false, false>(e, a, st);
-        return pad ? launch_one<R, G, NT, true, true, true, false, false>(e, a, st) : launch_one<R, G, NT, false, true, true, false, false>(e, a, st);
+    if (vert && !a.diag) {      // MODE_HH4, first sweep of MODE_SGBM_3WAY
+        if (!final) return pad ? launch_one<R, G, NT, true, true, false, FA, false>(e, a, st) : launch_one<R, G, NT, false, true, false, FA, false>(e, a, st);
+        return pad ? launch_one<R, G, NT, true, true, true, FA, false>(e, a, st) : launch_one<R, G, NT, false, true, true, FA, false>(e, a, st);
     }
     if (vert && !final) return pad ? launch_one<R, G, NT, true, true, false, FA>(e, a, st) : launch_one<R, G, NT, false, true, false, FA>(e, a, st);
     if (vert && final) return pad ? launch_one<R, G, NT, true, true, true, FA>(e, a, st) : launch_one<R, G, NT, false, true, true, FA>(e, a, st);
