@@ -36,3 +36,21 @@ def random_case(seed):
     else:
         l, r = color_pair(w, h, maxd, 300 + seed)
     return kw, l, r
+
+
+def random_bm_case(seed):
+    """StereoBM as the reference calls it (minDisparity 0) with random window / range / filter settings."""
+    rng = np.random.default_rng(8000 + seed)
+    D = 16 * int(rng.integers(1, 11))
+    bs = int(rng.choice([5, 7, 9, 11, 13, 15, 17, 19, 21, 23, 27]))
+    setters = {}
+    if rng.random() < 0.7:
+        setters["preFilterCap"] = int(rng.integers(1, 64))
+    if rng.random() < 0.7:
+        setters["textureThreshold"] = int(rng.choice([0, 5, 10, 50, 300]))
+    if rng.random() < 0.7:
+        setters["uniquenessRatio"] = int(rng.choice([0, 5, 15, 30]))
+    w = int(rng.integers(bs + 2, D + bs + 200))
+    h = int(rng.integers(bs + 1, 140))
+    l, r = synth_pair(w, h, max(D, 8), seed=9500 + seed)
+    return D, bs, setters, l, r

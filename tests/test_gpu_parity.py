@@ -377,3 +377,44 @@ def test_sgbm_random_sweep(seed):
     got = m.compute(l, r)
     assert not m.overflowed(), "case left the guaranteed domain: %r" % (kw,)
     assert np.array_equal(got, want), "%d pixels differ for %r %r" % ((got != want).sum(), kw, l.shape)
+
+
+@pytest.mark.parametrize("seed", range(60))
+def test_bm_random_sweep(seed, cv2ref):
+    from random_cases import random_bm_case
+    D, bs, setters, l, r = random_bm_case(seed)
+    want = cv2ref.bm_compute(l, r, D, bs, **setters)
+    m = sm.StereoBM_create(numDisparities=D, blockSize=bs)
+    for k, val in setters.items():
+        getattr(m, "set" + k[0].upper() + k[1:])(val)
+    got = m.compute(l, r)
+    assert np.array_equal(got, want), "%d pixels differ for %r" % ((got != want).sum(), (D, bs, setters, l.shape))
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_stage_ops_random_sweep(seed, cv2ref):
+    """remap (1 / 3 channels), cvtColor, medianBlur, filterSpeckles, reprojectImageTo3D on random shapes."""
+    import cv2
+    rng = np.random.default_rng(600 + seed)
+    sh, sw = int(rng.integers(3, 90)), int(rng.integers(3, 150))
+    H, W = int(rng.integers(1, 80)), int(rng.integers(1, 140))
+    src = rng.integers(0, 256, (sh, sw, 3), dtype=np.uint8)
+    mx = (rng.random((H, W), dtype=np.float32) * (sw + 8) - 4).astype(np.float32)
+    my = (rng.random((H, W), dtype=np.float32) * (sh + 8) - 4).astype(np.float32)
+    assert np.array_equal(sm.remap(src, mx, my, sm.INTER_LINEAR), cv2.remap(src, mx, my, cv2.INTER_LINEAR))
+    g = np.ascontiguousarray(src[..., 0])
+    assert np.array_equal(sm.remap(g, mx, my, sm.INTER_LINEAR), cv2.remap(g, mx, my, cv2.INTER_LINEAR))
+    assert np.array_equal(sm.cvtColor(src, sm.COLOR_BGR2GRAY), cv2.cvtColor(src, cv2.COLOR_BGR2GRAY))
+    d = (rng.integers(-1, 60, (H, W)) * int(rng.integers(1, 17))).astype(np.int16)
+    if min(H, W) >= 1:
+        assert np.array_equal(sm.medianBlur(d, 3), cv2.medianBlur(d, 3))
+    for size, diff in ((int(rng.integers(0, 60)), int(rng.integers(0, 40))),):
+        a, b = d.copy(), d.copy()
+        sm.filterSpeckles(a, -16, size, diff)
+        cv2.filterSpeckles(b, -16, size, diff)
+        assert np.array_equal(a, b), (size, diff, d.shape)
+    Q = KITTI_Q.copy()
+    Q[3, 3] = float(rng.random())
+    for hm in (False, True):
+        assert np.array_equal(sm.reprojectImageTo3D(d, Q, handleMissingValues=hm).view(np.uint32),
+                              cv2.reprojectImageTo3D(d, Q, handleMissingValues=hm).view(np.uint32))

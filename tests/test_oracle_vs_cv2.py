@@ -148,3 +148,10 @@ def test_sgbm_port_random_sweep(seed, port):
     want = cv2.StereoSGBM_create(**kw).compute(l, r)
     got = port.sgbm_compute(l, r, **kw)
     assert np.array_equal(got, want), "%d pixels differ for %r %r" % ((got != want).sum(), kw, l.shape)
+
+
+@pytest.mark.parametrize("seed", range(30))
+def test_bm_port_random_sweep(seed, port, cv2ref):
+    from random_cases import random_bm_case
+    D, bs, setters, l, r = random_bm_case(seed)
+    assert np.array_equal(port.bm_compute(l, r, D, bs, **setters), cv2ref.bm_compute(l, r, D, bs, **setters)), (D, bs, setters, l.shape)
