@@ -1,8 +1,27 @@
 // sgbm_wave.cu -- host side of the fused wavefront aggregation (see sgbm_wave.cuh).
 #include "sgbm_wave.cuh"
 
+// L_r <= C + P2 and C <= blockSize^2 * (2*ftzero + 63) (Sobel channel BT cost <= 2*ftzero, raw channel <= 255 >> 2):
+// if S1 (<= 32767) plus four such terms cannot reach 65536, the packed sums never carry between the halves
+static int wave_fastacc(const SgbmEff& e)
+{
+    const long long bs = 2 * e.SW2 + 1;
+    const long long lmax = bs * bs * (2LL * e.ftzero + 63) * e.cn + e.P2;     // cn colour channels add up
+    return (4 * lmax <= 32768) ? 1 : 0;
+}
+static int wave_diag(const SgbmEff& e) { return (e.ndirs == 4 || e.ndirs == 3) ? 0 : 1; }
+
+// does the lean kernel (sgbm_wave8.cu) run the sweeps with vertical directions?
+static bool wave_lean(const SgbmEff& e)
+{
+    WaveArgs a;
+    a.diag = wave_diag(e); a.fastacc = wave_fastacc(e);
+    return b2s_wave8_ok(e, a, 1);
+}
+
 int b2s_wave_threads(const SgbmEff& e)
 {
+    if (wave_lean(e)) return b2s_wave8_rows_per_band(e) * e.G;
     if (e.G != 8) return 256;
     // the 8-path sweeps with the widest lanes run a little faster in 16-row bands (see sgbm_wave.cuh); otherwise take
     // 16-row bands only where 32-row bands would compute at least 5 % more rows (short images: the 3WAY stripes)
@@ -33,6 +52,7 @@ size_t b2s_wave_edge_bytes(const SgbmEff& e) { return edge_layout(e).total; }
 
 static int launch_pass(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st)
 {
+    if (b2s_wave8_ok(e, a, vert)) return b2s_launch_wave8(e, a, final, st);
     switch (e.G) {
     case 8: return b2s_wave_threads(e) == 128 ? b2s_launch_wave_g8s(e, a, vert, final, st) : b2s_launch_wave_g8(e, a, vert, final, st);
     case 16: return b2s_launch_wave_g16(e, a, vert, final, st);
@@ -59,15 +79,9 @@ int b2s_launch_wave(const SgbmEff& e, const uint16_t* cost, uint16_t* S, uint16_
     const int mul = 100 - e.uniq;
     a.magic = mul > 0 ? ((1ull << 40) + (unsigned long long)mul - 1) / (unsigned long long)mul : 0ull;
     a.nbands = l.nbands;
-    a.diag = (e.ndirs == 4 || e.ndirs == 3) ? 0 : 1;
+    a.diag = wave_diag(e);
     a.zero = 0u;
-    // L_r <= C + P2 and C <= blockSize^2 * (2*ftzero + 63) (Sobel channel BT cost <= 2*ftzero, raw channel <= 255 >> 2):
-    // if S1 (<= 32767) plus four such terms cannot reach 65536, the packed sums never carry between the halves
-    {
-        const long long bs = 2 * e.SW2 + 1;
-        const long long lmax = bs * bs * (2LL * e.ftzero + 63) * e.cn + e.P2;     // cn colour channels add up
-        a.fastacc = (4 * lmax <= 32768) ? 1 : 0;
-    }
+    a.fastacc = wave_fastacc(e);
     int rc;
     B2S_CUDA_CHECK(cudaMemsetAsync(disp2key, 0xff, (size_t)e.batch * e.H * e.W * sizeof(uint32_t), st));
     // pass 1: -> , down-right, down, down-left (MODE_HH4, MODE_SGBM_3WAY: -> , down)

@@ -58,3 +58,7 @@ int b2s_launch_wave_g8(const SgbmEff& e, const WaveArgs& a, int vert, int final,
 int b2s_launch_wave_g8s(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st);       // 128 threads
 int b2s_launch_wave_g16(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st);
 int b2s_launch_wave_g32(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st);
+// the lean kernel for R = 8, D = 16 G (sgbm_wave8.cu): sweeps with the three vertical directions
+bool b2s_wave8_ok(const SgbmEff& e, const WaveArgs& a, int vert);
+int b2s_wave8_rows_per_band(const SgbmEff& e);
+int b2s_launch_wave8(const SgbmEff& e, const WaveArgs& a, int final, cudaStream_t st);

@@ -1,0 +1,96 @@
+"""GPU parity of the lean wavefront kernel (stereo_match_b200/csrc/sgbm_wave8.cu): its domain is numDisparities = 128
+(8 lanes per pixel) and 256 (16 lanes), MODE_HH (both sweeps) and MODE_SGBM (first sweep), sums that cannot overflow.
+Checked bit-exactly against live cv2 4.13.0 and, for the aggregated volume, against the C restatement.  Shapes are
+chosen around the kernel's own edges: heights below / at / just above one and two 16-row bands, widths that are not
+multiples of the 4-pixel chunks of the band pipeline, rows shorter than the prefetch distance, batches.
+"""
+import numpy as np
+import pytest
+import torch
+
+import stereo_match_b200 as sm
+from stereo_match_b200.synth import synth_pair
+
+pytestmark = pytest.mark.gpu
+
+
+def _kw(D, mode, **over):
+    kw = dict(minDisparity=0, numDisparities=D, blockSize=5, P1=600, P2=2400, disp12MaxDiff=1, preFilterCap=63,
+              uniquenessRatio=15, speckleWindowSize=0, speckleRange=2, mode=mode)
+    kw.update(over)
+    return kw
+
+
+CASES = []
+for D in (128, 256):
+    for h in (1, 2, 15, 16, 17, 31, 32, 33, 49, 70):
+        for dw in (16, 17, 18, 19, 23, 37, 64, 131):
+            if (h * 7 + dw) % 3 == 0 or h in (17, 33):            # a third of the grid, every band edge
+                CASES.append((D, h, D + dw + 3, 1 if (h + dw) % 2 else 0))
+
+
+@pytest.mark.parametrize("D,h,w,mode", CASES, ids=["D%d-h%d-w%d-m%d" % c for c in CASES])
+def test_wave8_shapes_match_cv2(D, h, w, mode):
+    import cv2
+    kw = _kw(D, mode)
+    l, r = synth_pair(w, h, D, seed=D + 3 * h + w)
+    want = cv2.StereoSGBM_create(**kw).compute(l, r)
+    got = sm.StereoSGBM_create(**kw).compute(l, r)
+    assert np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_wave8_random_parameters(seed):
+    """P1 / P2 / uniqueness / disp12MaxDiff / blockSize / negative minDisparity sweeps inside the no-overflow domain."""
+    import cv2
+    rng = np.random.default_rng(4200 + seed)
+    D = int(rng.choice([128, 128, 256]))
+    bs = int(rng.choice([1, 3, 5]))
+    cap = int(rng.choice([15, 31, 63]))
+    cmax = bs * bs * (2 * (max(cap, 15) | 1) + 63)
+    P2 = int(rng.integers(8, max(9, 8192 - cmax)))                 # 4 * (cmax + P2) <= 32768: the summed fast path
+    P1 = int(rng.integers(1, P2))
+    minD = int(rng.choice([0, 0, 5, -7, -40]))
+    w = max(D + minD, 0) + int(rng.integers(20, 150)) + abs(min(minD, 0))
+    h = int(rng.integers(1, 60))
+    kw = _kw(D, int(rng.integers(0, 2)), blockSize=bs, preFilterCap=cap, P1=P1, P2=P2, minDisparity=minD,
+             uniquenessRatio=int(rng.choice([0, 5, 15, 40, 99])), disp12MaxDiff=int(rng.choice([0, 1, 3, 1000])),
+             speckleWindowSize=int(rng.choice([0, 50])))
+    l, r = synth_pair(w, h, max(D + minD, 8), seed=500 + seed)
+    want = cv2.StereoSGBM_create(**kw).compute(l, r)
+    m = sm.StereoSGBM_create(**kw)
+    got = m.compute(l, r)
+    assert not m.overflowed()
+    assert np.array_equal(got, want), "%d pixels differ for %r %r" % ((got != want).sum(), kw, l.shape)
+
+
+@pytest.mark.parametrize("D,h,w", [(128, 37, 190), (256, 21, 300)])
+def test_wave8_volume_matches_oracle(D, h, w, port):
+    """The aggregated S volume of the lean sweeps against the restatement (stage tap, every cell)."""
+    kw = _kw(D, 1)
+    l, r = synth_pair(w, h, D, seed=77)
+    _, Cw, Sw, _ = port.sgbm_compute(l, r, want_volumes=True, **kw)
+    m = sm.StereoSGBM_create(**kw)
+    m.keep_volumes(True)
+    got = m.compute(torch.from_numpy(l).cuda(), torch.from_numpy(r).cuda()).cpu().numpy()
+    cost, S, g = m.debug_volumes(1, h, w)
+    cost = cost[0, :, :, :D].cpu().numpy().astype(np.int32) & 0xffff
+    S = S[0, :, :, :D].cpu().numpy()
+    assert np.array_equal(cost + g["P2"], Cw.astype(np.int32)), "block cost differs"
+    assert np.array_equal(S, Sw), "%d cells of S differ" % (S != Sw).sum()
+    assert np.array_equal(got, port.sgbm_compute(l, r, **kw))
+
+
+def test_wave8_batch_equals_singles_and_is_deterministic():
+    """Many pairs in flight (bands of different pairs share SMs through the ticket order) == one pair at a time."""
+    kw = _kw(128, 1, speckleWindowSize=100)
+    pairs = [synth_pair(211, 53, 128, seed=s) for s in range(9)]
+    L = torch.from_numpy(np.stack([p[0] for p in pairs])).cuda()
+    R = torch.from_numpy(np.stack([p[1] for p in pairs])).cuda()
+    m = sm.StereoSGBM_create(**kw)
+    out = m.compute(L, R).cpu().numpy()
+    again = m.compute(L, R).cpu().numpy()
+    assert np.array_equal(out, again)
+    single = sm.StereoSGBM_create(**kw)
+    for i, (l, r) in enumerate(pairs):
+        assert np.array_equal(out[i], single.compute(l, r)), "pair %d" % i
