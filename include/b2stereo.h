@@ -172,6 +172,8 @@ B2S_API int b2s_pipeline(b2s_handle sgbm, const uint8_t* left_raw, const uint8_t
 #define B2S_DT_I16 1
 #define B2S_DT_I32 2
 #define B2S_DT_F32 3
+#define B2S_DT_U16 4   /* b2s_map2dto3d, b2s_wls_filter only */
+#define B2S_DT_F64 5   /* b2s_map2dto3d only */
 /* xyz: [batch][H][W][3] float32.  Q_host: 16 doubles, row-major, HOST pointer.
    disp_scale multiplies the disparity after conversion to float32 (1.0 = cv2's
    behaviour; 1/16 fuses project_points_3D's "/16.0", stereo_vision.py:204).
@@ -179,6 +181,13 @@ B2S_API int b2s_pipeline(b2s_handle sgbm, const uint8_t* left_raw, const uint8_t
 B2S_API int b2s_reproject(const void* disp, int dtype, int H, int W, int batch,
                   const double* Q_host, float disp_scale, int handle_missing,
                   float* scratch, float* xyz, void* stream);
+/* map2Dto3D of the reference (mapTo3D.py:35-56, called at :116): pinhole back-projection of a depth image in float64,
+   u = -(col - cx) * z / fx, v = (row - cy) * z / fy, z, for the pixels with pt2d > threshold.  pt2d, depth:
+   [batch][H][W] of the given B2S_DT_* type; xyz: [batch][H][W][3] float64 (NaN where the pixel fails the threshold);
+   npass: one device uint64, receives the number of passing pixels (the reference only works when all pass). */
+B2S_API int b2s_map2dto3d(const void* pt2d, int pt2d_dtype, const void* depth, int depth_dtype,
+                  int H, int W, int batch, double cx, double cy, double fx, double fy,
+                  double threshold, double* xyz, unsigned long long* npass, void* stream);
 /* src: [batch][sH][sW][cn] uint8 ; maps: [H][W] float32 shared by the batch */
 B2S_API int b2s_remap_u8(const uint8_t* src, int sH, int sW, int cn, const float* mapx,
                  const float* mapy, int H, int W, int batch, uint8_t* dst, void* stream);
@@ -196,6 +205,30 @@ B2S_API size_t b2s_compact_points_scratch_bytes(int H, int W, int batch);
 B2S_API int b2s_compact_points(const float* xyz, const void* disp, int disp_dtype, double lo, double hi,
                        const uint8_t* bgr, int H, int W, int batch, float* verts, uint8_t* rgb,
                        long long* offsets, void* scratch, void* stream);
+/* ---- disparity WLS filter (stereo_vision/stereo_vision.py:171-182, disparity_test.py:182-199) -------------------
+   Replaces cv2.ximgproc.createDisparityWLSFilter(...).filter(displ, gray_l, None, dispr).  PARITY UNPINNED: no
+   cv2.ximgproc exists in this image; the kernels are bit-exact with the restatement in oracle/wls_oracle.c.
+   The parameter rules of createDisparityWLSFilter(matcher) live in the host layer (stereo_match_b200/wls.py). */
+typedef struct b2s_wls* b2s_wls_handle;
+typedef struct {
+    int32_t roi_x, roi_y, roi_w, roi_h;  /* valid-disparity rectangle of the left view */
+    int32_t min_disp;                    /* pixels outside the rectangle get 16 * (min_disp - 1) */
+    int32_t use_confidence;              /* 1: LRC / depth-discontinuity confidence (needs disp_right) */
+    int32_t lrc_thresh;                  /* 24 */
+    int32_t radius;                      /* depth-discontinuity radius */
+    float roll_off;                      /* 0.001 */
+    float lambda, sigma;                 /* setLambda / setSigmaColor */
+    int32_t num_iter;                    /* 3 */
+    float attenuation;                   /* 0.25 */
+} b2s_wls_params;
+B2S_API int b2s_wls_create(b2s_wls_handle* out);
+B2S_API void b2s_wls_destroy(b2s_wls_handle h);
+/* disp_left, disp_right (may be NULL without confidence), out: [batch][H][W] int16; guide: [batch][H][W][cn] uint8,
+   cn = 1 or 3; conf_out (may be NULL): [batch][H][W] float32, the confidence map (0..255, 0 outside the rectangle).
+   The handle owns the guide-weight table and a workspace grown on demand; everything is enqueued on `stream`. */
+B2S_API int b2s_wls_filter(b2s_wls_handle h, const int16_t* disp_left, const int16_t* disp_right,
+                   const uint8_t* guide, int cn, int H, int W, int batch, const b2s_wls_params* params,
+                   int16_t* out, float* conf_out, void* stream);
 B2S_API int b2s_median3_i16(const int16_t* src, int H, int W, int batch, int16_t* dst, void* stream);
 /* in place; labels: device scratch of batch*H*W int32, counts likewise */
 B2S_API int b2s_filter_speckles(int16_t* img, int H, int W, int batch, int newVal,

@@ -8,13 +8,14 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "liboracle.so")
 _SRC = os.path.join(_HERE, "stereo_oracle.c")
+_SRCS = [_SRC, os.path.join(_HERE, "wls_oracle.c")]
 
 
 def build(force=False):
     """Compile the C restatement with gcc (seconds)."""
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(_SRC):
-        subprocess.check_call(["gcc", "-O2", "-shared", "-fPIC", "-fvisibility=hidden",
-                               "-o", _SO, _SRC, "-lm"])
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(s) for s in _SRCS):
+        subprocess.check_call(["gcc", "-O2", "-ffp-contract=off", "-shared", "-fPIC", "-fvisibility=hidden",
+                               "-o", _SO] + _SRCS + ["-lm"])
     return _SO
 
 
@@ -26,7 +27,7 @@ class SgbmParams(C.Structure):
 
 class BmParams(C.Structure):
     _fields_ = [(n, C.c_int) for n in (
-        "numDisparities", "blockSize", "preFilterCap", "textureThreshold", "uniquenessRatio")]
+        "numDisparities", "blockSize", "preFilterCap", "textureThreshold", "uniquenessRatio", "minDisparity")]
 
 
 _lib = None
@@ -121,15 +122,23 @@ def sgbm_path(Cvol, P1, P2, k):
 
 
 def bm_compute(left, right, numDisparities=64, blockSize=21, preFilterCap=31,
-               textureThreshold=10, uniquenessRatio=15):
+               textureThreshold=10, uniquenessRatio=15, speckleWindowSize=0, speckleRange=0, minDisparity=0,
+               disp12MaxDiff=-1):
     left = np.ascontiguousarray(left, np.uint8)
     right = np.ascontiguousarray(right, np.uint8)
     H, W = left.shape
-    p = BmParams(numDisparities, blockSize, preFilterCap, textureThreshold, uniquenessRatio)
+    if 0 <= disp12MaxDiff < 100000:
+        raise ValueError("oracle: StereoBM's left-right check is only restated for disp12MaxDiff < 0 (off) or so large "
+                         "that it never rejects (the ximgproc factories set 1000000)")
+    p = BmParams(numDisparities, blockSize, preFilterCap, textureThreshold, uniquenessRatio, minDisparity)
     disp = np.empty((H, W), np.int16)
     rc = lib().orc_bm_compute(_p(left), _p(right), H, W, C.byref(p), _p(disp))
     if rc != 0:
         raise ValueError("oracle: bad BM parameters")
+    # cv2 4.13.0 StereoBM: the speckle range is passed to filterSpeckles unscaled (StereoSGBM passes 16 * range) and
+    # a negative range skips the filter (probed: tests/test_oracle_vs_cv2.py)
+    if speckleWindowSize > 0 and speckleRange >= 0:
+        disp = filter_speckles(disp, (minDisparity - 1) * 16, speckleWindowSize, speckleRange)
     return disp
 
 
@@ -171,3 +180,29 @@ def bgr2gray(bgr):
     out = np.empty(bgr.shape[:2], np.uint8)
     lib().orc_bgr2gray(_p(bgr), C.c_size_t(out.size), _p(out))
     return out
+
+
+class WlsParams(C.Structure):
+    _fields_ = [("roi_x", C.c_int), ("roi_y", C.c_int), ("roi_w", C.c_int), ("roi_h", C.c_int), ("min_disp", C.c_int),
+                ("use_confidence", C.c_int), ("lrc_thresh", C.c_int), ("radius", C.c_int), ("roll_off", C.c_float),
+                ("lambda_", C.c_float), ("sigma", C.c_float), ("num_iter", C.c_int), ("attenuation", C.c_float)]
+
+
+def wls_filter(disp_left, disp_right, guide, roi, min_disp=0, use_confidence=True, lambda_=8000.0, sigma=1.0,
+               lrc_thresh=24, radius=5, roll_off=0.001, num_iter=3, attenuation=0.25):
+    """oracle/wls_oracle.c (PARITY UNPINNED restatement of cv2.ximgproc's DisparityWLSFilter) -> (filtered int16,
+    confidence float32)."""
+    dl = np.ascontiguousarray(disp_left, np.int16)
+    dr = np.ascontiguousarray(disp_right, np.int16) if disp_right is not None else None
+    g = np.ascontiguousarray(guide, np.uint8)
+    H, W = dl.shape
+    cn = 1 if g.ndim == 2 else g.shape[2]
+    p = WlsParams(int(roi[0]), int(roi[1]), int(roi[2]), int(roi[3]), int(min_disp), int(bool(use_confidence)),
+                  int(lrc_thresh), int(radius), float(roll_off), float(lambda_), float(sigma), int(num_iter),
+                  float(attenuation))
+    out = np.empty((H, W), np.int16)
+    conf = np.empty((H, W), np.float32)
+    rc = lib().orc_wls_filter(_p(dl), _p(dr), _p(g), cn, H, W, C.byref(p), _p(out), _p(conf))
+    if rc != 0:
+        raise ValueError("oracle: bad WLS arguments")
+    return out, conf

@@ -479,7 +479,7 @@ ORC_API void orc_sgbm_geometry(const orc_sgbm_params* p, int W, int* out8)
 }
 
 /* ------------------------------------------------------------------ */
-/* StereoBM.compute, minDisparity = 0, XSOBEL prefilter */
+/* StereoBM.compute, XSOBEL prefilter, any minDisparity  */
 /* ------------------------------------------------------------------ */
 static void bm_prefilter(const uint8_t* I, int H, int W, int ftzero, uint8_t* P)
 {
@@ -500,57 +500,73 @@ static void bm_prefilter(const uint8_t* I, int H, int W, int ftzero, uint8_t* P)
 
 typedef struct {
     int numDisparities, blockSize, preFilterCap, textureThreshold, uniquenessRatio;
+    int minDisparity;     /* 0 in every direct call of the reference; -(D - 1) for the right-view matcher of
+                             cv2.ximgproc.createRightMatcher (stereo_vision/stereo_vision.py:171,179) */
 } orc_bm_params;
 
+/* General minDisparity (probed against cv2 4.13.0 for negative, zero and positive values, tests/test_oracle_vs_cv2.py):
+ *   lofs = max(D-1+minD, 0), rofs = -min(D-1+minD, 0), width1 = W - rofs - D + 1, FILTERED = (minD-1)*16;
+ *   output columns X = x + lofs for x in [0, width1), restricted to the valid rectangle
+ *   [max(0, minD+D-1) + r, W - r) x [r, H - r);
+ *   window column x+k of the left image is clamped to the image, the right image is read at
+ *   clamp(x+k, -rofs, W-D-rofs) + rofs + j for the internal index j = D-1-(d-minD): ONE clamp for all disparities, so
+ *   near the right border (negative minD) the right window stops moving while the left one goes on (cv2 quirk);
+ *   candidates are scanned from the largest disparity down with strict '<'. */
 ORC_API int orc_bm_compute(const uint8_t* left, const uint8_t* right, int H, int W,
                            const orc_bm_params* p, int16_t* disp)
 {
-    const int D = p->numDisparities, r = p->blockSize / 2, ftzero = p->preFilterCap;
-    const int FILTERED = -16;
+    const int D = p->numDisparities, r = p->blockSize / 2, ftzero = p->preFilterCap, minD = p->minDisparity;
+    const int FILTERED = (minD - 1) * 16;
     size_t n = (size_t)H * W;
     for (size_t i = 0; i < n; i++) disp[i] = (int16_t)FILTERED;
     if (D <= 0 || (D % 16) || !(p->blockSize & 1)) return -1;
+    const int lofs = imax(D - 1 + minD, 0), rofs = -imin(D - 1 + minD, 0), width1 = W - rofs - D + 1;
+    if (lofs >= W || rofs >= W || width1 < 1) return 0;
     uint8_t* PL = (uint8_t*)malloc(n), *PR = (uint8_t*)malloc(n);
     bm_prefilter(left, H, W, ftzero, PL);
     bm_prefilter(right, H, W, ftzero, PR);
-    int x0 = D - 1 + r, x1 = W - r, y0 = r, y1 = H - r;
-    if (x0 < x1 && y0 < y1) {
-        /* column sums of |PL - PR(d)| over the vertical window, per (x', d), rolling in y */
+    const int xmin = imax(0, minD + D - 1) + r, xmax = W - r, y0 = r, y1 = H - r;
+    if (xmin < xmax && y0 < y1) {
         int* sad = (int*)malloc(D * sizeof(int));
-        /* colsad[x'][d] for current y window; recomputed per row for clarity (oracle) */
-        int32_t* col = (int32_t*)malloc((size_t)W * D * sizeof(int32_t));
-        int32_t* tcol = (int32_t*)malloc((size_t)W * sizeof(int32_t));
+        const int ncol = width1 + 2 * r;                       /* window columns x = -r .. width1-1+r */
+        int32_t* col = (int32_t*)malloc((size_t)ncol * D * sizeof(int32_t));
+        int32_t* tcol = (int32_t*)malloc((size_t)ncol * sizeof(int32_t));
         for (int y = y0; y < y1; y++) {
-            for (int xx = x0 - r; xx < x1 + r; xx++) {
+            for (int c = 0; c < ncol; c++) {
+                const int xs = c - r;
+                const int lc = iclamp(xs, -lofs, W - 1 - lofs) + lofs;
+                const int rc = iclamp(xs, -rofs, W - D - rofs) + rofs;
                 int t = 0;
-                for (int yy = y - r; yy <= y + r; yy++) t += abs(PL[(size_t)yy * W + xx] - ftzero);
-                tcol[xx] = t;
-                for (int d = 0; d < D; d++) {
+                for (int yy = y - r; yy <= y + r; yy++) t += abs(PL[(size_t)yy * W + lc] - ftzero);
+                tcol[c] = t;
+                for (int j = 0; j < D; j++) {
                     int s = 0;
                     for (int yy = y - r; yy <= y + r; yy++)
-                        s += abs(PL[(size_t)yy * W + xx] - PR[(size_t)yy * W + xx - d]);
-                    col[(size_t)xx * D + d] = s;
+                        s += abs(PL[(size_t)yy * W + lc] - PR[(size_t)yy * W + rc + j]);
+                    col[(size_t)c * D + j] = s;
                 }
             }
-            for (int x = x0; x < x1; x++) {
+            for (int x = 0; x < width1; x++) {
+                const int X = x + lofs;
+                if (X < xmin || X >= xmax) continue;
                 int tsum = 0;
-                for (int d = 0; d < D; d++) sad[d] = 0;
-                for (int xx = x - r; xx <= x + r; xx++) {
-                    tsum += tcol[xx];
-                    for (int d = 0; d < D; d++) sad[d] += col[(size_t)xx * D + d];
+                for (int j = 0; j < D; j++) sad[j] = 0;
+                for (int c = x; c <= x + 2 * r; c++) {
+                    tsum += tcol[c];
+                    for (int j = 0; j < D; j++) sad[j] += col[(size_t)c * D + j];
                 }
-                int best = D - 1, minsad = sad[D - 1];
-                for (int d = D - 2; d >= 0; d--) if (sad[d] < minsad) { minsad = sad[d]; best = d; }
+                int best = 0, minsad = sad[0];                  /* internal order: first minimum = largest disparity */
+                for (int j = 1; j < D; j++) if (sad[j] < minsad) { minsad = sad[j]; best = j; }
                 if (tsum < p->textureThreshold) continue;
                 if (p->uniquenessRatio > 0) {
-                    int thresh = minsad + minsad * p->uniquenessRatio / 100, d;
-                    for (d = 0; d < D; d++) if (abs(d - best) > 1 && sad[d] <= thresh) break;
-                    if (d < D) continue;
+                    int thresh = minsad + minsad * p->uniquenessRatio / 100, j;
+                    for (j = 0; j < D; j++) if (abs(j - best) > 1 && sad[j] <= thresh) break;
+                    if (j < D) continue;
                 }
-                int pp = best > 0 ? sad[best - 1] : sad[best + 1];
-                int nn = best < D - 1 ? sad[best + 1] : sad[best - 1];
+                int pp = best < D - 1 ? sad[best + 1] : sad[best - 1];
+                int nn = best > 0 ? sad[best - 1] : sad[best + 1];
                 int dd = pp + nn - 2 * sad[best] + abs(pp - nn);
-                disp[(size_t)y * W + x] = (int16_t)((best * 256 + (dd ? (pp - nn) * 256 / dd : 0) + 15) >> 4);
+                disp[(size_t)y * W + X] = (int16_t)(((D - best - 1 + minD) * 256 + (dd ? (pp - nn) * 256 / dd : 0) + 15) >> 4);
             }
         }
         free(tcol); free(col); free(sad);

@@ -8,7 +8,7 @@ from ._lib import error, LIB_PATH
 from .engine import (StereoSGBM, StereoBM, StereoSGBM_create, StereoBM_create,
                      STEREO_SGBM_MODE_SGBM, STEREO_SGBM_MODE_HH, STEREO_SGBM_MODE_SGBM_3WAY,
                      STEREO_SGBM_MODE_HH4, INTER_LINEAR, COLOR_BGR2GRAY, CV_32F)
-from .ops import reprojectImageTo3D, remap, cvtColor, medianBlur, filterSpeckles, remap_gray, pipeline
+from .ops import map2Dto3D, reprojectImageTo3D, remap, cvtColor, medianBlur, filterSpeckles, remap_gray, pipeline
 from .cloud import point_cloud, write_ply
 from .stereo_vision import (compute_disparity, project_points_3D, parse_config_file,
                             create_left_matcher, createRightMatcher)
@@ -17,7 +17,7 @@ __all__ = [
     "error", "LIB_PATH", "StereoSGBM", "StereoBM", "StereoSGBM_create", "StereoBM_create",
     "STEREO_SGBM_MODE_SGBM", "STEREO_SGBM_MODE_HH", "STEREO_SGBM_MODE_SGBM_3WAY", "STEREO_SGBM_MODE_HH4",
     "INTER_LINEAR", "COLOR_BGR2GRAY", "CV_32F",
-    "reprojectImageTo3D", "remap", "cvtColor", "medianBlur", "filterSpeckles", "remap_gray", "pipeline",
+    "map2Dto3D", "reprojectImageTo3D", "remap", "cvtColor", "medianBlur", "filterSpeckles", "remap_gray", "pipeline",
     "point_cloud", "write_ply",
     "compute_disparity", "project_points_3D", "parse_config_file", "create_left_matcher", "createRightMatcher",
 ]

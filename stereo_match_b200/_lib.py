@@ -7,7 +7,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("B2S_LIB_PATH") or os.path.join(_HERE, "libb2stereo.so")   # override: A/B builds
 
 OK, E_INVALID, E_UNSUPPORTED, E_CUDA, E_NOMEM = 0, 1, 2, 3, 4
-DT_U8, DT_I16, DT_I32, DT_F32 = 0, 1, 2, 3
+DT_U8, DT_I16, DT_I32, DT_F32, DT_U16, DT_F64 = 0, 1, 2, 3, 4, 5
 
 
 class error(Exception):
@@ -28,6 +28,13 @@ class BmParams(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "numDisparities", "blockSize", "preFilterCap", "textureThreshold", "uniquenessRatio",
         "speckleWindowSize", "speckleRange")]
+
+
+class WlsParams(C.Structure):
+    _fields_ = [("roi_x", C.c_int32), ("roi_y", C.c_int32), ("roi_w", C.c_int32), ("roi_h", C.c_int32),
+                ("min_disp", C.c_int32), ("use_confidence", C.c_int32), ("lrc_thresh", C.c_int32), ("radius", C.c_int32),
+                ("roll_off", C.c_float), ("lambda_", C.c_float), ("sigma", C.c_float), ("num_iter", C.c_int32),
+                ("attenuation", C.c_float)]
 
 
 class SgbmGeometry(C.Structure):
@@ -56,6 +63,10 @@ PROTOTYPES = {
     "b2s_bm_create": (_i, [C.POINTER(BmParams), C.POINTER(_vp)]),
     "b2s_bm_compute": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "b2s_destroy": (None, [_vp]),
+    "b2s_wls_create": (_i, [C.POINTER(_vp)]),
+    "b2s_wls_destroy": (None, [_vp]),
+    "b2s_wls_filter": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, C.POINTER(WlsParams), _vp, _vp, _vp]),
+    "b2s_map2dto3d": (_i, [_vp, _i, _vp, _i, _i, _i, _i, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, _vp, _vp, _vp]),
     "b2s_reproject": (_i, [_vp, _i, _i, _i, _i, C.POINTER(C.c_double), C.c_float, _i, _vp, _vp, _vp]),
     "b2s_remap_u8": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "b2s_bgr2gray": (_i, [_vp, _sz, _vp, _vp]),

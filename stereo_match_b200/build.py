@@ -8,7 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_obj")
 LIB = os.path.join(HERE, "libb2stereo.so")
-SOURCES = ["api.cu", "sgbm_cost.cu", "sgbm_agg.cu", "sgbm_wave.cu", "sgbm_wave8.cu", "sgbm_wave_g8.cu", "sgbm_wave_g8s.cu", "sgbm_wave_g16.cu", "sgbm_wave_g32.cu", "sgbm_post.cu", "speckle.cu", "bm.cu", "geom.cu", "cloud.cu"]
+SOURCES = ["api.cu", "sgbm_cost.cu", "sgbm_agg.cu", "sgbm_wave.cu", "sgbm_wave8.cu", "sgbm_wave_g8.cu", "sgbm_wave_g8s.cu", "sgbm_wave_g16.cu", "sgbm_wave_g32.cu", "sgbm_post.cu", "speckle.cu", "bm.cu", "geom.cu", "cloud.cu", "wls.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "--fmad=false",            # reprojection must not contract fp64 mul+add (bitwise parity)
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "-Xptxas", "-v"]

@@ -409,7 +409,9 @@ extern "C" int b2s_bm_compute(b2s_handle h, const uint8_t* left, const uint8_t* 
     }
     cudaStream_t st = (cudaStream_t)stream;
     const size_t npix = (size_t)batch * H * W;
-    const bool speckle = h->bp.speckleWindowSize > 0;
+    // cv2 4.13.0 StereoBM: filterSpeckles(disp, FILTERED, speckleWindowSize, speckleRange) -- the range is NOT scaled by
+    // 16 here (only StereoSGBM scales it) and the filter is skipped for a negative range (probed against cv2)
+    const bool speckle = h->bp.speckleWindowSize > 0 && h->bp.speckleRange >= 0;
     size_t need = 2 * align_up(npix) + (speckle ? 2 * align_up(npix * sizeof(int32_t)) : 0);
     if ((rc = ensure_ws(h, need, st))) return rc;
     uint8_t* PL = (uint8_t*)h->ws;
@@ -418,7 +420,7 @@ extern "C" int b2s_bm_compute(b2s_handle h, const uint8_t* left, const uint8_t* 
     if (speckle) {
         int32_t* labels = (int32_t*)(PR + align_up(npix));
         int32_t* counts = (int32_t*)((char*)labels + align_up(npix * sizeof(int32_t)));
-        rc = b2s_launch_speckles(disp, H, W, batch, -16, h->bp.speckleWindowSize, 16 * h->bp.speckleRange, labels, counts, st);
+        rc = b2s_launch_speckles(disp, H, W, batch, -16, h->bp.speckleWindowSize, h->bp.speckleRange, labels, counts, st);
         if (rc) return rc;
     }
     h->last_stream = st;

@@ -340,11 +340,8 @@ int b2s_bm_run(const uint8_t* left, const uint8_t* right, int H, int W, int batc
         b2s_set_error("StereoBM: numDisparities*blockSize too large (needs %zu B shared memory)", smem);
         return B2S_E_UNSUPPORTED;
     }
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_bm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    // the attribute belongs to the current device's context: set it before every launch (cheap), not once per process
+    if (smem > 48 * 1024) B2S_CUDA_CHECK(cudaFuncSetAttribute(k_bm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int TR = 32;
     dim3 grid(b2s_cdiv(xe - xs, BM_TW), b2s_cdiv(ye - ys, TR), batch);
     k_bm<<<grid, BM_NT, smem, st>>>(PL, PR, e, TR, disp);

@@ -100,6 +100,69 @@ extern "C" int b2s_reproject(const void* disp, int dtype, int H, int W, int batc
     return B2S_E_INVALID;
 }
 
+// ---- map2Dto3D (reference mapTo3D.py:35-56, called at :116) ----------------------------------------------------
+// Pinhole back-projection of a DEPTH image, float64 like the reference's numpy expression:
+//   u = -(((col - cx) * z) / fx) ,  v = ((row - cy) * z) / fy ,  z      for the pixels with pt2D > threshold.
+// (Not expressible through reprojectImageTo3D: W = 1/z would be needed, which Q * [x, y, z, 1] cannot produce.)
+// The reference reshapes the masked result to the image shape, so it only works when every pixel passes; failing
+// pixels are written as NaN here and counted, the host wrapper raises numpy's reshape error for them.
+__device__ __forceinline__ double load_as_f64(const void* p, int dt, size_t i)
+{
+    switch (dt) {
+    case B2S_DT_U8:  return (double)((const uint8_t*)p)[i];
+    case B2S_DT_I16: return (double)((const int16_t*)p)[i];
+    case B2S_DT_I32: return (double)((const int32_t*)p)[i];
+    case B2S_DT_F32: return (double)((const float*)p)[i];
+    case B2S_DT_U16: return (double)((const uint16_t*)p)[i];
+    default:         return ((const double*)p)[i];
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_map2dto3d(const void* __restrict__ pt2d, int dt2d, const void* __restrict__ depth, int dtd, int H, int W,
+            double cx, double cy, double fx, double fy, double threshold, double* __restrict__ xyz,
+            unsigned long long* __restrict__ npass)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    const bool in = x < W;
+    bool pass = false;
+    if (in) {
+        const size_t i = ((size_t)blockIdx.z * H + y) * W + x;
+        pass = load_as_f64(pt2d, dt2d, i) > threshold;
+        double u = __longlong_as_double(0x7ff8000000000000ll), v = u, z = u;
+        if (pass) {
+            z = load_as_f64(depth, dtd, i);
+            u = -__ddiv_rn(__dmul_rn(__dsub_rn((double)x, cx), z), fx);
+            v = __ddiv_rn(__dmul_rn(__dsub_rn((double)y, cy), z), fy);
+        }
+        double* o = xyz + i * 3;
+        o[0] = u; o[1] = v; o[2] = z;
+    }
+    const unsigned n = __popc(__ballot_sync(0xffffffffu, pass));
+    if ((threadIdx.x & 31) == 0 && n) atomicAdd(npass, (unsigned long long)n);
+}
+
+extern "C" int b2s_map2dto3d(const void* pt2d, int pt2d_dtype, const void* depth, int depth_dtype, int H, int W, int batch,
+                             double cx, double cy, double fx, double fy, double threshold, double* xyz,
+                             unsigned long long* npass, void* stream)
+{
+    if (!pt2d || !depth || !xyz || !npass || H <= 0 || W <= 0 || batch <= 0) {
+        b2s_set_error("map2Dto3D: null pointer or empty image");
+        return B2S_E_INVALID;
+    }
+    if (pt2d_dtype < B2S_DT_U8 || pt2d_dtype > B2S_DT_F64 || depth_dtype < B2S_DT_U8 || depth_dtype > B2S_DT_F64) {
+        b2s_set_error("map2Dto3D: image types must be u8, u16, i16, i32, f32 or f64");
+        return B2S_E_INVALID;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    B2S_CUDA_CHECK(cudaMemsetAsync(npass, 0, sizeof(unsigned long long), st));
+    dim3 grid(b2s_cdiv(W, 256), H, batch);
+    k_map2dto3d<<<grid, 256, 0, st>>>(pt2d, pt2d_dtype, depth, depth_dtype, H, W, cx, cy, fx, fy, threshold, xyz, npass);
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}
+
 // A.7: fixed-point bilinear gather, 5 fractional bits, 15-bit weights, constant-0 border
 template <int CN>
 __global__ void __launch_bounds__(256)

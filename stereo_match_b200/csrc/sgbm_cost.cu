@@ -649,11 +649,8 @@ static int b2s_launch_cost_generic(const uint2* descL, const uint2* descR, const
         return B2S_E_UNSUPPORTED;
     }
     int TR = 64;
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    // per device / context attribute: set before every launch, not once per process
+    if (smem > 48 * 1024) B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid(b2s_cdiv(e.width1, TW), b2s_cdiv(e.H, TR), e.batch);
     k_cost<<<grid, COST_NT, smem, st>>>(descL, descR, e, TW, TR, cost, overflow_flag);
     B2S_LAUNCH_CHECK();

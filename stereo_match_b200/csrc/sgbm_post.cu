@@ -89,7 +89,8 @@ k_wta(const uint16_t* __restrict__ S, SgbmEff e, int16_t* __restrict__ disp, uin
     int16_t* drow = disp + (size_t)by * e.W;
     if (bad) { drow[x + e.minX1] = (int16_t)e.invalid; return; }
     int x2 = x + e.minX1 - best - e.minD;
-    atomicMin(disp2key + (size_t)by * e.W + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
+    // cv2: disp2cost starts at SHRT_MAX and is only replaced by a strictly smaller cost
+    if (minS < 32767) atomicMin(disp2key + (size_t)by * e.W + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
     int dq = best * 16;
     if (best > 0 && best < e.D - 1) {
         int denom2 = max((int)sm1 + (int)sp1 - 2 * minS, 1);

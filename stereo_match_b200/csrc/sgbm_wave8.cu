@@ -28,7 +28,6 @@ using wave::publish_progress;
 using wave::mbar_init;
 using wave::mbar_arrive;
 using wave::mbar_wait;
-using wave::cp_async_wait_all;
 using wave::group_min_x2;
 using wave::step;
 
@@ -50,10 +49,12 @@ struct Plan {
     static constexpr int ringC = ringB + RB * 4 * REC;                  // [RB][2][REC]   predecessor x+1
     static constexpr int scratch = ringC + RB * 2 * REC;                // [RB][REC]      (FINAL)
     static constexpr int ringmin = scratch + (FINAL ? RB * REC : 0);    // [RB][4] uint4  (-, m0, m1, m2) per consumer step
-    static constexpr int stagemin = ringmin + RB * 64;                  // [2][4] uint4
+    static constexpr int MINROW = 80;                                   // bytes per row of ringmin: 64 + 16, so that the four rows of a warp hit different banks
+    static constexpr int stagemin = ringmin + RB * MINROW;              // [2][4] uint4, 128-byte aligned (toggles by XOR 64)
+    static_assert((RB * MINROW) % 128 == 0, "stagemin must stay 128-byte aligned");
     static constexpr int zero = stagemin + 128;                         // [REC] zeros, then 16 zero bytes
-    static constexpr int misc = zero + REC + 16;                        // work item (int), mbarrier at +8
-    static constexpr int total = misc + 16 + ALIGN;                     // + slack to align the stage
+    static constexpr int misc = zero + REC + 16;                        // work item (int), step mbarrier at +8, stage mbarrier at +16
+    static constexpr int total = misc + 32 + ALIGN;                     // + slack to align the stage
 };
 
 __device__ __forceinline__ void lds128(unsigned addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d)
@@ -81,6 +82,11 @@ __device__ __forceinline__ void cp16(unsigned dst, const void* src)
 {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
+// this thread's earlier cp.async copies arrive on the mbarrier when they land (no scoreboard wait in the issuing warp)
+__device__ __forceinline__ void cp_async_arrive(unsigned bar)
+{
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void pf_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void ldg_rec(const uint4* p, uint32_t (&r)[8], int g)
 {
@@ -92,6 +98,12 @@ __device__ __forceinline__ void stg_rec(uint4* p, const uint32_t (&r)[8], int g)
     p[0] = make_uint4(r[0], r[1], r[2], r[3]);
     p[g] = make_uint4(r[4], r[5], r[6], r[7]);
 }
+// streaming store (evict-first in L2): the S1 volume is read again only by the next launch, long after it left L2
+__device__ __forceinline__ void stg_rec_cs(uint4* p, const uint32_t (&r)[8], int g)
+{
+    __stcs(p, make_uint4(r[0], r[1], r[2], r[3]));
+    __stcs(p + g, make_uint4(r[4], r[5], r[6], r[7]));
+}
 // per 16-bit half: 1 if (short)s + (short)k >= 1 else 0   (VIADDMNMX.S16x2.RELU)
 __device__ __forceinline__ uint32_t ge_flag_x2(uint32_t s, uint32_t k) { return __viaddmin_s16x2_relu(s, k, 0x00010001u); }
 
@@ -99,13 +111,14 @@ __device__ __forceinline__ uint32_t ge_flag_x2(uint32_t s, uint32_t k) { return 
 // Sv: register i packs S of the cells (16*lane + i, 16*lane + 8 + i).  scr: this row's scratch record (shared window).
 template <int G>
 __device__ __forceinline__ void wta8(const uint32_t (&Sv)[8], int lane, const SgbmEff& e, unsigned magic32, unsigned scr,
-                                     bool act, unsigned pix, int xcode, uint2* __restrict__ rec, uint32_t* __restrict__ disp2key)
+                                     bool act, unsigned pix, int xcode, uint2* __restrict__ rec, uint32_t* __restrict__ disp2key,
+                                     uint32_t k65536)
 {
     const unsigned dbase = (unsigned)lane * 16u;
     uint32_t key = 0xffffffffu;
 #pragma unroll
     for (int i = 0; i < 8; i++) {
-        const uint32_t k0 = Sv[i] * 65536u + (uint32_t)i;                    // S(lo) << 16 | cell   (IMAD)
+        const uint32_t k0 = Sv[i] * k65536 + (uint32_t)i;                    // S(lo) << 16 | cell   (IMAD: fma pipe)
         const uint32_t k1 = __byte_perm(Sv[i], 8 + i, 0x3254);               // S(hi) << 16 | cell
         key = __vimin3_u32(key, k0, k1);
     }
@@ -155,18 +168,19 @@ k_wave8(const SgbmEff e, const WaveArgs a)
     using P = Plan<G, NT, FINAL>;
     constexpr int RB = P::RB, REC = P::REC, RECV = REC / 16, CSB = G * 16;
     constexpr int XS = FINAL ? -1 : 1;                     // memory direction of the sweep (the final sweep is flipped)
-    static_assert(NT == 16 * G && (RB % 2) == 0, "chunk staging and the publication step assume NT == 16 G");
+    static_assert((RB % 2) == 0, "the publication step assumes an even number of rows per band");
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const unsigned sm_raw = (unsigned)__cvta_generic_to_shared(smem_raw);
     const unsigned sm0 = (sm_raw + P::ALIGN - 1) & ~(unsigned)(P::ALIGN - 1);
     unsigned char* const smem = smem_raw + (sm0 - sm_raw);
     int* const s_item = reinterpret_cast<int*>(smem + P::misc);
-    const unsigned bar_addr = sm0 + P::misc + 8;
+    const unsigned bar_addr = sm0 + P::misc + 8, sbar = sm0 + P::misc + 16;     // step barrier, stage barrier
     const int tid = (int)threadIdx.x;
 
     if (tid == 0) {
         *s_item = (int)atomicAdd(a.ticket, 1u);
         mbar_init(bar_addr, NT / 32);
+        mbar_init(sbar, NT);                          // every thread arrives once per staged chunk
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     for (int i = tid; i < 24 * REC / 16; i += NT) reinterpret_cast<uint4*>(smem + P::stage)[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -213,7 +227,7 @@ k_wave8(const SgbmEff e, const WaveArgs a)
         rA = sm0 + P::ringA + (g - 1) * 4 * REC + laneb;
         rB = sm0 + P::ringB + (g - 1) * 4 * REC + laneb;
         rC = sm0 + P::ringC + (g - 1) * 2 * REC + laneb;
-        rM = sm0 + P::ringmin + (g - 1) * 64;
+        rM = sm0 + P::ringmin + (g - 1) * P::MINROW;
     } else {
         rA = sm0 + P::stage + laneb;
         rB = sm0 + P::stage + 8 * REC + laneb;
@@ -221,25 +235,29 @@ k_wave8(const SgbmEff e, const WaveArgs a)
         rM = sm0 + P::stagemin;
     }
     const unsigned wA = sm0 + P::ringA + g * 4 * REC + laneb, wB = sm0 + P::ringB + g * 4 * REC + laneb,
-                   wC = sm0 + P::ringC + g * 2 * REC + laneb, wM = sm0 + P::ringmin + g * 64;
+                   wC = sm0 + P::ringC + g * 2 * REC + laneb, wM = sm0 + P::ringmin + g * P::MINROW;
     const unsigned zrec = sm0 + P::zero + laneb;
     const unsigned scr = sm0 + P::scratch + g * REC;
     const bool edgerow = has_below && g == gl;
     const bool wedge = has_below && (tid / 32) == (gl * G) / 32;        // this warp holds the band's last row
     const int pubthread = gl * G;
-
-    // chunk staging (consumer side): granule tid of [2 directions][4 records][RECV], the lower half of the CTA also
-    // moves direction 2, four threads of the upper half the minima
-    const int ck = tid / (NT / 2), crem = tid % (NT / 2), cr = crem / RECV;
+    // chunk staging (consumer side): the 12 * RECV 16-byte granules of [3 directions][4 records] are spread over the
+    // CTA (NT == 16 G: the lower half of the threads moves a second granule, direction 2), four threads add the minima;
+    // every thread's copies arrive on the stage mbarrier when they land (cp.async.wait_all would wait on the scoreboard
+    // the global loads of the step share: 6 % of the first sweep's stall samples)
+    static_assert(NT == 16 * G || NT == 32 * G, "chunk staging: 24 G granules over NT threads");
+    const int ck = tid / (4 * RECV), crem = tid % (4 * RECV), cr = crem / RECV;
+    const bool cvalid = tid < 12 * RECV, csecond = NT == 16 * G && tid < 4 * RECV;
     const uint4* csrc = eabove + (size_t)ck * wrecv + crem;             // chunk 0
     unsigned cdst = sm0 + P::stage + ck * 8 * REC + crem * 16;
-    unsigned cdstm = sm0 + P::stagemin + (unsigned)(tid - NT / 2) * 16u;
+    unsigned cdstm = sm0 + P::stagemin + (unsigned)(tid - (NT - 4)) * 16u;
     auto stage_chunk = [&](int c4) {                                    // records c4 .. c4+3 of the band above
-        if (c4 + cr < w1) {
+        if (cvalid && c4 + cr < w1) {
             cp16(cdst, csrc);
-            if (tid < NT / 2) cp16(cdst + 16 * REC, csrc + 2 * (size_t)wrecv);
+            if (csecond) cp16(cdst + 16 * REC, csrc + 2 * (size_t)wrecv);
         }
-        if (tid >= NT / 2 && tid < NT / 2 + 4 && c4 + (tid - NT / 2) < w1) cp16(cdstm, eabove_min + c4 + (tid - NT / 2));
+        if (tid >= NT - 4 && c4 + (tid - (NT - 4)) < w1) cp16(cdstm, eabove_min + c4 + (tid - (NT - 4)));
+        cp_async_arrive(sbar);
         csrc += 4 * RECV;
         cdst ^= 4u * REC;
         cdstm ^= 64u;
@@ -256,13 +274,13 @@ k_wave8(const SgbmEff e, const WaveArgs a)
         if (tid == 0) wait_progress(min(5, w1));
         __syncthreads();
         stage_chunk(0);
-        cp_async_wait_all();
-        __syncthreads();
     }
+    unsigned sphase = 0;                                               // parity of the stage barrier (first row's warp)
 
     const uint32_t p1x2 = (uint32_t)e.P1 * 0x10001u;
     const uint32_t p2m1x2 = (uint32_t)(e.P2 - e.P1) * 0x10001u;
     const unsigned magic32 = FINAL ? (unsigned)(((1ull << 32) + (unsigned)(100 - e.uniq) - 1ull) / (unsigned)(100 - e.uniq)) : 0u;
+    const uint32_t k65536 = 65536u + a.zero;            // opaque to the compiler: keeps the key build an IMAD (fma pipe)
     uint32_t nopad[8];
 #pragma unroll
     for (int i = 0; i < 8; i++) nopad[i] = 0u;
@@ -295,6 +313,8 @@ k_wave8(const SgbmEff e, const WaveArgs a)
             if (has_above && t + 2 < w1) stage_chunk(t + 2);                  // records t+2 .. t+5, first read at step t+2
         }
         if (J == 1 && has_above && tid == 0 && t + 3 < w1) wait_progress(min(t + 8, w1));     // for the chunk staged at t+1
+        // the warp of the band's first row reads records t .. t+3 from now on: their chunk (staged two steps ago) landed?
+        if (J == 0 && has_above && tid < 32 && t < w1) { mbar_wait(sbar, sphase); sphase ^= 1u; }
 
         // ---- operands of the row above (issued first: their latency hides behind the global loads) ---------
         uint32_t Lv[3][8], m0, m1, m2;
@@ -390,7 +410,6 @@ k_wave8(const SgbmEff e, const WaveArgs a)
                 }
             }
         }
-        if (J == 3 && has_above) cp_async_wait_all();
         // this warp's part of step t is visible: arrive, and keep working on what no other row needs
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(bar_addr);
@@ -404,10 +423,10 @@ k_wave8(const SgbmEff e, const WaveArgs a)
             Sv[i] = __viaddmin_u16x2(FINAL ? v + S1c[i] : v, Lh[i], 0x7fff7fffu);
         }
         if (FINAL) {
-            wta8<G>(Sv, lane, e, magic32, scr, act, pix, 0xffff - (xorg + XS * xs), a.rec, a.disp2key);
+            wta8<G>(Sv, lane, e, magic32, scr, act, pix, 0xffff - (xorg + XS * xs), a.rec, a.disp2key, k65536);
             if (dbgbase != nullptr && act) stg_rec(dbgbase + vcur, Sv, G);
         } else {
-            if (act) stg_rec(sbase + vcur, Sv, G);
+            if (act) stg_rec_cs(sbase + vcur, Sv, G);
         }
         vcur += (unsigned)(XS * RECV);
         pix += (unsigned)XS;
@@ -455,19 +474,28 @@ static int launch(const SgbmEff& e, const WaveArgs& a, cudaStream_t st)
 }  // namespace wave8
 
 // the lean kernel covers: R = 8 with every disparity cell real (D = 16 G), G = 8 or 16, the sweeps with all three
-// vertical directions, sums that cannot overflow (fastacc), a uniqueness ratio below 100, rows long enough for chunks
+// vertical directions, sums that cannot overflow (fastacc), a uniqueness ratio below 99 (the 32-bit reciprocal of
+// 100 - ratio must fit), rows long enough for chunks
 bool b2s_wave8_ok(const SgbmEff& e, const WaveArgs& a, int vert)
 {
     static const bool off = [] { const char* s = getenv("B2S_WAVE8"); return s && s[0] == '0'; }();
     if (off) return false;
-    return vert && a.diag && a.fastacc && e.R == 8 && e.D == e.Dp && (e.G == 8 || e.G == 16) && e.uniq < 100 &&
+    return vert && a.diag && a.fastacc && e.R == 8 && e.D == e.Dp && (e.G == 8 || e.G == 16) && e.uniq < 99 &&
            e.width1 >= 16 && e.uqle == 0;
 }
 
-int b2s_wave8_rows_per_band(const SgbmEff&) { return 16; }
+// rows per band (= threads / G).  G = 8: 16 rows (four CTAs of four warps per SM); B2S_WAVE8_ROWS=32 selects the
+// 32-row variant (half the edge traffic, two CTAs of eight warps per SM) for A/B measurements
+static int wave8_rows8()
+{
+    static const int rows = [] { const char* s = getenv("B2S_WAVE8_ROWS"); return (s && atoi(s) == 32) ? 32 : 16; }();
+    return rows;
+}
+int b2s_wave8_rows_per_band(const SgbmEff& e) { return e.G == 8 ? wave8_rows8() : 16; }
 
 int b2s_launch_wave8(const SgbmEff& e, const WaveArgs& a, int final, cudaStream_t st)
 {
+    if (e.G == 8 && wave8_rows8() == 32) return final ? wave8::launch<8, 256, true>(e, a, st) : wave8::launch<8, 256, false>(e, a, st);
     if (e.G == 8) return final ? wave8::launch<8, 128, true>(e, a, st) : wave8::launch<8, 128, false>(e, a, st);
     return final ? wave8::launch<16, 256, true>(e, a, st) : wave8::launch<16, 256, false>(e, a, st);
 }

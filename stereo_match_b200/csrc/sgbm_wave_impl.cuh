@@ -302,7 +302,7 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
         const uint32_t sp1 = best < e.D - 1 ? scr[b2s_cell_pos(best + 1, R, G, CSB != 16)] : 0u;
         const int xi = xreal + e.minX1;
         rec[rowpix + xi] = make_uint2((uint32_t)minS | (bad ? 0xffff0000u : (uint32_t)best << 16), sm1 | (sp1 << 16));
-        if (!bad) {
+        if (!bad && minS < 32767) {       // cv2: disp2cost starts at SHRT_MAX and is only replaced by a smaller cost
             const int x2 = xi - best - e.minD;
             atomicMin(disp2key + rowpix + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - xreal));
         }
@@ -636,11 +636,8 @@ template <int R, int G, int NT, bool PAD, bool VERT, bool FINAL, bool FA, bool D
 int launch_one(const SgbmEff& e, const WaveArgs& a, cudaStream_t st)
 {
     using P = Plan<R, G, NT, VERT, FINAL>;
-    static bool configured = false;
-    if (!configured) {
-        B2S_CUDA_CHECK(cudaFuncSetAttribute(k_wave<R, G, NT, PAD, VERT, FINAL, FA, DIAG>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
-        configured = true;
-    }
+    // the attribute belongs to the current device's context (one process may drive several GPUs): set it every launch
+    B2S_CUDA_CHECK(cudaFuncSetAttribute(k_wave<R, G, NT, PAD, VERT, FINAL, FA, DIAG>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
     const int grid = e.batch * a.nbands;
     k_wave<R, G, NT, PAD, VERT, FINAL, FA, DIAG><<<grid, NT, P::total, st>>>(e, a);
     B2S_LAUNCH_CHECK();

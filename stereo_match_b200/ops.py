@@ -51,6 +51,41 @@ def reprojectImageTo3D(disparity, Q, _3dImage=None, handleMissingValues=False, d
     return res
 
 
+_DT_ANY = dict(_DT)
+_DT_ANY.update({torch.uint16: _lib.DT_U16, torch.float64: _lib.DT_F64})
+
+
+def map2Dto3D(pt2D, ptd, cx, cy, fx, fy, threshold):
+    """map2Dto3D of the reference (mapTo3D.py:35-56, called at :116): 3-D points of a depth image,
+    u = -(col - cx) * z / fx, v = (row - cy) * z / fy, z, in float64 like the reference's numpy expression.
+
+    pt2D (H, W) selects the pixels (pt2D > threshold), ptd (H, W) is the depth map.  Returns (H, W, 3) float64.
+    Like the reference, which reshapes the masked result back to the image shape, it raises ValueError unless
+    every pixel passes the threshold.  Batched (B, H, W) input is accepted as an extension."""
+    a, kind = _to_device(pt2D, "pt2D")
+    z, _ = _to_device(ptd, "ptd")
+    if a.dtype == torch.bool:
+        a = a.to(torch.uint8)
+    if a.dtype not in _DT_ANY or z.dtype not in _DT_ANY:
+        raise error("map2Dto3D: images must be uint8, uint16, int16, int32, float32 or float64")
+    if a.shape != z.shape or a.dim() not in (2, 3):
+        raise error("map2Dto3D: pt2D and ptd must be (H, W) arrays of the same shape")
+    squeeze = a.dim() == 2
+    if squeeze:
+        a, z = a[None], z[None]
+    B, H, W = a.shape
+    out = torch.empty((B, H, W, 3), dtype=torch.float64, device=a.device)
+    npass = torch.zeros(1, dtype=torch.int64, device=a.device)
+    with torch.cuda.device(a.device):
+        _lib.check(_lib.load().b2s_map2dto3d(_ptr(a), _DT_ANY[a.dtype], _ptr(z), _DT_ANY[z.dtype], H, W, B,
+                                             float(cx), float(cy), float(fx), float(fy), float(threshold),
+                                             _ptr(out), _ptr(npass), _stream()))
+    n = int(npass.item())
+    if n != B * H * W:          # numpy's message for the reference's np.reshape(u3d, pt2D.shape)
+        raise ValueError("cannot reshape array of size %d into shape %s" % (n, str(tuple(a.shape[1:] if squeeze else a.shape))))
+    return _from_device(out[0] if squeeze else out, kind)
+
+
 def remap(src, map1, map2, interpolation=INTER_LINEAR, dst=None, borderMode=0, borderValue=0):
     """cv2.remap(src, mapx, mapy, cv2.INTER_LINEAR), BORDER_CONSTANT 0 (rectified_img_cal.py:253-254;
     SURVEY.md A.7).  src (H,W) / (H,W,3) uint8, or batched (B,H,W) is NOT inferred: pass

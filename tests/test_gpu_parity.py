@@ -418,3 +418,30 @@ def test_stage_ops_random_sweep(seed, cv2ref):
     for hm in (False, True):
         assert np.array_equal(sm.reprojectImageTo3D(d, Q, handleMissingValues=hm).view(np.uint32),
                               cv2.reprojectImageTo3D(d, Q, handleMissingValues=hm).view(np.uint32))
+
+
+def _ref_map2Dto3D(pt2D, ptd, cx, cy, fx, fy, threshold):
+    """The reference's own function body (mapTo3D.py:35-56), restated for the test."""
+    rows, cols = np.where(pt2D > threshold)
+    z = ptd[pt2D > threshold]
+    u3d = (cols - cx) * z / fx
+    v3d = (rows - cy) * z / fy
+    return np.stack([-np.reshape(u3d, pt2D.shape), np.reshape(v3d, pt2D.shape), np.reshape(z, pt2D.shape)], axis=2)
+
+
+@pytest.mark.parametrize("dt", [np.uint8, np.uint16, np.int16, np.int32, np.float32, np.float64])
+def test_map2Dto3D_matches_reference_expression(dt):
+    """mapTo3D.py:116: map2Dto3D(gray, depth, c_x, c_y, focal_x, focal_y, -1): bitwise float64."""
+    rng = np.random.default_rng(11)
+    gray = rng.integers(0, 256, (37, 53), dtype=np.uint8)
+    depth = (rng.random((37, 53)) * 200).astype(dt)
+    args = (319.5, 239.5, 525.0, 530.5, -1)
+    want = _ref_map2Dto3D(gray, depth, *args)
+    got = sm.map2Dto3D(gray, depth, *args)
+    assert got.dtype == np.float64 and got.shape == (37, 53, 3)
+    assert np.array_equal(got.view(np.uint64), want.view(np.uint64))
+    with pytest.raises(ValueError, match="cannot reshape array of size"):   # the reference fails the same way
+        sm.map2Dto3D(gray, depth, 319.5, 239.5, 525.0, 530.5, 100)
+    t = sm.map2Dto3D(torch.from_numpy(gray).cuda(), torch.from_numpy(depth).cuda() if dt != np.uint16 else
+                     torch.from_numpy(depth.astype(np.int32)).cuda(), *args)
+    assert t.is_cuda and np.array_equal(t.cpu().numpy().view(np.uint64), want.view(np.uint64))

@@ -112,6 +112,9 @@ BM_VECTORS = [
     (300, 250, 48, 11, {}),                                 # several column strips and row bands
     (260, 120, 160, 13, dict(uniquenessRatio=5)),           # 10 disparity warps
     (200, 110, 16, 19, dict(textureThreshold=200)),         # one warp per CTA
+    (220, 130, 32, 9, dict(speckleWindowSize=80, speckleRange=2)),      # speckle filter: range NOT scaled by 16
+    (220, 130, 32, 9, dict(speckleWindowSize=40, speckleRange=0)),
+    (220, 130, 32, 9, dict(speckleWindowSize=80, speckleRange=-1)),     # negative range: filter skipped
 ]
 
 # full-size configurations of BASELINE.json
