@@ -79,8 +79,9 @@ typedef struct b2s_sgbm_params {
     int32_t mode;
 } b2s_sgbm_params;
 
-/* cv2.StereoBM parameters that the reference path can reach (minDisparity is 0,
-   prefilter is XSOBEL, no LR check: SURVEY.md A.9) */
+/* cv2.StereoBM parameters that the reference path can reach (prefilter XSOBEL).  minDisparity is 0 in
+   the reference's own calls and -(numDisparities - 1) in the right-view matcher that cv2.ximgproc.createRightMatcher
+   derives from it (stereo_vision/stereo_vision.py:165-171,179); any value is bit-exact with cv2 4.13.0. */
 typedef struct b2s_bm_params {
     int32_t numDisparities;   /* >0, multiple of 16 */
     int32_t blockSize;        /* odd, 5..255 */
@@ -89,6 +90,9 @@ typedef struct b2s_bm_params {
     int32_t uniquenessRatio;  /* cv2 default 15 */
     int32_t speckleWindowSize;/* cv2 default 0 */
     int32_t speckleRange;     /* cv2 default 0 */
+    int32_t minDisparity;     /* cv2 default 0 */
+    int32_t disp12MaxDiff;    /* cv2 default -1 (off).  >= 4096 can never reject (the ximgproc factories set 1000000)
+                                 and is accepted; 0..4095 is B2S_E_UNSUPPORTED (cv2's validateDisparity is not restated) */
 } b2s_bm_params;
 
 typedef struct b2s_matcher* b2s_handle;

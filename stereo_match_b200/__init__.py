@@ -10,6 +10,8 @@ from .engine import (StereoSGBM, StereoBM, StereoSGBM_create, StereoBM_create,
                      STEREO_SGBM_MODE_HH4, INTER_LINEAR, COLOR_BGR2GRAY, CV_32F)
 from .ops import map2Dto3D, reprojectImageTo3D, remap, cvtColor, medianBlur, filterSpeckles, remap_gray, pipeline
 from .cloud import point_cloud, write_ply
+from .wls import DisparityWLSFilter, createDisparityWLSFilter, createDisparityWLSFilterGeneric
+from . import wls as ximgproc_wls
 from .stereo_vision import (compute_disparity, project_points_3D, parse_config_file,
                             create_left_matcher, createRightMatcher)
 
@@ -18,6 +20,18 @@ __all__ = [
     "STEREO_SGBM_MODE_SGBM", "STEREO_SGBM_MODE_HH", "STEREO_SGBM_MODE_SGBM_3WAY", "STEREO_SGBM_MODE_HH4",
     "INTER_LINEAR", "COLOR_BGR2GRAY", "CV_32F",
     "map2Dto3D", "reprojectImageTo3D", "remap", "cvtColor", "medianBlur", "filterSpeckles", "remap_gray", "pipeline",
-    "point_cloud", "write_ply",
+    "point_cloud", "write_ply", "DisparityWLSFilter", "createDisparityWLSFilter", "createDisparityWLSFilterGeneric",
+    "ximgproc",
     "compute_disparity", "project_points_3D", "parse_config_file", "create_left_matcher", "createRightMatcher",
 ]
+
+
+class _Ximgproc:
+    """Namespace mirroring the three cv2.ximgproc names the reference calls (stereo_vision/stereo_vision.py:171-172,
+    disparity_test.py:180-182), so that `cv2.ximgproc.X` becomes `stereo_match_b200.ximgproc.X`."""
+    createRightMatcher = staticmethod(createRightMatcher)
+    createDisparityWLSFilter = staticmethod(createDisparityWLSFilter)
+    createDisparityWLSFilterGeneric = staticmethod(createDisparityWLSFilterGeneric)
+
+
+ximgproc = _Ximgproc()

@@ -27,7 +27,7 @@ class SgbmParams(C.Structure):
 class BmParams(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "numDisparities", "blockSize", "preFilterCap", "textureThreshold", "uniquenessRatio",
-        "speckleWindowSize", "speckleRange")]
+        "speckleWindowSize", "speckleRange", "minDisparity", "disp12MaxDiff")]
 
 
 class WlsParams(C.Structure):

@@ -383,6 +383,12 @@ static int bm_validate(const b2s_bm_params& p)
     if (p.preFilterCap < 1 || p.preFilterCap > 63) { b2s_set_error("StereoBM: preFilterCap must be within 1..63"); return B2S_E_INVALID; }
     if (p.textureThreshold < 0) { b2s_set_error("StereoBM: texture threshold must be non-negative"); return B2S_E_INVALID; }
     if (p.uniquenessRatio < 0) { b2s_set_error("StereoBM: uniqueness ratio must be non-negative"); return B2S_E_INVALID; }
+    if (p.disp12MaxDiff >= 0 && p.disp12MaxDiff < 4096) {
+        b2s_set_error("StereoBM: disp12MaxDiff in 0..4095 (cv2's validateDisparity) is not supported; use -1 (off, the cv2 "
+                      "default) or a value that never rejects (cv2.ximgproc's factories set 1000000)");
+        return B2S_E_UNSUPPORTED;
+    }
+    if (p.minDisparity < -32000 || p.minDisparity > 32000) { b2s_set_error("StereoBM: minDisparity out of range"); return B2S_E_INVALID; }
     return B2S_OK;
 }
 
@@ -420,7 +426,7 @@ extern "C" int b2s_bm_compute(b2s_handle h, const uint8_t* left, const uint8_t* 
     if (speckle) {
         int32_t* labels = (int32_t*)(PR + align_up(npix));
         int32_t* counts = (int32_t*)((char*)labels + align_up(npix * sizeof(int32_t)));
-        rc = b2s_launch_speckles(disp, H, W, batch, -16, h->bp.speckleWindowSize, h->bp.speckleRange, labels, counts, st);
+        rc = b2s_launch_speckles(disp, H, W, batch, (h->bp.minDisparity - 1) * 16, h->bp.speckleWindowSize, h->bp.speckleRange, labels, counts, st);
         if (rc) return rc;
     }
     h->last_stream = st;

@@ -1,10 +1,20 @@
 // bm.cu -- StereoBM: x-Sobel prefilter + sliding-window SAD block matching.
 // Replaces cv2.StereoBM_create(numDisparities, blockSize).compute
-// (reference call site stereo_vision/stereo_vision.py:165-166,178).  minDisparity = 0 only.
+// (reference call site stereo_vision/stereo_vision.py:165-166,178) and, with minDisparity = -(D - 1), the right-view
+// matcher cv2.ximgproc.createRightMatcher builds from it (:171,179).
+//
+// Any minDisparity (restated in oracle/stereo_oracle.c, probed against cv2 4.13.0): disparity index dd = d - minD in
+// [0, D); the window column X' of the left image is compared with column min(X' - minD, W - 1) - dd of the right
+// image -- ONE clamp for all disparities, so for negative minD the right window stops moving in the last blockSize/2
+// valid columns while the left one goes on.  Valid output: X in [max(0, minD + D - 1) + r, min(W - r, W + minD)),
+// y in [r, H - r); everything else FILTERED = (minD - 1) * 16.  The fast kernel covers the columns whose windows are
+// not clamped, the generic kernel the (at most r) clamped ones.
 #include "common.cuh"
 
 struct BmEff {
     int H, W, batch, D, r, ftzero, tex, uniq;
+    int minD, filtered;       // FILTERED = (minD - 1) * 16
+    int xa, xb;               // output columns of this launch
 };
 
 // prefilter: rows are filtered with weights (1,2,1) and reflect-101 rows, except that for an
@@ -42,15 +52,15 @@ k_bm(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, BmEff e, in
     uint32_t* col = sm;                       // [CW][D]
     uint32_t* sad = col + (size_t)CW * D;     // [BM_TW][D]
     uint32_t* tcol = sad + (size_t)BM_TW * D; // [CW]
-    const int xs = e.D - 1 + r;               // first valid output column
-    const int x0 = xs + blockIdx.x * BM_TW;
+    const int x0 = e.xa + blockIdx.x * BM_TW;
     const int y0 = r + blockIdx.y * TR;
     const int y1 = min(y0 + TR, e.H - r);
     const size_t base = (size_t)blockIdx.z * e.H * e.W;
     const uint8_t* L = PL + base;
     const uint8_t* Rr = PR + base;
-    const int xmax = e.W - r;                 // one past last valid output column
+    const int xmax = e.xb;                    // one past the last output column of this launch
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int wlast = e.W - 1;
 
     for (int i = threadIdx.x; i < CW * D; i += BM_NT) col[i] = 0;
     for (int i = threadIdx.x; i < CW; i += BM_NT) tcol[i] = 0;
@@ -65,8 +75,9 @@ k_bm(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, BmEff e, in
             int xc = it / D, d = it - xc * D;
             int x = x0 - r + xc;
             if (x < e.W) {
-                int a = abs((int)L[(size_t)yin * e.W + x] - (int)Rr[(size_t)yin * e.W + x - d]);
-                if (sub) a -= abs((int)L[(size_t)yold * e.W + x] - (int)Rr[(size_t)yold * e.W + x - d]);
+                const int xr = min(x - e.minD, wlast) - d;        // one clamp for all disparities (see the file header)
+                int a = abs((int)L[(size_t)yin * e.W + x] - (int)Rr[(size_t)yin * e.W + xr]);
+                if (sub) a -= abs((int)L[(size_t)yold * e.W + x] - (int)Rr[(size_t)yold * e.W + xr]);
                 col[it] += a;
             }
         }
@@ -115,12 +126,12 @@ k_bm(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, BmEff e, in
                     bad = bad || __any_sync(0xffffffffu, hit);
                 }
                 if (lane == 0) {
-                    int out = -16;
+                    int out = e.filtered;
                     if (!bad) {
                         int p = best_d > 0 ? (int)sp[best_d - 1] : (int)sp[best_d + 1];
                         int n = best_d < D - 1 ? (int)sp[best_d + 1] : (int)sp[best_d - 1];
                         int dd = p + n - 2 * (int)best_s + abs(p - n);
-                        out = (best_d * 256 + (dd ? (p - n) * 256 / dd : 0) + 15) >> 4;
+                        out = ((best_d + e.minD) * 256 + (dd ? (p - n) * 256 / dd : 0) + 15) >> 4;
                     }
                     disp[base + (size_t)yout * e.W + x] = (int16_t)out;
                 }
@@ -160,13 +171,13 @@ k_bm_fast(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, BmEff 
     uint32_t* const badf = cand_d + NW * 32;                         // [32]
     int* const tsum_s = reinterpret_cast<int*>(badf + 32);           // [32]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nthreads = blockDim.x;
-    const int xs = D - 1 + r, xe = e.W - r;
-    const int x0 = xs + blockIdx.x * 32, x = x0 + lane;
+    const int xe = e.xb;
+    const int x0 = e.xa + blockIdx.x * 32, x = x0 + lane;
     const int y0 = r + blockIdx.y * TR, y1 = min(y0 + TR, e.H - r);
     const size_t base = (size_t)blockIdx.z * e.H * e.W;
     const int dlo = 16 * warp;
     const int xL0 = x0 - r;                                          // image column of Lrows byte 0
-    const int xR0 = x0 - r - (D - 1) - 8;                            // image column of Rrows byte 0
+    const int xR0 = x0 - r - (D - 1) - e.minD - 8;                   // image column of Rrows byte 0
     // byte offset of the right window start for d = dlo (largest start of this thread's range)
     const int smax = lane + (D - 1) - dlo + 8;
     const int rw = smax >> 2, rsh = (smax & 3) * 8;
@@ -267,12 +278,12 @@ k_bm_fast(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, BmEff 
             }
             __syncthreads();
             if (warp == 0 && x < xe) {
-                int out = -16;
+                int out = e.filtered;
                 if (!(tsum_s[lane] < e.tex) && !badf[lane]) {
                     const int p = (int)sad[(best_d > 0 ? best_d - 1 : best_d + 1) * 33 + lane];
                     const int n = (int)sad[(best_d < D - 1 ? best_d + 1 : best_d - 1) * 33 + lane];
                     const int dd = p + n - 2 * (int)best_s + abs(p - n);
-                    out = (best_d * 256 + (dd ? (p - n) * 256 / dd : 0) + 15) >> 4;
+                    out = ((best_d + e.minD) * 256 + (dd ? (p - n) * 256 / dd : 0) + 15) >> 4;
                 }
                 disp[base + (size_t)yout * e.W + x] = (int16_t)out;
             }
@@ -290,9 +301,9 @@ static int launch_bm_fast(const uint8_t* PL, const uint8_t* PR, const BmEff& e, 
     const int NW = e.D / 16;
     const size_t smem = (size_t)NS * (LBYTES + RBYTES) + ((size_t)e.D * 33 + 2 * NW * 32 + 64) * 4;
     if (smem > 48 * 1024) B2S_CUDA_CHECK(cudaFuncSetAttribute(k_bm_fast<BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int xs = e.D - 1 + e.r, xe = e.W - e.r, ys = e.r, ye = e.H - e.r;
+    const int ys = e.r, ye = e.H - e.r;
     const int TR = 96;
-    dim3 grid(b2s_cdiv(xe - xs, 32), b2s_cdiv(ye - ys, TR), e.batch);
+    dim3 grid(b2s_cdiv(e.xb - e.xa, 32), b2s_cdiv(ye - ys, TR), e.batch);
     k_bm_fast<BS><<<grid, 32 * NW, smem, st>>>(PL, PR, e, TR, disp);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
@@ -305,35 +316,8 @@ k_fill_i16(int16_t* p, size_t n, int16_t v)
     if (i < n) p[i] = v;
 }
 
-int b2s_bm_run(const uint8_t* left, const uint8_t* right, int H, int W, int batch, const b2s_bm_params& p,
-               uint8_t* PL, uint8_t* PR, int16_t* disp, cudaStream_t st)
+static int launch_bm_generic(const uint8_t* PL, const uint8_t* PR, const BmEff& e, int16_t* disp, cudaStream_t st)
 {
-    BmEff e;
-    e.H = H; e.W = W; e.batch = batch; e.D = p.numDisparities; e.r = p.blockSize / 2;
-    e.ftzero = p.preFilterCap; e.tex = p.textureThreshold; e.uniq = p.uniquenessRatio;
-    const size_t n = (size_t)batch * H * W;
-    k_fill_i16<<<b2s_cdiv((long long)n, 256), 256, 0, st>>>(disp, n, (int16_t)-16);
-    B2S_LAUNCH_CHECK();
-    const int xs = e.D - 1 + e.r, xe = W - e.r, ys = e.r, ye = H - e.r;
-    if (xs >= xe || ys >= ye) return B2S_OK;           // no valid pixel: everything FILTERED
-    dim3 gp(b2s_cdiv(W, 256), H, batch);
-    k_bm_prefilter<<<gp, 256, 0, st>>>(left, H, W, e.ftzero, PL);
-    B2S_LAUNCH_CHECK();
-    k_bm_prefilter<<<gp, 256, 0, st>>>(right, H, W, e.ftzero, PR);
-    B2S_LAUNCH_CHECK();
-    if (e.D <= 512) {
-        switch (p.blockSize) {
-        case 5: return launch_bm_fast<5>(PL, PR, e, disp, st);
-        case 7: return launch_bm_fast<7>(PL, PR, e, disp, st);
-        case 9: return launch_bm_fast<9>(PL, PR, e, disp, st);
-        case 11: return launch_bm_fast<11>(PL, PR, e, disp, st);
-        case 13: return launch_bm_fast<13>(PL, PR, e, disp, st);
-        case 15: return launch_bm_fast<15>(PL, PR, e, disp, st);
-        case 17: return launch_bm_fast<17>(PL, PR, e, disp, st);
-        case 19: return launch_bm_fast<19>(PL, PR, e, disp, st);
-        case 21: return launch_bm_fast<21>(PL, PR, e, disp, st);
-        }
-    }
     const int CW = BM_TW + 2 * e.r;
     size_t smem = ((size_t)CW * e.D + (size_t)BM_TW * e.D + CW) * sizeof(uint32_t);
     if (smem > 220 * 1024) {
@@ -343,8 +327,55 @@ int b2s_bm_run(const uint8_t* left, const uint8_t* right, int H, int W, int batc
     // the attribute belongs to the current device's context: set it before every launch (cheap), not once per process
     if (smem > 48 * 1024) B2S_CUDA_CHECK(cudaFuncSetAttribute(k_bm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int TR = 32;
-    dim3 grid(b2s_cdiv(xe - xs, BM_TW), b2s_cdiv(ye - ys, TR), batch);
+    dim3 grid(b2s_cdiv(e.xb - e.xa, BM_TW), b2s_cdiv(e.H - 2 * e.r, TR), e.batch);
     k_bm<<<grid, BM_NT, smem, st>>>(PL, PR, e, TR, disp);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
+}
+
+int b2s_bm_run(const uint8_t* left, const uint8_t* right, int H, int W, int batch, const b2s_bm_params& p,
+               uint8_t* PL, uint8_t* PR, int16_t* disp, cudaStream_t st)
+{
+    BmEff e;
+    e.H = H; e.W = W; e.batch = batch; e.D = p.numDisparities; e.r = p.blockSize / 2;
+    e.ftzero = p.preFilterCap; e.tex = p.textureThreshold; e.uniq = p.uniquenessRatio;
+    e.minD = p.minDisparity; e.filtered = (p.minDisparity - 1) * 16;
+    const size_t n = (size_t)batch * H * W;
+    k_fill_i16<<<b2s_cdiv((long long)n, 256), 256, 0, st>>>(disp, n, (int16_t)e.filtered);
+    B2S_LAUNCH_CHECK();
+    // cv2's geometry (stereobm.cpp: lofs / rofs / width1 and getValidDisparityROI), see the file header
+    const int span = e.D - 1 + e.minD;
+    const int lofs = span > 0 ? span : 0, rofs = span < 0 ? -span : 0, width1 = W - rofs - e.D + 1;
+    if (lofs >= W || rofs >= W || width1 < 1) return B2S_OK;
+    const int xmin = lofs + e.r, xend = (W - e.r < W + e.minD) ? W - e.r : W + e.minD, ys = e.r, ye = H - e.r;
+    if (xmin >= xend || ys >= ye) return B2S_OK;           // no valid pixel: everything FILTERED
+    dim3 gp(b2s_cdiv(W, 256), H, batch);
+    k_bm_prefilter<<<gp, 256, 0, st>>>(left, H, W, e.ftzero, PL);
+    B2S_LAUNCH_CHECK();
+    k_bm_prefilter<<<gp, 256, 0, st>>>(right, H, W, e.ftzero, PR);
+    B2S_LAUNCH_CHECK();
+    // columns whose window reaches past W - 1 + minD have a clamped right window: generic kernel
+    int xfast = xend;
+    if (e.minD < 0 && W + e.minD - e.r < xfast) xfast = W + e.minD - e.r;
+    if (xfast < xmin) xfast = xmin;
+    const bool fast = e.D <= 512 && p.blockSize >= 5 && p.blockSize <= 21;
+    int rc = B2S_OK;
+    if (fast && xfast > xmin) {
+        e.xa = xmin; e.xb = xfast;
+        switch (p.blockSize) {
+        case 5: rc = launch_bm_fast<5>(PL, PR, e, disp, st); break;
+        case 7: rc = launch_bm_fast<7>(PL, PR, e, disp, st); break;
+        case 9: rc = launch_bm_fast<9>(PL, PR, e, disp, st); break;
+        case 11: rc = launch_bm_fast<11>(PL, PR, e, disp, st); break;
+        case 13: rc = launch_bm_fast<13>(PL, PR, e, disp, st); break;
+        case 15: rc = launch_bm_fast<15>(PL, PR, e, disp, st); break;
+        case 17: rc = launch_bm_fast<17>(PL, PR, e, disp, st); break;
+        case 19: rc = launch_bm_fast<19>(PL, PR, e, disp, st); break;
+        case 21: rc = launch_bm_fast<21>(PL, PR, e, disp, st); break;
+        }
+        if (rc) return rc;
+    }
+    e.xa = fast ? xfast : xmin; e.xb = xend;
+    if (e.xa < e.xb) rc = launch_bm_generic(PL, PR, e, disp, st);
+    return rc;
 }

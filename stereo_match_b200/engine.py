@@ -207,16 +207,17 @@ def StereoSGBM_create(minDisparity=0, numDisparities=16, blockSize=3, P1=0, P2=0
 
 
 class StereoBM(_Matcher):
-    """Drop-in for cv2.StereoBM_create(numDisparities, blockSize) (minDisparity 0, XSOBEL prefilter)."""
+    """Drop-in for cv2.StereoBM_create(numDisparities, blockSize) (XSOBEL prefilter; any minDisparity; disp12MaxDiff
+    either off (< 0, the cv2 default) or so large that it never rejects, as cv2.ximgproc's factories set it)."""
 
     _FIELDS = ("numDisparities", "blockSize", "preFilterCap", "textureThreshold", "uniquenessRatio",
-               "speckleWindowSize", "speckleRange")
+               "speckleWindowSize", "speckleRange", "minDisparity", "disp12MaxDiff")
 
     def __init__(self, numDisparities=0, blockSize=21):
         super().__init__()
         self._p = _lib.BmParams(numDisparities=int(numDisparities) if numDisparities else 64, blockSize=int(blockSize),
                                 preFilterCap=31, textureThreshold=10, uniquenessRatio=15,
-                                speckleWindowSize=0, speckleRange=0)
+                                speckleWindowSize=0, speckleRange=0, minDisparity=0, disp12MaxDiff=-1)
         _lib.check(_lib.load().b2s_bm_create(C.byref(self._p), C.byref(self._h)))
 
     def _push(self):

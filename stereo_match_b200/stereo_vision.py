@@ -68,35 +68,53 @@ def create_left_matcher(disparity_settings, method="SGBM"):
 
 
 def createRightMatcher(left_matcher):
-    """cv2.ximgproc.createRightMatcher for an SGBM matcher (stereo_vision.py:171): the same
-    algorithm over the mirrored range, to be called as compute(right, left).
-    cv2.ximgproc is absent from this image, so the factory's parameter rule comes from
-    SURVEY.md 8(f)-1 and is unpinned; the negative-range engine underneath is parity-tested."""
+    """cv2.ximgproc.createRightMatcher (stereo_vision.py:171): the same algorithm over the mirrored disparity range,
+    to be called as compute(right, left).  StereoSGBM and StereoBM left matchers, like the original.
+
+    cv2.ximgproc is absent from this image, so the factory's parameter rule -- minDisparity = -(minD + D) + 1, same
+    D / blockSize (SGBM: P1, P2, mode, preFilterCap), uniquenessRatio = 0 (BM: textureThreshold = 0 as well),
+    disp12MaxDiff = 1000000, speckleWindowSize = 0 -- is restated from the opencv_contrib sources from memory and is
+    UNPINNED; the negative-range engines underneath are bit-exact with plain cv2.StereoSGBM / cv2.StereoBM."""
+    if isinstance(left_matcher, engine.StereoBM):
+        m = engine.StereoBM(numDisparities=left_matcher.getNumDisparities(), blockSize=left_matcher.getBlockSize())
+        m.setMinDisparity(-(left_matcher.getMinDisparity() + left_matcher.getNumDisparities()) + 1)
+        m.setTextureThreshold(0)
+        m.setUniquenessRatio(0)
+        m.setDisp12MaxDiff(1000000)
+        m.setSpeckleWindowSize(0)
+        return m
     if not isinstance(left_matcher, engine.StereoSGBM):
-        raise error("createRightMatcher: only StereoSGBM matchers are supported", 2)
+        raise error("createRightMatcher: only StereoSGBM and StereoBM matchers are supported", 2)
     p = {f: getattr(left_matcher, "get" + f[0].upper() + f[1:])() for f in engine.StereoSGBM._FIELDS}
     p['minDisparity'] = -(p['minDisparity'] + p['numDisparities']) + 1
     p['uniquenessRatio'] = 0
     p['disp12MaxDiff'] = 1000000
     p['speckleWindowSize'] = 0
+    p['speckleRange'] = 0
     return engine.StereoSGBM(**p)
 
 
 def compute_disparity(gray_l, gray_r, disparity_settings, method="SGBM", return_right=False):
-    """Disparity of a rectified grayscale pair (stereo_vision.py:132-184).
+    """Disparity of a rectified grayscale pair (stereo_vision.py:132-184): returns (displ, filtered_img) like the
+    reference, both int16 Q4 maps.
 
-    Returns (displ, filtered_img) like the reference.  `displ` is the int16 Q4 map of
-    left_matcher.compute and is bit-exact with cv2.  The reference's second output is the
-    cv2.ximgproc WLS-filtered map (:171-182); that filter is the next row of the scope table
-    (no oracle available in this image) and is not built yet, so
-    `filtered_img` is None.  With return_right=True the right-view map of :179 is returned
-    as a third element.
+    The reference's order of calls is kept: the right matcher is derived from the left one (:171), then
+    createDisparityWLSFilter(left_matcher) (:172) -- which, like the original, switches the left matcher's
+    uniqueness / LR / speckle filters off, so `displ` is the raw map the filter wants -- then lambda and sigma from
+    the settings (:174-175), both computes (:178-179) and wls_filter.filter(displ, gray_l, None, dispr) (:182).
+    `displ` and `dispr` are bit-exact with cv2 for these parameters; the ximgproc factories and the filter itself are
+    UNPINNED (no cv2.ximgproc in this image, see wls.py).  With return_right=True `dispr` is returned as a third element.
     """
+    from . import wls
     left_matcher = create_left_matcher(disparity_settings, method)
+    right_matcher = createRightMatcher(left_matcher)
+    wls_filter = wls.createDisparityWLSFilter(left_matcher)
+    wls_filter.setLambda(disparity_settings['lmbda'])
+    wls_filter.setSigmaColor(disparity_settings['sigma'])
     displ = left_matcher.compute(gray_l, gray_r)
-    filtered_img = None
+    dispr = right_matcher.compute(gray_r, gray_l)
+    filtered_img = wls_filter.filter(displ, gray_l, None, dispr)
     if return_right:
-        dispr = createRightMatcher(left_matcher).compute(gray_r, gray_l)
         return displ, filtered_img, dispr
     return displ, filtered_img
 

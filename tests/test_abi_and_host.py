@@ -73,6 +73,20 @@ def test_matcher_parameters_follow_reference(built_lib):
         == (120, 192, -144, 15, 2, 5, 1, 10)
     r = sm.createRightMatcher(sm.create_left_matcher(s))
     assert (r.getMinDisparity(), r.getUniquenessRatio(), r.getDisp12MaxDiff(), r.getSpeckleWindowSize()) == (-127, 0, 1000000, 0)
+    # method="BM" (stereo_vision.py:165-171): BM right matcher over the mirrored range; the WLS factory re-parametrises
+    # the left matcher like cv2.ximgproc.createDisparityWLSFilter does (restated from memory: unpinned)
+    lb = sm.create_left_matcher(s, method="BM")
+    rb = sm.createRightMatcher(lb)
+    assert (rb.getMinDisparity(), rb.getNumDisparities(), rb.getBlockSize(), rb.getTextureThreshold(), rb.getUniquenessRatio(),
+            rb.getDisp12MaxDiff()) == (-127, 128, 5, 0, 0, 1000000)
+    f = sm.createDisparityWLSFilter(lb)
+    assert (lb.getTextureThreshold(), lb.getUniquenessRatio(), lb.getDisp12MaxDiff(), lb.getSpeckleWindowSize()) == (0, 0, 1000000, 0)
+    assert f.getDepthDiscontinuityRadius() == 2 and f.getLRCthresh() == 24 and f.getLambda() == 8000.0
+    ls = sm.create_left_matcher(s)
+    f = sm.createDisparityWLSFilter(ls)
+    f.setLambda(80000); f.setSigmaColor(1.2)
+    assert (ls.getUniquenessRatio(), ls.getDisp12MaxDiff(), ls.getSpeckleWindowSize()) == (0, 1000000, 0)
+    assert (f.getDepthDiscontinuityRadius(), f.getLambda(), f.getSigmaColor()) == (3, 80000.0, 1.2)
     with pytest.raises(RuntimeError, match="Method not supported"):
         sm.create_left_matcher(s, method="ELAS")
     # the cv2 geometry rule agrees with the oracle's

@@ -264,26 +264,64 @@ def test_pipeline_one_call(cv2ref, cn):
     assert none is None and np.array_equal(disp2, wd)
 
 
-def test_compute_disparity_surface(cv2ref):
-    """The reference's compute_disparity (stereo_vision.py:132-184) with settings.ini values."""
+def test_compute_disparity_surface(cv2ref, port):
+    """The reference's compute_disparity (stereo_vision.py:132-184) with settings.ini values: (displ, filtered_img).
+
+    cv2.ximgproc.createDisparityWLSFilter(left_matcher) re-parametrises the left matcher (uniquenessRatio 0,
+    disp12MaxDiff 1000000, speckleWindowSize 0) BEFORE it computes; that rule, createRightMatcher's and the filter
+    are UNPINNED restatements (no cv2.ximgproc here) -- what IS pinned: the two raw maps against plain cv2 with those
+    parameters, and the filter kernels against oracle/wls_oracle.c."""
     settings = sm.parse_config_file(None)
     settings.update(window_size=5, num_disparities=64)
     l, r = synth_pair(200, 80, 64, seed=11)
-    displ, filtered = sm.compute_disparity(l, r, settings)
-    want = cv2ref.sgbm_compute(l, r, minDisparity=0, numDisparities=64, blockSize=5, P1=600, P2=2400, disp12MaxDiff=1,
-                               uniquenessRatio=15, speckleWindowSize=0, speckleRange=2, preFilterCap=63)
-    assert np.array_equal(displ, want) and filtered is None
+    displ, filtered, dispr = sm.compute_disparity(l, r, settings, return_right=True)
+    raw = dict(numDisparities=64, blockSize=5, P1=600, P2=2400, disp12MaxDiff=1000000, uniquenessRatio=0,
+               speckleWindowSize=0, preFilterCap=63)
+    assert np.array_equal(displ, cv2ref.sgbm_compute(l, r, minDisparity=0, speckleRange=2, **raw))
+    assert np.array_equal(dispr, cv2ref.sgbm_compute(r, l, minDisparity=-63, speckleRange=0, **raw))
+    want, _ = port.wls_filter(displ, dispr, l, (64, 0, 200 - 64, 80), min_disp=0, lambda_=80000, sigma=1.2, radius=3)
+    assert filtered.dtype == np.int16 and filtered.shape == l.shape and np.array_equal(filtered, want)
+    two = sm.compute_disparity(l, r, settings)
+    assert len(two) == 2 and np.array_equal(two[0], displ) and np.array_equal(two[1], filtered)
     with pytest.raises(RuntimeError, match="Method not supported"):
         sm.compute_disparity(l, r, settings, method="ELAS")
+    # method="BM" (stereo_vision.py:165-166): StereoBM left matcher, BM right matcher over the mirrored range
     settings["num_disparities"] = 32
-    displ_bm, _ = sm.compute_disparity(l, r, settings, method="BM")
-    assert np.array_equal(displ_bm, cv2ref.bm_compute(l, r, 32, 5))
-    # right-view matcher = plain SGBM over the mirrored range, compute(right, left)
-    _, _, dispr = sm.compute_disparity(l, r, settings, return_right=True)
-    want_r = cv2ref.sgbm_compute(r, l, minDisparity=-31, numDisparities=32, blockSize=5, P1=600, P2=2400,
-                                 disp12MaxDiff=1000000, uniquenessRatio=0, speckleWindowSize=0, speckleRange=2,
-                                 preFilterCap=63)
-    assert np.array_equal(dispr, want_r)
+    displ_bm, filt_bm, dispr_bm = sm.compute_disparity(l, r, settings, method="BM", return_right=True)
+    assert np.array_equal(displ_bm, cv2ref.bm_compute(l, r, 32, 5, textureThreshold=0, uniquenessRatio=0,
+                                                       disp12MaxDiff=1000000, speckleWindowSize=0))
+    assert np.array_equal(dispr_bm, cv2ref.bm_compute(r, l, 32, 5, minDisparity=-31, textureThreshold=0, uniquenessRatio=0,
+                                                       disp12MaxDiff=1000000, speckleWindowSize=0))
+    want_bm, _ = port.wls_filter(displ_bm, dispr_bm, l, (32 + 2, 2, 200 - 34 - 2, 80 - 4), min_disp=0, lambda_=80000,
+                                 sigma=1.2, radius=2)
+    assert np.array_equal(filt_bm, want_bm)
+
+
+@pytest.mark.parametrize("w,h,D,bs,minD", [(120, 50, 32, 9, -31), (140, 40, 16, 7, -10), (140, 40, 16, 7, -40), (140, 40, 16, 7, 5),
+                                            (140, 41, 48, 11, -47), (300, 80, 128, 15, -127), (90, 45, 64, 21, -63),
+                                            (100, 40, 16, 5, -200), (160, 60, 32, 23, -31), (60, 40, 32, 5, -31)])
+def test_bm_min_disparity_matches_cv2(w, h, D, bs, minD, cv2ref):
+    """StereoBM with minDisparity != 0 (the right-view matcher of createRightMatcher uses -(D - 1)), incl. the columns
+    where cv2 clamps the right window only (negative minDisparity) and the generic kernel (blockSize 23)."""
+    l, r = synth_pair(w, h, max(D + minD, 8), seed=5)
+    if minD < 0:
+        l, r = r, l
+    # (cv2 4.13.0 with minDisparity > 0 AND disp12MaxDiff >= 0 writes minDisparity stray pixels into the first row below
+    #  the valid rectangle -- an overrun of its own, not a contract; the ximgproc factories only produce minD <= 0)
+    for extra in ({}, dict(textureThreshold=0, uniquenessRatio=0, **(dict(disp12MaxDiff=1000000) if minD <= 0 else {}))):
+        m = sm.StereoBM_create(numDisparities=D, blockSize=bs)
+        m.setMinDisparity(minD)
+        for k, v in extra.items():
+            getattr(m, "set" + k[0].upper() + k[1:])(v)
+        want = cv2ref.bm_compute(l, r, D, bs, minDisparity=minD, **extra)
+        got = m.compute(l, r)
+        if minD > 0:        # cv2 also leaks a few computed values into the row below the valid rectangle (SURVEY A.9)
+            want[h - bs // 2:] = (minD - 1) * 16
+        assert np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
+    m = sm.StereoBM_create(numDisparities=D, blockSize=bs)
+    m.setDisp12MaxDiff(1)
+    with pytest.raises(sm.error, match="disp12MaxDiff"):
+        m.compute(l, r)
 
 
 def test_launch_counter_and_library_loaded():

@@ -115,6 +115,11 @@ BM_VECTORS = [
     (220, 130, 32, 9, dict(speckleWindowSize=80, speckleRange=2)),      # speckle filter: range NOT scaled by 16
     (220, 130, 32, 9, dict(speckleWindowSize=40, speckleRange=0)),
     (220, 130, 32, 9, dict(speckleWindowSize=80, speckleRange=-1)),     # negative range: filter skipped
+    # minDisparity != 0: the right-view matcher of cv2.ximgproc.createRightMatcher is StereoBM over [-(D-1), 0]
+    (150, 60, 32, 9, dict(minDisparity=-31, textureThreshold=0, uniquenessRatio=0, disp12MaxDiff=1000000)),
+    (150, 60, 48, 15, dict(minDisparity=-47)),
+    (150, 60, 16, 7, dict(minDisparity=-40)),                           # range entirely negative (rofs > 0)
+    (150, 60, 32, 23, dict(minDisparity=-31)),                          # generic kernel
 ]
 
 # full-size configurations of BASELINE.json
