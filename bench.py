@@ -33,7 +33,8 @@ W, H, D = 1242, 375, 128
 SGBM_KW = dict(minDisparity=0, numDisparities=D, blockSize=5, P1=600, P2=2400, disp12MaxDiff=1,
                uniquenessRatio=15, speckleWindowSize=100, speckleRange=2, preFilterCap=63, mode=1)
 GDE_PER_PAIR = W * H * D / 1e9
-WORKLOAD = "kitti_1242x375_D128_MODE_HH_remap+sgbm+speckle+reproject (BASELINE configs[2]/[4])"
+WORKLOAD = ("kitti_1242x375_D128_MODE_HH_remap+sgbm+speckle+reproject (BASELINE configs[2]/[4]; the left-view chain only: "
+            "the right-view matcher and the WLS filter of compute_disparity are not part of the BASELINE metric)")
 
 
 def measured_peaks():
@@ -55,56 +56,72 @@ def make_pairs(n, seed0=0):
 
 
 # --------------------------------------------------------------------------------------
-# reference arm / cpu_baseline: cv2 on the host cores, pair-parallel worker processes
+# reference arm / cpu_baseline: cv2 on the host cores, pair-parallel PERSISTENT worker processes
 # --------------------------------------------------------------------------------------
-def _cv2_worker(args):
-    npairs, seed = args
+def _cv2_worker(idx, k, nwarm, nsteps, barrier, out):
+    """One worker = one host core.  Everything that is not the per-pair chain -- synthetic input, rectification maps,
+    matcher object -- is built ONCE, before the timed region; then `nwarm` untimed and `nsteps` timed steps of k pairs."""
     import cv2
     from stereo_match_b200.synth import synth_pair, KITTI_Q, kitti_rect_maps
     cv2.setNumThreads(1)
-    l, r = synth_pair(W, H, D, seed=seed)
+    l, r = synth_pair(W, H, D, seed=1000 + idx)
     mx, my = kitti_rect_maps(W, H)
     m = cv2.StereoSGBM_create(**SGBM_KW)
-    t0 = time.perf_counter()
-    for _ in range(npairs):
+    Q = KITTI_Q.astype(np.float32)
+
+    def one_pair():
         lr = cv2.remap(l, mx, my, cv2.INTER_LINEAR)
         rr = cv2.remap(r, mx, my, cv2.INTER_LINEAR)
         d = m.compute(lr, rr)
-        cv2.reprojectImageTo3D(d.astype(np.float32) / 16.0, KITTI_Q.astype(np.float32))
-    return time.perf_counter() - t0
+        return cv2.reprojectImageTo3D(d.astype(np.float32) / 16.0, Q)
 
-
-def cv2_pairs_per_s(pool, cores, pairs_per_worker):
+    for _ in range(nwarm * k):
+        one_pair()
+    barrier.wait()                       # start of the timed region (the parent takes the time at the same barrier)
     t0 = time.perf_counter()
-    pool.map(_cv2_worker, [(pairs_per_worker, 1000 + i) for i in range(cores)])
+    for _ in range(nsteps * k):
+        one_pair()
+    out[idx] = time.perf_counter() - t0
+    barrier.wait()                       # end of the timed region
+
+
+def cv2_pairs_per_s(cores, k, nwarm, nsteps):
+    """pairs/s of cv2 over `cores` worker processes x cv2.setNumThreads(1) (StereoSGBM MODE_HH is serial inside OpenCV,
+    SURVEY.md section 6): cores * nsteps * k pairs between two barriers."""
+    import multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    barrier = ctx.Barrier(cores + 1)
+    out = ctx.Array("d", cores)
+    procs = [ctx.Process(target=_cv2_worker, args=(i, k, nwarm, nsteps, barrier, out), daemon=True) for i in range(cores)]
+    for p in procs:
+        p.start()
+    barrier.wait()
+    t0 = time.perf_counter()
+    barrier.wait()
     dt = time.perf_counter() - t0
-    return cores * pairs_per_worker / dt, dt
+    for p in procs:
+        p.join()
+    return cores * nsteps * k / dt, dt, max(out[:])
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    import multiprocessing as mp
     import cv2
     cores = os.cpu_count() or 1
-    ctx = mp.get_context("spawn")
-    with ctx.Pool(cores) as pool:
-        for _ in range(args.warmup):
-            cv2_pairs_per_s(pool, cores, 1)
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            cv2_pairs_per_s(pool, cores, 1)
-        dt = time.perf_counter() - t0
-    pairs = cores * args.steps
-    v = pairs / dt
+    k = args.ref_pairs
+    v, dt, slowest = cv2_pairs_per_s(cores, k, min(args.warmup, 1), args.steps)
     line = {
         "impl": "reference", "metric": "pairs_per_s", "value": v, "unit": "pairs/s", "gde_per_s": v * GDE_PER_PAIR,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int16", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "pairs_per_step": cores, "note": "cv2 %s, %d worker processes x cv2.setNumThreads(1)" % (cv2.__version__, cores)},
+        "config": {"workload": WORKLOAD, "pairs_per_step": cores * k,
+                   "note": "cv2 %s, %d persistent worker processes x cv2.setNumThreads(1); inputs, maps and matcher built "
+                           "once per worker before the timed region" % (cv2.__version__, cores)},
         "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "reference",
-                         "sample": "%d steps x %d pairs (one per worker process), remap x2 + StereoSGBM MODE_HH + reprojectImageTo3D" % (args.steps, cores)},
+                         "sample": "%d steps x %d pairs (%d per worker process), remap x2 + StereoSGBM MODE_HH + speckle + "
+                                   "reprojectImageTo3D, %.1f s wall (slowest worker %.1f s)" % (args.steps, cores * k, k, dt, slowest)},
         "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -159,6 +176,156 @@ class ClockSampler:
                     reasons.add(n)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------------------
+# cfg5 job, other configurations, latency
+# --------------------------------------------------------------------------------------
+def _synth_job_pair(seed):
+    from stereo_match_b200.synth import synth_pair
+    return synth_pair(W, H, D, seed=seed)
+
+
+def run_job(args, sm, torch, dist, dev, rank, world, chain, matcher, barrier, max_over_ranks, mx, my, Q):
+    """BASELINE configs[4]: a batch of `--job` synthetic KITTI-shape pairs (seeds 0 .. N-1, all distinct),
+    remap + SGBM + reprojection, sharded pair-parallel: rank r owns the contiguous block shard_range(N, r, world),
+    streams it from pinned host memory in batches of B, reads disparity and XYZ back, and checksums the XYZ bits of
+    every pair on the device.  One pair per rank (a different one on every rank) is checked against cv2."""
+    import multiprocessing as mp
+    from stereo_match_b200.batch import shard_range
+    B = args.batch
+    lo, hi = shard_range(args.job, rank, world)
+    n = hi - lo
+    with mp.get_context("spawn").Pool(max(1, (os.cpu_count() or 1) // world)) as pool:
+        pairs = pool.map(_synth_job_pair, range(lo, hi), chunksize=8)
+    Lall = torch.from_numpy(np.stack([p[0] for p in pairs])).pin_memory()
+    Rall = torch.from_numpy(np.stack([p[1] for p in pairs])).pin_memory()
+    del pairs
+    NS = 2
+    streams = [torch.cuda.Stream(device=dev) for _ in range(NS)]
+    ms = [matcher, sm.StereoSGBM_create(**SGBM_KW)]
+    Ls = [torch.empty((B, H, W), dtype=torch.uint8, device=dev) for _ in range(NS)]
+    Rs = [torch.empty((B, H, W), dtype=torch.uint8, device=dev) for _ in range(NS)]
+    disp_h = [torch.empty((B, H, W), dtype=torch.int16).pin_memory() for _ in range(NS)]
+    xyz_h = [torch.empty((B, H, W, 3), dtype=torch.float32).pin_memory() for _ in range(NS)]
+    sums = torch.zeros(n, dtype=torch.int64, device=dev)
+    pick = lo + (7919 * (rank + 1)) % n                       # the pair this rank checks against cv2
+    keep_pick = {}
+    keep = [None] * NS
+
+    def run(measure):
+        for bi, b0 in enumerate(range(0, n, B)):
+            k, nb = bi % NS, min(B, n - b0)
+            with torch.cuda.stream(streams[k]):
+                Ls[k][:nb].copy_(Lall[b0:b0 + nb], non_blocking=True)
+                Rs[k][:nb].copy_(Rall[b0:b0 + nb], non_blocking=True)
+                disp, xyz = chain(Ls[k][:nb], Rs[k][:nb], ms[k])
+                disp_h[k][:nb].copy_(disp, non_blocking=True)
+                xyz_h[k][:nb].copy_(xyz, non_blocking=True)
+                sums[b0:b0 + nb] = xyz.view(torch.int32).to(torch.int64).sum(dim=(1, 2, 3))
+                if measure and b0 <= pick - lo < b0 + nb:
+                    keep_pick["d"] = disp[pick - lo - b0].clone()
+                    keep_pick["x"] = xyz[pick - lo - b0].clone()
+                keep[k] = (disp, xyz)
+        for st in streams:
+            st.synchronize()
+
+    run(False)                                                # warm-up pass (workspaces, page-in)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    run(True)
+    e1.record()
+    barrier()
+    ms_job = max_over_ranks(e0.elapsed_time(e1))
+    import cv2
+    cv2.setNumThreads(max(1, (os.cpu_count() or 1) // world))
+    lr = cv2.remap(Lall[pick - lo].numpy(), mx, my, cv2.INTER_LINEAR)
+    rr = cv2.remap(Rall[pick - lo].numpy(), mx, my, cv2.INTER_LINEAR)
+    want = cv2.StereoSGBM_create(**SGBM_KW).compute(lr, rr)
+    wxyz = cv2.reprojectImageTo3D(want.astype(np.float32) / 16.0, Q)
+    ok = bool(np.array_equal(keep_pick["d"].cpu().numpy(), want) and
+              np.array_equal(keep_pick["x"].cpu().numpy().view(np.uint32), wxyz.view(np.uint32)))
+    ok = ok and int(sums[pick - lo].item()) == int(wxyz.view(np.int32).astype(np.int64).sum())
+    info = torch.tensor([1 if ok else 0, pick, int(sums.sum().item() & 0x7fffffffffffffff)], dtype=torch.int64, device=dev)
+    if world > 1:
+        allinfo = [torch.zeros_like(info) for _ in range(world)]
+        dist.all_gather(allinfo, info)
+    else:
+        allinfo = [info]
+    return {"pairs": args.job, "distinct": True, "seeds": "0..%d" % (args.job - 1), "batch": B, "shard": "contiguous (batch.shard_range)",
+            "seconds": ms_job / 1e3, "pairs_per_s": args.job / (ms_job / 1e3),
+            "h2d_bytes": int(args.job) * 2 * H * W, "d2h_bytes": int(args.job) * H * W * 14,
+            "parity_ok_per_rank": [bool(int(t[0].item())) for t in allinfo], "pair_checked_per_rank": [int(t[1].item()) for t in allinfo],
+            "xyz_checksum_per_rank": [int(t[2].item()) for t in allinfo]}
+
+
+def run_extras(sm, torch, chain, Ld, Rd, Lh, mx, my, Q, peak):
+    """cfg1 / cfg2 / cfg4 of BASELINE.json (device-resident, parity against cv2 on one pair, dominant-stage roofline)
+    and the cfg3 chain at batch 1 and 8 (a video frame at a time)."""
+    import cv2
+    from stereo_match_b200.synth import synth_pair
+    cv2.setNumThreads(os.cpu_count() or 1)
+
+    def timed(fn, iters):
+        fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / iters
+
+    other = {}
+    cfgs = (("cfg1_sgbm_640x480_D64_bs5", 640, 480, 64, 1, 128, dict(SGBM_KW, numDisparities=64, mode=0, speckleWindowSize=0)),
+            ("cfg4_hh_2864x1988_D256", 2864, 1988, 256, 4, 8, dict(SGBM_KW, numDisparities=256)))
+    for name, w, h, d, seed, nb, kw in cfgs:
+        l, r = synth_pair(w, h, d, seed=seed)
+        L = torch.from_numpy(np.stack([l] * nb)).cuda()
+        R = torch.from_numpy(np.stack([r] * nb)).cuda()
+        L[-1], R[-1] = torch.from_numpy(l[::-1].copy()).cuda(), torch.from_numpy(r[::-1].copy()).cuda()   # not all pairs alike
+        m = sm.StereoSGBM_create(**kw)
+        m.enable_timing(True)
+        ms = timed(lambda: m.compute(L, R), 3)
+        st = m.stage_ms()
+        out = m.compute(L, R)
+        ok = bool(np.array_equal(out[0].cpu().numpy(), cv2.StereoSGBM_create(**kw).compute(l, r)) and
+                  np.array_equal(out[-1].cpu().numpy(), cv2.StereoSGBM_create(**kw).compute(l[::-1].copy(), r[::-1].copy())))
+        g = m.geometry(w)
+        ndir = g["ndirs"]
+        # algorithmic bytes of the aggregation stage (SURVEY 8d): MODE_HH C r+r, S w+r; MODE_SGBM has no S1 round trip
+        alg = (8.0 if ndir == 8 else 4.0) * g["width1"] * h * d * nb
+        ach = alg / (st["aggregate"] / 1e3) / 1e9
+        other[name] = {"batch": nb, "ms_per_batch": ms, "pairs_per_s": nb / ms * 1e3, "gde_per_s": nb / ms * 1e3 * w * h * d / 1e9,
+                       "parity_ok": ok, "stage_ms": st,
+                       "roofline": {"kernel": "aggregation sweeps", "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
+                                    "frac": ach / peak, "algorithmic_bytes": alg}}
+        del m, L, R, out
+        torch.cuda.empty_cache()
+    l, r = synth_pair(1280, 720, 128, seed=2)
+    nb = 64
+    L = torch.from_numpy(np.stack([l] * nb)).cuda()
+    R = torch.from_numpy(np.stack([r] * nb)).cuda()
+    bm = sm.StereoBM_create(numDisparities=128, blockSize=15)
+    ms = timed(lambda: bm.compute(L, R), 3)
+    ok = bool(np.array_equal(bm.compute(L, R)[nb - 1].cpu().numpy(), cv2.StereoBM_create(numDisparities=128, blockSize=15).compute(l, r)))
+    other["cfg2_bm_1280x720_D128_bs15"] = {"batch": nb, "ms_per_batch": ms, "pairs_per_s": nb / ms * 1e3,
+                                           "gde_per_s": nb / ms * 1e3 * 1280 * 720 * 128 / 1e9, "parity_ok": ok,
+                                           "roofline": {"kernel": "k_bm_fast<15>", "bound": "integer ALU pipe (VABSDIFF4), image-sized HBM traffic",
+                                                        "achieved": 4.0 * 1280 * 720 * nb / (ms / 1e3) / 1e9, "peak": peak, "unit": "GB/s",
+                                                        "frac": 4.0 * 1280 * 720 * nb / (ms / 1e3) / 1e9 / peak}}
+    del bm, L, R
+    torch.cuda.empty_cache()
+    latency = {}
+    for nb in (1, 8):
+        m = sm.StereoSGBM_create(**SGBM_KW)
+        ms = timed(lambda: chain(Ld[:nb], Rd[:nb], m), 20)
+        latency["batch_%d" % nb] = {"ms_per_call": ms, "pairs_per_s": nb / ms * 1e3,
+                                    "what": "remap x2 + StereoSGBM MODE_HH + speckle + reprojectImageTo3D, device-resident, per call"}
+        del m
+    return other, latency
 
 
 # --------------------------------------------------------------------------------------
@@ -282,18 +449,75 @@ def run_b200(args):
     e2e_value = world * B * args.steps / (ms_e2e / 1e3)
     h2d = int(Lh.numel() + Rh.numel())
     d2h = int(disp_h[0].numel() * 2 + xyz_h[0].numel() * 4)
-    disp_h, xyz_h = disp_h[(args.steps - 1) % NS], xyz_h[(args.steps - 1) % NS]
+    last = (args.steps - 1) % NS
 
-    # ---- parity gate of the run: the result just produced against cv2 on pair 0 ------------
-    parity = None
-    if rank == 0 and not args.no_parity:
+    # ---- e2e variants, reported BESIDE the dense one (never instead of it): what comes back over the host link ----
+    # disp: the int16 disparity only (what matcher.compute returns);  cloud: disparity + the ordered compacted point
+    # cloud points_3d[mask] that disparity_calculation.py:308-321 actually consumes (mask = valid disparity)
+    e2e_variants = {}
+    if not args.no_variants:
+        verts_h = torch.empty((B * H * W, 3), dtype=torch.float32).pin_memory()
+        vdisp_h = [torch.empty((B, H, W), dtype=torch.int16).pin_memory() for _ in range(NS)]
+
+        def variant_step(i, mode):
+            k = i % NS
+            with torch.cuda.stream(streams[k]):
+                Ls[k].copy_(Lh, non_blocking=True)
+                Rs[k].copy_(Rh, non_blocking=True)
+                disp, xyz = chain(Ls[k], Rs[k], matchers[k])
+                vdisp_h[k].copy_(disp, non_blocking=True)
+                nbytes = disp.numel() * 2
+                if mode == "cloud":
+                    verts, _, offs = sm.point_cloud(disp, xyz, None, lo=0)      # one sync inside: the vertex count
+                    verts_h[: verts.shape[0]].copy_(verts, non_blocking=True)
+                    nbytes += verts.numel() * 4 + offs.numel() * 8
+                keep[k] = (disp, xyz)
+            return nbytes
+
+        for mode in ("disp", "cloud"):
+            vsteps = max(3, args.steps // 3)
+            for i in range(NS):
+                variant_step(i, mode)
+            e2e_sync()
+            barrier()
+            e0.record()
+            nb = 0
+            for i in range(vsteps):
+                nb = variant_step(i, mode)
+            for st in streams:
+                torch.cuda.current_stream().wait_stream(st)
+            e1.record()
+            barrier()
+            ms_v = max_over_ranks(e0.elapsed_time(e1))
+            e2e_variants[mode] = {"value": world * B * vsteps / (ms_v / 1e3), "unit": "pairs/s", "steps": vsteps,
+                                  "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(nb)}
+        del verts_h, vdisp_h
+
+    disp_h, xyz_h = disp_h[last], xyz_h[last]
+    # ---- parity gate of the run: EVERY rank checks pairs of the result it just produced against cv2 ------
+    parity, parity_detail = None, None
+    if not args.no_parity:
         import cv2
-        lr = cv2.remap(Lh[0].numpy(), mx, my, cv2.INTER_LINEAR)
-        rr = cv2.remap(Rh[0].numpy(), mx, my, cv2.INTER_LINEAR)
-        want = cv2.StereoSGBM_create(**SGBM_KW).compute(lr, rr)
-        wxyz = cv2.reprojectImageTo3D(want.astype(np.float32) / 16.0, Q)
-        parity = bool(np.array_equal(disp_h[0].numpy(), want) and
-                      np.array_equal(xyz_h[0].numpy().view(np.uint32), wxyz.view(np.uint32)))
+        cv2.setNumThreads(max(1, (os.cpu_count() or 1) // world))
+        picks = sorted({0, (17 * rank + 5) % B, B - 1})
+        ok = True
+        for i in picks:
+            lr = cv2.remap(Lh[i].numpy(), mx, my, cv2.INTER_LINEAR)
+            rr = cv2.remap(Rh[i].numpy(), mx, my, cv2.INTER_LINEAR)
+            want = cv2.StereoSGBM_create(**SGBM_KW).compute(lr, rr)
+            wxyz = cv2.reprojectImageTo3D(want.astype(np.float32) / 16.0, Q)
+            ok = ok and bool(np.array_equal(disp_h[i].numpy(), want) and
+                             np.array_equal(xyz_h[i].numpy().view(np.uint32), wxyz.view(np.uint32)))
+        flags = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+        if world > 1:
+            gathered = [torch.zeros_like(flags) for _ in range(world)]
+            dist.all_gather(gathered, flags)
+            per_rank = [bool(int(t.item())) for t in gathered]
+        else:
+            per_rank = [ok]
+        parity = all(per_rank)
+        parity_detail = {"per_rank": per_rank, "pairs_checked_per_rank": len(picks),
+                         "what": "int16 disparity equal and float32 XYZ bitwise equal to cv2 on the e2e result"}
 
     # ---- roofline of the dominant stage -----------------------------------------------------
     g = matcher.geometry(W)
@@ -312,7 +536,7 @@ def run_b200(args):
             if t.get("batch") == B:
                 traffic, traffic_src = t["avg_dram_bytes_per_launch"], "profiles/" + os.path.basename(fn)
                 break
-    roofline = {"bound": "hbm", "kernel": "k_wave (2 launches per step: forward sweep of 4 path directions, mirrored sweep of the "
+    roofline = {"bound": "hbm", "kernel": "k_wave8 (2 launches per step: forward sweep of 4 path directions, mirrored sweep of the "
                                           "other 4 with the winner-take-all fused)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes_step / nl,
@@ -320,15 +544,44 @@ def run_b200(args):
                 "stage_ms_per_step": {k: v / args.steps for k, v in stage_sum.items()},
                 "stage_share_of_step": {k: v / args.steps / (ms_total / args.steps) for k, v in stage_sum.items()}}
 
+    # ---- free the e2e buffers before the extra measurements ---------------------------------------------------
+    wsbytes = matcher.workspace_bytes(H, W, B)
+    del keep, Ls, Rs, matchers
+    torch.cuda.empty_cache()
+
+    # ---- cfg5 as BASELINE.json states it: --job N DISTINCT seeded pairs, sharded contiguously over the ranks -----
+    job = None
+    if args.job > 0:
+        job = run_job(args, sm, torch, dist, dev, rank, world, chain, matcher, barrier, max_over_ranks, mx, my, Q)
+
+    # ---- optional NCCL gather of the point clouds (north_star: "NCCL is used only to gather point clouds if requested")
+    gathered_cloud = None
+    if world > 1:
+        from stereo_match_b200.batch import gather_host_results
+        disp, xyz = chain(Ld[:8], Rd[:8])
+        torch.cuda.synchronize()
+        e0.record()
+        allxyz = gather_host_results(xyz, 8 * world, dst=0)          # CUDA tensors -> ncclAllGather over NVLink
+        e1.record()
+        torch.cuda.synchronize()
+        gms = max_over_ranks(e0.elapsed_time(e1))
+        if rank == 0:
+            gathered_cloud = {"pairs": 8 * world, "bytes": int(allxyz.numel() * 4), "ms": gms,
+                              "GBps": allxyz.numel() * 4 / gms / 1e6, "rank0_block_equal": bool(torch.equal(allxyz[:8], xyz))}
+        del allxyz, disp, xyz
+
+    # ---- the other BASELINE configurations and the small-batch ("video frame") latency, rank 0 of a 1-GPU run ------
+    other, latency = None, None
+    if rank == 0 and world == 1 and not args.no_extras:
+        other, latency = run_extras(sm, torch, chain, Ld, Rd, Lh, mx, my, Q, peak)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        import multiprocessing as mp
         cores = os.cpu_count() or 1
-        with mp.get_context("spawn").Pool(cores) as pool:
-            cv2_pairs_per_s(pool, cores, 1)                      # warm-up (imports, page-in)
-            v, dt = cv2_pairs_per_s(pool, cores, args.cpu_pairs)
+        v, dt, _ = cv2_pairs_per_s(cores, args.cpu_pairs, 1, 1)
         cpu = {"value": v, "unit": "pairs/s", "cores": cores, "kind": "reference",
-               "sample": "%d pairs (%d per worker process, cv2.setNumThreads(1) each), same chain, %.1f s" % (cores * args.cpu_pairs, args.cpu_pairs, dt)}
+               "sample": "%d pairs (%d per persistent worker process, cv2.setNumThreads(1) each, setup outside the timed "
+                         "region), same chain, %.1f s" % (cores * args.cpu_pairs, args.cpu_pairs, dt)}
 
     if rank == 0:
         line = {
@@ -336,11 +589,13 @@ def run_b200(args):
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int16", "data": "synthetic",
             "config": {"workload": WORKLOAD, "pairs_per_step_per_gpu": B, "parallelism": "pair-parallel x%d, no collective" % world,
-                       "l2": "per-step working set %.1f GB >> 126 MB L2 (no flush needed)" % (matcher.workspace_bytes(H, W, B) / 1e9)},
+                       "l2": "per-step working set %.1f GB >> 126 MB L2 (no flush needed)" % (wsbytes / 1e9)},
             "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps, "wall_ms_per_step": wall_e2e / args.steps,
-                    "how": "%d streams x 1 matcher handle each" % NS + ", pinned host buffers, H2D + kernels + D2H per step"},
-            "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "parity_ok": parity,
+                    "how": "%d streams x 1 matcher handle each" % NS + ", pinned host buffers, H2D + kernels + D2H per step",
+                    "variants": e2e_variants},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "parity_ok": parity, "parity": parity_detail,
+            "job": job, "gathered_cloud": gathered_cloud, "other_configs": other, "latency": latency,
         }
         emit(line)
     if world > 1:
@@ -378,9 +633,13 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=128, help="pairs per step per GPU")
     ap.add_argument("--cpu-pairs", type=int, default=40, help="cpu_baseline: pairs per worker process")
+    ap.add_argument("--ref-pairs", type=int, default=2, help="--impl reference: pairs per worker process and step")
     ap.add_argument("--e2e-streams", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-variants", action="store_true", help="skip the disparity-only / compacted-cloud e2e variants")
+    ap.add_argument("--no-extras", action="store_true", help="skip other_configs and the small-batch latency figures")
+    ap.add_argument("--job", type=int, default=0, help="cfg5 as BASELINE.json states it: this many DISTINCT pairs, sharded over the ranks")
     ap.add_argument("--traffic", type=float, default=None,
                     help="dram bytes per k_aggregate launch from the committed ncu capture (profiles/)")
     args = ap.parse_args()
