@@ -32,7 +32,8 @@ L = torch.from_numpy(np.stack([pairs[i][0] for i in range(lo, hi)])).cuda()
 R = torch.from_numpy(np.stack([pairs[i][1] for i in range(lo, hi)])).cuda()
 m = sm.StereoSGBM_create(**kw)
 disp = m.compute(L, R)
-xyz = sm.reprojectImageTo3D(disp, KITTI_Q, disp_scale=1.0 / 16.0)
+Q = KITTI_Q.astype(np.float32)
+xyz = sm.reprojectImageTo3D(disp, Q, disp_scale=1.0 / 16.0)
 alld = gather_host_results(disp, n, dst=0)            # CUDA tensors: ncclAllGather
 allx = gather_host_results(xyz, n, dst=0)
 if rank == 0:
@@ -42,7 +43,7 @@ if rank == 0:
         want = cv2.StereoSGBM_create(**kw).compute(*pairs[i])
         ok = ok and np.array_equal(alld[i].cpu().numpy(), want)
         ok = ok and np.array_equal(allx[i].cpu().numpy().view(np.uint32),
-                                   cv2.reprojectImageTo3D(want.astype(np.float32) / 16.0, KITTI_Q.astype(np.float32)).view(np.uint32))
+                                   cv2.reprojectImageTo3D(want.astype(np.float32) / 16.0, Q).view(np.uint32))
     print(json.dumps({"ok": bool(ok)}))
 dist.destroy_process_group()
 """
@@ -55,8 +56,8 @@ def test_nccl_gather_of_disparity_and_clouds(tmp_path):
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
                           "127.0.0.1", "--master-port", "29617", str(script)], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stderr[-3000:]
-    line = [ln for ln in out.stdout.splitlines() if ln.startswith("{")][-1]
-    assert json.loads(line)["ok"]
+    lines = [ln for ln in out.stdout.splitlines() if ln.startswith("{")]
+    assert lines and json.loads(lines[-1])["ok"], (out.stdout[-2000:], out.stderr[-2000:])
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
