@@ -13,14 +13,20 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 OBJ = os.path.join(ROOT, "stereo_match_b200", "_obj")
 OUT = os.path.join(ROOT, "profiles")
-TAG = sys.argv[1] if len(sys.argv) > 1 else "r01"
+TAG = sys.argv[1] if len(sys.argv) > 1 else "r02"
 
 # (object file, regex on the demangled kernel name, output name)
 KERNELS = [
-    ("sgbm_wave_g8.o", r"k_wave<8, 8, 128, false, true, false, true, true>", "k_wave_R8_G8_pass1"),
-    ("sgbm_wave_g8.o", r"k_wave<8, 8, 128, false, true, true, true, true>", "k_wave_R8_G8_pass2_wta"),
+    # the headline sweeps: the lean kernel, 128 threads (the instantiation bench.py and the ncu captures run)
+    ("sgbm_wave8.o", r"k_wave8<8, 128, false>", "k_wave8_G8_128_pass1"),
+    ("sgbm_wave8.o", r"k_wave8<8, 128, true>", "k_wave8_G8_128_pass2_wta"),
+    ("sgbm_wave8.o", r"k_wave8<16, 256, true>", "k_wave8_G16_256_pass2_wta"),
+    # the generic template (every other mode / range), 128-thread instantiations where the host picks them
+    ("sgbm_wave_g8s.o", r"k_wave<8, 8, 128, false, true, false, true, true>", "k_wave_R8_G8_128_pass1"),
+    ("sgbm_wave_g8s.o", r"k_wave<8, 8, 128, false, true, true, true, true>", "k_wave_R8_G8_128_pass2_wta"),
     ("sgbm_wave_g8.o", r"k_wave<4, 8, 256, false, false, true, false, true>", "k_wave_R4_G8_sgbm_last"),
     ("sgbm_wave_g8.o", r"k_wave<8, 8, 256, false, true, true, false, false>", "k_wave_R8_G8_hh4_pass2_wta"),
+    ("wls.o", r"k_wls_solve", "k_wls_solve"),
     ("sgbm_cost.o", r"k_cost_fast<5, 16, false, true, 1>", "k_cost_fast_BS5"),
     ("sgbm_cost.o", r"k_cost_fast<5, 16, false, true, 3>", "k_cost_fast_BS5_color"),
     ("cloud.o", r"k_cloud_write<short>", "k_cloud_write_i16"),
@@ -50,10 +56,10 @@ def sass_listings():
         for k, m in enumerate(hits[:2]):
             txt = subprocess.run(["cuobjdump", "-sass", "-fun", m, path], capture_output=True, text=True).stdout
             lines = [re.sub(r"\s*/\* 0x[0-9a-f]+ \*/\s*$", "", ln) for ln in txt.splitlines()
-                     if re.match(r"\s+/\*[0-9a-f]{4}\*/", ln) or "Function" in ln]
+                     if re.match(r"\s+/\*[0-9a-f]{4,5}\*/", ln) or "Function" in ln]
             ops = {}
             for ln in lines:
-                mm = re.match(r"\s+/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", ln)
+                mm = re.match(r"\s+/\*[0-9a-f]{4,5}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", ln)
                 if mm:
                     op = mm.group(1).split(".")[0]
                     ops[op] = ops.get(op, 0) + 1

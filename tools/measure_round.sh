@@ -4,7 +4,7 @@
 # 3. one full ncu capture each of k_wave (both sweeps), k_cost_fast, k_bm_fast  4. small-section capture of one whole step
 # Everything lands in gpurun_out/ (scratch); tools/make_profiles.py turns it into profiles/.
 # gpurun copies back at most 64 MiB: run it in parts (second argument: bench | ncu | all; default everything)
-TAG=${1:-r01}
+TAG=${1:-r02}
 PART=${2:-everything}
 O=gpurun_out
 mkdir -p $O
@@ -20,9 +20,18 @@ $NCU --metrics gpu__time_duration.sum -c 600 --csv --log-file $O/launches_$TAG.c
     python bench.py --steps 2 --warmup 3 --batch 128 --no-cpu --no-parity > $O/ncu.log 2>&1
 fi
 if want ncu; then
-$NCU --set full --import-source on -k regex:k_wave -s 2 -c 2 -o $O/wave_$TAG -f python tools/run_sgbm_once.py 128 2 > $O/ncu_wave.log 2>&1
+$NCU --set full --import-source on -k regex:k_wave8 -s 2 -c 2 -o $O/wave_$TAG -f python tools/run_sgbm_once.py 128 2 > $O/ncu_wave.log 2>&1
 $NCU --set full --import-source on -k regex:k_cost -s 1 -c 1 -o $O/cost_$TAG -f python tools/run_sgbm_once.py 128 2 > $O/ncu_cost.log 2>&1
 $NCU --set full --import-source on -k regex:k_bm_fast -s 1 -c 1 -o $O/bm_$TAG -f python tools/bench_configs.py cfg2 > $O/ncu_bm.log 2>&1
+fi
+if want sanitizer; then
+# memcheck + racecheck + synccheck of the band pipeline (mbarriers, cp.async staging, release/acquire
+# progress counters) on small parity cases of both wavefront kernels
+for tool in memcheck racecheck synccheck; do
+  timeout 1500 compute-sanitizer --tool $tool --error-exitcode 9 python -m pytest tests/test_gpu_wave8.py tests/test_gpu_parity.py \
+      -x -q -k "(wave8_shapes and (h17 or h33 or h1-)) or wave8_batch or test_sgbm_matches_oracle" > $O/sanitizer_${tool}_$TAG.log 2>&1
+  echo "exit code $?" >> $O/sanitizer_${tool}_$TAG.log
+done
 fi
 if want all; then
 $NCU --section SpeedOfLight --section LaunchStats --section Occupancy --section MemoryWorkloadAnalysis -s 30 -c 30 -o $O/all_$TAG -f \
