@@ -239,6 +239,16 @@ B2S_API int b2s_filter_speckles(int16_t* img, int H, int W, int batch, int newVa
                         int maxSpeckleSize, int maxDiff, int32_t* labels,
                         int32_t* counts, void* stream);
 
+/* No counterpart in the reference.  b2s_filter_speckles for callers that
+   cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): the labels / counts
+   scratch is a static device array inside the library (8 MiB per GPU that loads it, held until exit), so the call
+   allocates nothing.  Limit: batch*H*W <= B2S_SPECKLE_NOALLOC_MAX_PIXELS, larger calls return B2S_E_UNSUPPORTED.
+   All calls on a device share that scratch: calls that overlap on the GPU race -- keep them ordered (one stream, or
+   events between streams).  The first call on a device resolves the array's address (do it before a capture starts). */
+#define B2S_SPECKLE_NOALLOC_MAX_PIXELS (1 << 20)
+B2S_API int b2s_filter_speckles_noalloc(int16_t* img, int H, int W, int batch, int newVal,
+                        int maxSpeckleSize, int maxDiff, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

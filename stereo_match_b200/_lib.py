@@ -77,6 +77,7 @@ PROTOTYPES = {
     "b2s_compact_points": (_i, [_vp, _vp, _i, C.c_double, C.c_double, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "b2s_median3_i16": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "b2s_filter_speckles": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "b2s_filter_speckles_noalloc": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp]),
 }
 
 _lib = None

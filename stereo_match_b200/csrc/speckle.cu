@@ -173,3 +173,55 @@ int b2s_launch_speckles(int16_t* img, int H, int W, int batch, int newVal, int m
     B2S_LAUNCH_CHECK();
     return B2S_OK;
 }
+
+// ---- b2s_filter_speckles_noalloc: the same four kernels with a built-in scratch ------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  labels + counts live in a file-scope
+// device array of a fixed, modest size: 2 x B2S_SPECKLE_NOALLOC_MAX_PIXELS int32 = 8 MiB, which every GPU that loads
+// the library holds until the process exits.  Nothing here allocates: no cudaMalloc / cudaFree, no allocating library
+// routine.  In host code `g_speckle_scratch` is only a host-side stand-in for the symbol, NOT a device address: the
+// address is resolved once per device, with that device current, through cudaGetSymbolAddress and cached.
+//
+// Every call on a device shares the one array, and the array keeps the last call's contents.  Nothing has to be cleared
+// between calls: k_speckle_runs rewrites labels[] for every pixel of the call and zeroes counts[] at every run start,
+// and run starts are the only cells of counts[] the later kernels read or add to.  Calls that overlap on the GPU
+// (different streams without an ordering between them, concurrent host threads) RACE on the scratch: serialise them.
+static __device__ __align__(256) int32_t g_speckle_scratch[2 * (size_t)B2S_SPECKLE_NOALLOC_MAX_PIXELS];
+
+#include <mutex>
+static int speckle_scratch_for_current_device(int32_t** out)
+{
+    constexpr int MAXDEV = 64;
+    static int32_t* cached[MAXDEV] = {};
+    static std::mutex mu;
+    int dev = -1;
+    B2S_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAXDEV) { b2s_set_error("filterSpeckles (no-alloc): device ordinal %d out of range", dev); return B2S_E_UNSUPPORTED; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!cached[dev]) {
+        int32_t* p = nullptr;
+        B2S_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_speckle_scratch));      // the DEVICE address on the current device
+        if (!p) { b2s_set_error("filterSpeckles (no-alloc): cudaGetSymbolAddress returned a null address"); return B2S_E_CUDA; }
+        cached[dev] = p;
+    }
+    *out = cached[dev];
+    return B2S_OK;
+}
+
+extern "C" int b2s_filter_speckles_noalloc(int16_t* img, int H, int W, int batch, int newVal, int maxSpeckleSize, int maxDiff,
+                                           void* stream)
+{
+    if (!img || H <= 0 || W <= 0 || batch <= 0) { b2s_set_error("filterSpeckles (no-alloc): bad argument"); return B2S_E_INVALID; }
+    const long long n = (long long)batch * H * W;
+    if (n > (long long)B2S_SPECKLE_NOALLOC_MAX_PIXELS) {
+        b2s_set_error("filterSpeckles (no-alloc): batch*H*W = %lld pixels exceeds the built-in scratch of %d pixels "
+                      "(B2S_SPECKLE_NOALLOC_MAX_PIXELS); use b2s_filter_speckles with caller-provided scratch", n,
+                      (int)B2S_SPECKLE_NOALLOC_MAX_PIXELS);
+        return B2S_E_UNSUPPORTED;
+    }
+    int32_t* scratch = nullptr;
+    const int rc = speckle_scratch_for_current_device(&scratch);
+    if (rc) return rc;
+    return b2s_launch_speckles(img, H, W, batch, newVal, maxSpeckleSize, maxDiff, scratch, scratch + B2S_SPECKLE_NOALLOC_MAX_PIXELS,
+                               (cudaStream_t)stream);
+}
