@@ -111,7 +111,7 @@ def run_reference(args):
     import cv2
     cores = os.cpu_count() or 1
     k = args.ref_pairs
-    v, dt, slowest = cv2_pairs_per_s(cores, k, min(args.warmup, 1), args.steps)
+    v, dt, slowest = cv2_pairs_per_s(cores, k, max(args.warmup, 1), args.steps)      # W untimed steps, then K timed ones
     line = {
         "impl": "reference", "metric": "pairs_per_s", "value": v, "unit": "pairs/s", "gde_per_s": v * GDE_PER_PAIR,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
@@ -578,10 +578,12 @@ def run_b200(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
-        v, dt, _ = cv2_pairs_per_s(cores, args.cpu_pairs, 1, 1)
+        # the same shape as `--impl reference --steps 20 --warmup 5`: steps of 2 pairs per worker, a short warm-up
+        ksteps = max(1, args.cpu_pairs // 2)
+        v, dt, _ = cv2_pairs_per_s(cores, 2, 3, ksteps)
         cpu = {"value": v, "unit": "pairs/s", "cores": cores, "kind": "reference",
-               "sample": "%d pairs (%d per persistent worker process, cv2.setNumThreads(1) each, setup outside the timed "
-                         "region), same chain, %.1f s" % (cores * args.cpu_pairs, args.cpu_pairs, dt)}
+               "sample": "%d pairs (%d steps x 2 per persistent worker process, cv2.setNumThreads(1) each, setup and 6 warm-up "
+                         "pairs per worker outside the timed region), same chain, %.1f s" % (cores * 2 * ksteps, ksteps, dt)}
 
     if rank == 0:
         line = {

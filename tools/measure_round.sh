@@ -24,15 +24,9 @@ $NCU --set full --import-source on -k regex:k_wave8 -s 2 -c 2 -o $O/wave_$TAG -f
 $NCU --set full --import-source on -k regex:k_cost -s 1 -c 1 -o $O/cost_$TAG -f python tools/run_sgbm_once.py 128 2 > $O/ncu_cost.log 2>&1
 $NCU --set full --import-source on -k regex:k_bm_fast -s 1 -c 1 -o $O/bm_$TAG -f python tools/bench_configs.py cfg2 > $O/ncu_bm.log 2>&1
 fi
-if want sanitizer; then
-# memcheck + racecheck + synccheck of the band pipeline (mbarriers, cp.async staging, release/acquire
-# progress counters) on small parity cases of both wavefront kernels
-for tool in memcheck racecheck synccheck; do
-  timeout 1500 compute-sanitizer --tool $tool --error-exitcode 9 python -m pytest tests/test_gpu_wave8.py tests/test_gpu_parity.py \
-      -x -q -k "(wave8_shapes and (h17 or h33 or h1-)) or wave8_batch or test_sgbm_matches_oracle" > $O/sanitizer_${tool}_$TAG.log 2>&1
-  echo "exit code $?" >> $O/sanitizer_${tool}_$TAG.log
-done
-fi
+# (No compute-sanitizer pass: the GPU pool refuses it -- "compute-sanitizer is closed on this pool and stays closed",
+#  exit code 86, recorded in profiles/README.md.  Races and bad accesses in the band pipeline are hunted with the parity
+#  suites instead: small shapes around every band / chunk edge, batch == singles, repeated calls, all against cv2.)
 if want all; then
 $NCU --section SpeedOfLight --section LaunchStats --section Occupancy --section MemoryWorkloadAnalysis -s 30 -c 30 -o $O/all_$TAG -f \
     python bench.py --steps 1 --warmup 3 --batch 32 --no-cpu --no-parity > $O/ncu_all.log 2>&1
