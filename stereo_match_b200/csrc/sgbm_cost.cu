@@ -9,6 +9,8 @@
 //                                 d >= D hold 0 (the aggregation kernel pins their L_r at 0x7fff)
 #include "common.cuh"
 #include <cuda.h>
+#include <cstdlib>
+#include <type_traits>
 
 // ---------------------------------------------------------------------------
 // descriptors
@@ -341,6 +343,10 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
+__device__ __forceinline__ void lds64(unsigned addr, uint32_t& a, uint32_t& b)
+{
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "r"(addr));
+}
 __device__ __forceinline__ uint32_t lds32(unsigned addr)
 {
     uint32_t v;
@@ -354,9 +360,9 @@ __device__ __forceinline__ uint32_t lds32(unsigned addr)
 #ifndef B2S_COST_PRODUCER_LAST
 #define B2S_COST_PRODUCER_LAST 1
 #endif
-template <int MAXW> struct CostPlan {
+template <int MAXW, int WIN = 32> struct CostPlan {
     static constexpr int NSTG = B2S_COST_NSTG;                            // rows in flight
-    static constexpr int NELP = (32 + 8 * MAXW + 16 + 63) / 64 * 64 + 32; // plane pitch in smem: copies land 64 B apart mod 128
+    static constexpr int NELP = (WIN + 8 * MAXW + 16 + 63) / 64 * 64 + 32; // plane pitch in smem: copies land 64 B apart mod 128
     static constexpr int STAGE = 12 * NELP * 2;
     static constexpr int bars = NSTG * STAGE;                             // full[NSTG], empty[NSTG]
     static constexpr int total = bars + 2 * NSTG * 8;
@@ -509,6 +515,199 @@ k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap
     if (2 * (int)m + 3 * e.P2 > 32767) atomicOr(overflow_flag, 1);
 }
 
+// ---------------------------------------------------------------------------
+// k_cost_fast2: the same kernel with TWO adjacent columns per thread (interleaved records only: P8, every cell real).
+// A warp covers 64 window columns, lane l the columns 2l and 2l + 1.  What that buys (measured: three quarters of
+// the 24 LDS.32 per thread and row cost 1.5 ms of 8.75, the window-sum shuffles 0.7 ms, per 128 KITTI pairs):
+//   * the right-image operands of the two columns overlap in all but one word: 5 words per plane for 16 cell pairs
+//     instead of 8, fetched as three aligned LDS.64 (lanes are 8 bytes apart: 256 contiguous bytes, no conflicts);
+//   * the horizontal window sum works on column pairs q = p(2l) + p(2l+1):
+//         s(2l) = q(l) + ... + q(l+h-1) + p(2(l+h)),  s(2l+1) = s(2l) - p(2l) + p(2(l+h)+1)      (h = BS/2)
+//     h + 1 shuffles for two columns instead of 3 each (BS = 5);
+//   * BS - 1 halo columns per 64 instead of per 32.
+// Columns outside the cropped image (cv2 clamps the window on the cropped axis) are computed on whatever lies there
+// and then replaced by the border column's pixel cost with shuffles, in the first and the last strip only.
+// ---------------------------------------------------------------------------
+template <int BS, int MAXW, int CN>
+__global__ void __launch_bounds__(32 * MAXW, 1)
+k_cost_fast2(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap tmap, SgbmEff e, int TR,
+             uint16_t* __restrict__ cost, int* __restrict__ overflow_flag)
+{
+    using P = CostPlan<MAXW, 64>;
+    constexpr int SW2 = BS / 2, TW = 64 - (BS - 1), NSTG = P::NSTG, NELP = P::NELP;
+    extern __shared__ __align__(128) unsigned char smem_c[];
+    const unsigned sm0 = (unsigned)__cvta_generic_to_shared(smem_c);
+    const int Dp = e.Dp;
+    const int lane = threadIdx.x & 31, oct = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const int x0 = blockIdx.x * TW, yb = blockIdx.y * TR;
+    const unsigned b = blockIdx.z;
+    const int yend = min(yb + TR, e.H);
+    const int nrows = yend - yb + 2 * SW2;
+    // window column c = 2*lane + s (s = 0, 1) is the cropped-axis column x0 - SW2 + c
+    const int xa = x0 - SW2 + 2 * lane;                                       // slot 0's column (slot 1: xa + 1)
+    const int clo = max(0, SW2 - x0), chi = min(63, e.width1 - 1 - (x0 - SW2));   // window columns inside the cropped image
+    const bool border = clo > 0 || chi < 63;                                  // CTA-uniform
+    // image column of reversed element 0: the last window column inside the image, plus a margin of two elements.  The
+    // lane whose slot 0 is that column has its slot 1 one column outside: its e1 - par is then still >= 0, so the
+    // clamp of roff below only ever touches lanes with BOTH columns outside (margin <= B2S_RPAD: the planes are padded)
+    const int XRM = min(x0 - SW2 + 63, e.width1 - 1) + e.minX1 - e.minD + 2;
+    const int gbase = B2S_RPAD + (e.W - 1 - XRM);
+    const int shift = gbase & 3, gal = gbase - shift;                         // bulk copies start 16-byte aligned
+    const int dfirst = 16 * (oct >> 1) + 4 * (oct & 1);                       // first cell of this warp
+    // staged element of (column, cell dfirst + w): e(c) + w, e(c + 1) = e(c) - 1.  The two columns need e1 .. e1 + 4
+    // (e1 = slot 1's); three LDS.64 fetch the six words from the even index e1 - par on.  par is the same for all lanes.
+    const int e1 = shift + XRM - (xa + 1 + e.minX1 - e.minD) + dfirst;
+    const int par = (shift + XRM - (x0 - SW2 + 1 + e.minX1 - e.minD) + dfirst) & 1;
+    const unsigned roff = (unsigned)max(e1 - par, 0) * 4u;                    // (columns beyond the image: clamped, replaced later)
+    const int opos = b2s_cell_pos(dfirst, e.R, e.G, e.swz);
+    const int xo = x0 + 2 * lane;                                             // output column of slot 0
+    const bool outa = 2 * lane < TW && xo < e.width1, outb = 2 * lane + 1 < TW && xo + 1 < e.width1;
+    const size_t ostride = (size_t)e.width1 * Dp;
+    uint16_t* optr = cost + (((size_t)b * e.H + yb) * e.width1 + min(xo, e.width1 - 1)) * Dp + opos;
+    const unsigned bsrc = b / (unsigned)e.nst;
+    const int s0 = b2s_stripe_start(e, (int)(b % (unsigned)e.nst));
+    const unsigned plane = (unsigned)(e.Hsrc * e.W);
+    const unsigned bimg = bsrc * CN * plane + (unsigned)(s0 * e.W);
+    const unsigned rowbase = bsrc * CN * (unsigned)e.Hsrc + (unsigned)s0;
+    const int hrel = e.Hsrc - 1 - s0;
+    const int nitems = nrows * CN;
+    const int xla = min(max(xa + e.minX1, 0), e.W - 1), xlb = min(max(xa + 1 + e.minX1, 0), e.W - 1);   // left pixels (addresses kept inside the row)
+    auto src_row = [&](int r) { return min(max(yb - SW2 + r, 0), hrel); };
+    auto left_words = [&](int q, uint2& wa, uint2& wb) {
+        const int r = q / CN, c = q - r * CN;
+        const uint2* row = descL + (bimg + (unsigned)c * plane + (unsigned)(src_row(r) * e.W));
+        wa = __ldg(row + xla); wb = __ldg(row + xlb);
+    };
+    const int gal8 = gal >> 2;                                                // in 16-byte units (arithmetic shift: may be negative, TMA zero-fills)
+    auto issue = [&](int q) {
+        const int r = q / CN, c = q - r * CN;
+        const int yr = src_row(r);
+        const unsigned st = (unsigned)(q & (NSTG - 1));
+        const unsigned full = sm0 + P::bars + st * 8, dst = sm0 + st * P::STAGE;
+        if (q >= NSTG) cmbar_wait(sm0 + P::bars + (NSTG + st) * 8, (unsigned)((q / NSTG) - 1) & 1u);
+        cmbar_expect_tx(full, (unsigned)P::STAGE);
+        const int row = (int)((rowbase + (unsigned)(c * e.Hsrc + yr)) * 6u);
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                     ::"r"(dst), "l"(&tmap), "r"(0), "r"(gal8), "r"(row), "r"(full) : "memory");
+    };
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < NSTG; i++) {
+            cmbar_init(sm0 + P::bars + i * 8, 1);
+            cmbar_init(sm0 + P::bars + (NSTG + i) * 8, nwarps);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const bool producer = threadIdx.x == blockDim.x - 32;
+    if (producer)
+        for (int q = 0; q < NSTG - 1 && q < nitems; q++) issue(q);
+    uint32_t acc[2][4], ring[BS][2][4], vmax = 0;
+#pragma unroll
+    for (int w = 0; w < 4; w++) {
+        acc[0][w] = acc[1][w] = 0;
+#pragma unroll
+        for (int s = 0; s < BS; s++) ring[s][0][w] = ring[s][1][w] = 0;
+    }
+    uint2 wla_next, wlb_next;
+    left_words(0, wla_next, wlb_next);
+    // border strips: window column c takes the pixel cost of column min(max(c, clo), chi)
+    const int ca = min(max(2 * lane, clo), chi), cb = min(max(2 * lane + 1, clo), chi);
+
+    // BT cost of the two columns against one channel's three planes (value, lo, hi): PAR selects where the needed
+    // five words sit among the six fetched ones (slot 1: PAR .. PAR + 3, slot 0: PAR + 1 .. PAR + 4)
+    auto channel = [&](auto parc, unsigned base, uint32_t wordA, uint32_t wordB, uint32_t (&ca4)[4], uint32_t (&cb4)[4]) {
+        constexpr int PAR = decltype(parc)::value;
+        uint32_t V[6], LO[6], HI[6];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            lds64(base + 8 * k, V[2 * k], V[2 * k + 1]);
+            lds64(base + NELP * 4 + 8 * k, LO[2 * k], LO[2 * k + 1]);
+            lds64(base + 2 * NELP * 4 + 8 * k, HI[2 * k], HI[2 * k + 1]);
+        }
+        const uint32_t ua = __byte_perm(wordA, 0, 0x4040), loa = __byte_perm(wordA, 0, 0x4141), hia = __byte_perm(wordA, 0, 0x4242);
+        const uint32_t ub = __byte_perm(wordB, 0, 0x4040), lob = __byte_perm(wordB, 0, 0x4141), hib = __byte_perm(wordB, 0, 0x4242);
+#pragma unroll
+        for (int w = 0; w < 4; w++) {
+            ca4[w] = bt2(ua, loa, hia, V[w + PAR + 1], LO[w + PAR + 1], HI[w + PAR + 1]);
+            cb4[w] = bt2(ub, lob, hib, V[w + PAR], LO[w + PAR], HI[w + PAR]);
+        }
+    };
+
+    for (int r0 = 0; r0 < nrows; r0 += BS) {
+#pragma unroll
+        for (int s = 0; s < BS; s++) {
+            const int r = r0 + s;
+            if (r >= nrows) break;                                            // uniform
+            // ---- phase A: pixel costs of (2 columns, 8 cells), summed over the colour channels ----
+            uint32_t pa[4] = { 0, 0, 0, 0 }, pb[4] = { 0, 0, 0, 0 };
+#pragma unroll
+            for (int c = 0; c < CN; c++) {
+                const int q = r * CN + c;
+                if (producer && q + NSTG - 1 < nitems) issue(q + NSTG - 1);      // keep NSTG-1 items ahead
+                const uint2 wa = wla_next, wb = wlb_next;
+                if (q + 1 < nitems) left_words(q + 1, wla_next, wlb_next);
+                const unsigned st = (unsigned)(q & (NSTG - 1));
+                cmbar_wait(sm0 + P::bars + st * 8, (unsigned)(q / NSTG) & 1u);
+                const unsigned rb = sm0 + st * P::STAGE + roff;
+                uint32_t ga[4], gb[4], ra[4], rbv[4];
+                if (par) {
+                    channel(std::integral_constant<int, 1>{}, rb, wa.x, wb.x, ga, gb);
+                    channel(std::integral_constant<int, 1>{}, rb + 3 * NELP * 4, wa.y, wb.y, ra, rbv);
+                } else {
+                    channel(std::integral_constant<int, 0>{}, rb, wa.x, wb.x, ga, gb);
+                    channel(std::integral_constant<int, 0>{}, rb + 3 * NELP * 4, wa.y, wb.y, ra, rbv);
+                }
+#pragma unroll
+                for (int w = 0; w < 4; w++) {
+                    // (cr - bias) >> 2 == ((cr >> 2) & 0x7f) - 0x40 per half
+                    pa[w] += ga[w] + ((ra[w] >> 2) & 0x007f007fu) - (B2S_BIAS + 0x00400040u);
+                    pb[w] += gb[w] + ((rbv[w] >> 2) & 0x007f007fu) - (B2S_BIAS + 0x00400040u);
+                }
+                __syncwarp();
+                if (lane == 0) cmbar_arrive(sm0 + P::bars + (NSTG + st) * 8);  // this warp is done with the stage
+            }
+            if (border) {
+#pragma unroll
+                for (int w = 0; w < 4; w++) {
+                    const uint32_t a0 = __shfl_sync(0xffffffffu, pa[w], ca >> 1), a1 = __shfl_sync(0xffffffffu, pb[w], ca >> 1);
+                    const uint32_t b0 = __shfl_sync(0xffffffffu, pa[w], cb >> 1), b1 = __shfl_sync(0xffffffffu, pb[w], cb >> 1);
+                    pa[w] = (ca & 1) ? a1 : a0;
+                    pb[w] = (cb & 1) ? b1 : b0;
+                }
+            }
+            // ---- phase B: window sums over column pairs, vertical running sums, stores ----
+#pragma unroll
+            for (int w = 0; w < 4; w++) {
+                uint32_t sa, sb;
+                if (SW2 == 0) { sa = pa[w]; sb = pb[w]; }
+                else {
+                    const uint32_t q2 = pa[w] + pb[w];
+                    uint32_t Q = q2;
+#pragma unroll
+                    for (int j = 1; j < SW2; j++) Q += __shfl_down_sync(0xffffffffu, q2, j);
+                    sa = Q + __shfl_down_sync(0xffffffffu, pa[w], SW2);
+                    sb = sa - pa[w] + __shfl_down_sync(0xffffffffu, pb[w], SW2);
+                }
+                acc[0][w] += sa - ring[s][0][w];           // halves never borrow: acc >= old contribution
+                ring[s][0][w] = sa;
+                acc[1][w] += sb - ring[s][1][w];
+                ring[s][1][w] = sb;
+            }
+            // a half can only wrap past 0xffff after first being seen >= 0x8000
+            vmax = __vimax3_u16x2(vmax, __vmaxu2(acc[0][0], acc[0][1]), __vmaxu2(acc[0][2], acc[0][3]));
+            vmax = __vimax3_u16x2(vmax, __vmaxu2(acc[1][0], acc[1][1]), __vmaxu2(acc[1][2], acc[1][3]));
+            if (r >= 2 * SW2) {                            // output row yb + r - 2*SW2
+                if (outa) *reinterpret_cast<uint4*>(optr) = make_uint4(acc[0][0], acc[0][1], acc[0][2], acc[0][3]);
+                if (outb) *reinterpret_cast<uint4*>(optr + Dp) = make_uint4(acc[1][0], acc[1][1], acc[1][2], acc[1][3]);
+                optr += ostride;
+            }
+        }
+    }
+    uint32_t m = max(vmax & 0xffffu, vmax >> 16);
+    if (2 * lane >= TW) m = 0;                             // lanes whose window leaves the warp hold garbage
+    if (2 * (int)m + 3 * e.P2 > 32767) atomicOr(overflow_flag, 1);
+}
+
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
 typedef CUresult (*tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -563,9 +762,53 @@ static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const S
     return B2S_OK;
 }
 
+// two columns per thread (k_cost_fast2): interleaved records with every cell real; B2S_COST2=0 falls back (A/B runs)
+template <int BS, int MAXW, int CN>
+static int launch_cost_fast2(const uint2* descL, const uint16_t* planesR, const SgbmEff& e, uint16_t* cost, int* flag, cudaStream_t st)
+{
+    using P = CostPlan<MAXW, 64>;
+    constexpr int TW = 64 - (BS - 1);
+    int TR = 125;
+    for (const int cand : { 125, 75, 47, 25 }) {
+        TR = cand;
+        if ((long long)b2s_cdiv(e.width1, TW) * b2s_cdiv(e.H, TR) * e.batch >= 4 * 148) break;
+    }
+    dim3 grid(b2s_cdiv(e.width1, TW), b2s_cdiv(e.H, TR), e.batch);
+    const int nthreads = 32 * (e.Dp / 8);
+    const int PW = plane_pitch(e.W);
+    tmap_encode_fn enc = tmap_encoder();
+    if (!enc) { b2s_set_error("cuTensorMapEncodeTiled is not available from this driver"); return B2S_E_CUDA; }
+    CUtensorMap tmap;
+    const cuuint64_t rowu16 = 2 * (cuuint64_t)PW;
+    const cuuint64_t gdim[3] = { 8, rowu16 / 8, (cuuint64_t)(e.batch / e.nst) * CN * e.Hsrc * 6 };
+    const cuuint64_t gstr[2] = { 16, rowu16 * 2 };
+    const cuuint32_t box[3] = { 8, (cuuint32_t)(2 * P::NELP) / 8, 6 };
+    const cuuint32_t estr[3] = { 1, 1, 1 };
+    CUresult cr = enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, (void*)planesR, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                      CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) { b2s_set_error("cuTensorMapEncodeTiled failed (%d)", (int)cr); return B2S_E_CUDA; }
+    B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast2<BS, MAXW, CN>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
+    k_cost_fast2<BS, MAXW, CN><<<grid, nthreads, P::total, st>>>(descL, tmap, e, TR, cost, flag);
+    B2S_LAUNCH_CHECK();
+    return B2S_OK;
+}
+
+static bool cost2_enabled()
+{
+    static const bool on = [] { const char* s = getenv("B2S_COST2"); return !(s && s[0] == '0'); }();
+    return on;
+}
+
 template <int BS, int MAXW>
 static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const SgbmEff& e, uint16_t* cost, int* flag, cudaStream_t st)
 {
+    // (1024-thread CTAs are capped at 64 registers and large blocks need BS * 8 registers for the vertical ring: both
+    //  would spill in the two-column kernel)
+    if constexpr (MAXW == 16 && BS <= 5) {
+        if (e.swz && e.D == e.Dp && cost2_enabled())
+            return e.cn == 3 ? launch_cost_fast2<BS, MAXW, 3>(descL, planesR, e, cost, flag, st)
+                             : launch_cost_fast2<BS, MAXW, 1>(descL, planesR, e, cost, flag, st);
+    }
     if (e.cn == 3)
         return e.swz ? launch_cost_fast<BS, MAXW, true, 3>(descL, planesR, e, cost, flag, st)
                      : launch_cost_fast<BS, MAXW, false, 3>(descL, planesR, e, cost, flag, st);

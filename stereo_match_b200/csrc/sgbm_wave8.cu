@@ -42,22 +42,19 @@ template <int G, int NT, bool FINAL>
 struct Plan {
     static constexpr int RB = NT / G;
     static constexpr int REC = 32 * G;                                  // bytes of one [Dp] record
-    // the band above, per direction a ring of four records indexed by the consumer's step (record r at slot r & 3),
-    // filled two records at a time: the band's first row reads it with the same constant offsets as the other rows
-    // read the rings of their predecessor
-    static constexpr int stage = 0;                                     // [3][4][REC]
-    static constexpr int ringA = stage + 12 * REC;                      // [RB-1][4][REC]   predecessor x-1
-    static constexpr int ringB = ringA + (RB - 1) * 4 * REC;            // [RB-1][4][REC]   predecessor x
-    static constexpr int ringC = ringB + (RB - 1) * 4 * REC;            // [RB-1][2][REC]   predecessor x+1
-    static constexpr int scratch = ringC + (RB - 1) * 2 * REC;          // [RB][REC]      (FINAL)
-    static constexpr int ringmin = scratch + (FINAL ? RB * REC : 0);    // [RB-1][4] uint4  (-, m0, m1, m2) per consumer step
+    static constexpr int ALIGN = 8 * REC;                               // the stage toggles by XOR with 2/4 records
+    static constexpr int stage = 0;                                     // [3][2][4][REC]
+    static constexpr int ringA = stage + 24 * REC;                      // [RB][4][REC]   predecessor x-1
+    static constexpr int ringB = ringA + RB * 4 * REC;                  // [RB][4][REC]   predecessor x
+    static constexpr int ringC = ringB + RB * 4 * REC;                  // [RB][2][REC]   predecessor x+1
+    static constexpr int scratch = ringC + RB * 2 * REC;                // [RB][REC]      (FINAL)
+    static constexpr int ringmin = scratch + (FINAL ? RB * REC : 0);    // [RB][4] uint4  (-, m0, m1, m2) per consumer step
     static constexpr int MINROW = 80;                                   // bytes per row of ringmin: 64 + 16, so that the four rows of a warp hit different banks
-    static constexpr int stagemin = ringmin + (RB - 1) * MINROW;        // [4] uint4
-    static constexpr int zero = stagemin + 64;                          // [REC] zeros, then 16 zero bytes
-    static constexpr int misc = zero + REC + 16;                        // work item (int), step mbarrier at +8, stage mbarriers at +16, +24
-    static constexpr int total = misc + 32;
-    // (the band's last row has no ring: its successors read the edge stream.  G = 8, 16 rows: 43.1 KB for the first
-    //  sweep -- five CTAs per SM -- and 47.1 KB for the final one)
+    static constexpr int stagemin = ringmin + RB * MINROW;              // [2][4] uint4, 128-byte aligned (toggles by XOR 64)
+    static_assert((RB * MINROW) % 128 == 0, "stagemin must stay 128-byte aligned");
+    static constexpr int zero = stagemin + 128;                         // [REC] zeros, then 16 zero bytes
+    static constexpr int misc = zero + REC + 16;                        // work item (int), step mbarrier at +8, stage mbarrier at +16
+    static constexpr int total = misc + 32 + ALIGN;                     // + slack to align the stage
 };
 
 __device__ __forceinline__ void lds128(unsigned addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d)
@@ -131,7 +128,7 @@ __device__ __forceinline__ void wta8(const uint32_t (&Sv)[8], int lane, const Sg
     const unsigned best = key & 0xffffu, minS = key >> 16;                   // first minimum (lowest d on ties)
 
     // the scratch copy of S serves the winner's two neighbours
-    sts_rec(scr + lane * 32, Sv, 16);
+    sts_rec(scr + lane * 16, Sv, G * 16);                                    // chunk c of lane j at (c*G + j)*16: no bank conflicts
 
     // uniqueness: exists d, |d - best| > 1, S(d) * (100 - uniq) < minS * 100   <=>   S(d) < T = ceil(minS*100 / mul)
     const unsigned mul = 100u - (unsigned)e.uniq;
@@ -151,10 +148,10 @@ __device__ __forceinline__ void wta8(const uint32_t (&Sv)[8], int lane, const Sg
 
     __syncwarp();
     if (lane == 0 && act) {
-        // cell d of the scratch record: lane d>>4 at 32 bytes each, register d&7, half (d>>3)&1
+        // cell d of the scratch record: lane j = d>>4, register i = d&7 (chunk i>>2, word i&3), half (d>>3)&1
         const unsigned dm = best - 1u, dp = best + 1u;
-        const unsigned am = ((dm & 0xf0u) << 1) + ((dm & 7u) << 2) + ((dm >> 2) & 2u);
-        const unsigned ap = ((dp & 0xf0u) << 1) + ((dp & 7u) << 2) + ((dp >> 2) & 2u);
+        const unsigned am = (dm & 0xf0u) + ((dm & 4u) ? G * 16u : 0u) + ((dm & 3u) << 2) + ((dm >> 2) & 2u);
+        const unsigned ap = (dp & 0xf0u) + ((dp & 4u) ? G * 16u : 0u) + ((dp & 3u) << 2) + ((dp >> 2) & 2u);
         const uint32_t sm1 = best > 0u ? lds16(scr + am) : 0u;
         const uint32_t sp1 = best < (unsigned)e.D - 1u ? lds16(scr + ap) : 0u;
         rec[pix] = make_uint2(minS | (bad ? 0xffff0000u : best << 16), sm1 | (sp1 << 16));
@@ -164,32 +161,30 @@ __device__ __forceinline__ void wta8(const uint32_t (&Sv)[8], int lane, const Sg
     __syncwarp();
 }
 
-#ifndef B2S_W8_CTAS1
-#define B2S_W8_CTAS1 5      // CTAs per SM of the first sweep with 128 threads (registers: 65536 / (5 * 128) -> 96)
-#endif
 template <int G, int NT, bool FINAL>
-__global__ void __launch_bounds__(NT, (NT == 128 && !FINAL) ? B2S_W8_CTAS1 : 512 / NT)
+__global__ void __launch_bounds__(NT, 512 / NT)
 k_wave8(const SgbmEff e, const WaveArgs a)
 {
     using P = Plan<G, NT, FINAL>;
     constexpr int RB = P::RB, REC = P::REC, RECV = REC / 16, CSB = G * 16;
     constexpr int XS = FINAL ? -1 : 1;                     // memory direction of the sweep (the final sweep is flipped)
     static_assert((RB % 2) == 0, "the publication step assumes an even number of rows per band");
-    extern __shared__ __align__(16) unsigned char smem[];
-    const unsigned sm0 = (unsigned)__cvta_generic_to_shared(smem);
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const unsigned sm_raw = (unsigned)__cvta_generic_to_shared(smem_raw);
+    const unsigned sm0 = (sm_raw + P::ALIGN - 1) & ~(unsigned)(P::ALIGN - 1);
+    unsigned char* const smem = smem_raw + (sm0 - sm_raw);
     int* const s_item = reinterpret_cast<int*>(smem + P::misc);
-    const unsigned bar_addr = sm0 + P::misc + 8, sbar = sm0 + P::misc + 16;     // step barrier, two stage barriers
+    const unsigned bar_addr = sm0 + P::misc + 8, sbar = sm0 + P::misc + 16;     // step barrier, stage barrier
     const int tid = (int)threadIdx.x;
 
     if (tid == 0) {
         *s_item = (int)atomicAdd(a.ticket, 1u);
         mbar_init(bar_addr, NT / 32);
-        mbar_init(sbar, NT);                          // every thread arrives once per staged chunk,
-        mbar_init(sbar + 8, NT);                      // chunks alternate between the two barriers
+        mbar_init(sbar, NT);                          // every thread arrives once per staged chunk
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int i = tid; i < 12 * REC / 16; i += NT) reinterpret_cast<uint4*>(smem + P::stage)[i] = make_uint4(0u, 0u, 0u, 0u);
-    for (int i = tid; i < (64 + REC + 16) / 16; i += NT) reinterpret_cast<uint4*>(smem + P::stagemin)[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = tid; i < 24 * REC / 16; i += NT) reinterpret_cast<uint4*>(smem + P::stage)[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = tid; i < (128 + REC + 16) / 16; i += NT) reinterpret_cast<uint4*>(smem + P::stagemin)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
     const int item = *s_item;
     // band-major ticket order: a consumer's producer holds an earlier ticket (see sgbm_wave.cuh)
@@ -226,8 +221,8 @@ k_wave8(const SgbmEff e, const WaveArgs a)
     // ---- shared-memory addresses (32-bit shared window) ---------------------------------------------------------
     const unsigned laneb = (unsigned)lane * 16u;
     unsigned rA, rB, rC, rM;
-    // the ring of direction 2 has two slots, the stage four: the band's first row adds togC2 at the steps 2, 3 (mod 4)
-    const unsigned togC2 = g == 0 ? 2u * REC : 0u;
+    const unsigned togA = g == 0 ? 4u * REC : 0u, togC2 = g == 0 ? 2u * REC : 0u, togC0 = g == 0 ? 6u * REC : 0u,
+                   togM = g == 0 ? 64u : 0u;
     if (g > 0) {
         rA = sm0 + P::ringA + (g - 1) * 4 * REC + laneb;
         rB = sm0 + P::ringB + (g - 1) * 4 * REC + laneb;
@@ -235,33 +230,37 @@ k_wave8(const SgbmEff e, const WaveArgs a)
         rM = sm0 + P::ringmin + (g - 1) * P::MINROW;
     } else {
         rA = sm0 + P::stage + laneb;
-        rB = sm0 + P::stage + 4 * REC + laneb;
-        rC = sm0 + P::stage + 8 * REC + laneb;
+        rB = sm0 + P::stage + 8 * REC + laneb;
+        rC = sm0 + P::stage + 16 * REC + laneb;
         rM = sm0 + P::stagemin;
     }
     const unsigned wA = sm0 + P::ringA + g * 4 * REC + laneb, wB = sm0 + P::ringB + g * 4 * REC + laneb,
                    wC = sm0 + P::ringC + g * 2 * REC + laneb, wM = sm0 + P::ringmin + g * P::MINROW;
-    const bool ringrow = g < RB - 1;                                    // the band's last row feeds the edge stream only
     const unsigned zrec = sm0 + P::zero + laneb;
     const unsigned scr = sm0 + P::scratch + g * REC;
     const bool edgerow = has_below && g == gl;
     const bool wedge = has_below && (tid / 32) == (gl * G) / 32;        // this warp holds the band's last row
     const int pubthread = gl * G;
-    // chunk staging (consumer side): a chunk = two records of the three directions (3 * 2 * RECV 16-byte granules, one
-    // per thread) plus their two records of minima (two more threads); every thread's copy arrives on the chunk's
-    // mbarrier when it lands (cp.async.wait_all would wait on the scoreboard the global loads of the step share)
-    constexpr int PD = 2 * RECV;                                        // granules per direction and chunk
-    static_assert(NT >= 3 * PD + 2, "chunk staging: one granule per thread");
-    const bool cdata = tid < 3 * PD, cmin = tid >= 3 * PD && tid < 3 * PD + 2;
-    const int ck = tid / PD, crem = tid % PD, cj = tid - 3 * PD;
-    const int crec = cdata ? crem / RECV : cj;                          // which of the chunk's two records
-    const uint4* csrc = cdata ? eabove + (size_t)ck * wrecv + crem : eabove_min + (cmin ? cj : 0);      // chunk 0
-    const unsigned cdst = cdata ? sm0 + P::stage + ck * 4 * REC + crem * 16 : sm0 + P::stagemin + (cmin ? cj : 0) * 16;
-    const unsigned ctog = cdata ? 2u * REC : 32u, cadv = cdata ? 2u * RECV : 2u;
-    auto stage_chunk = [&](int c2) {                                    // records c2, c2 + 1 -> slots c2 & 3, (c2 & 3) + 1
-        if ((cdata || cmin) && c2 + crec < w1) cp16(cdst + ((c2 & 2) ? ctog : 0u), csrc);
-        cp_async_arrive(sbar + ((c2 & 2) ? 8u : 0u));
-        csrc += cadv;
+    // chunk staging (consumer side): the 12 * RECV 16-byte granules of [3 directions][4 records] are spread over the
+    // CTA (NT == 16 G: the lower half of the threads moves a second granule, direction 2), four threads add the minima;
+    // every thread's copies arrive on the stage mbarrier when they land (cp.async.wait_all would wait on the scoreboard
+    // the global loads of the step share: 6 % of the first sweep's stall samples)
+    static_assert(NT == 16 * G || NT == 32 * G, "chunk staging: 24 G granules over NT threads");
+    const int ck = tid / (4 * RECV), crem = tid % (4 * RECV), cr = crem / RECV;
+    const bool cvalid = tid < 12 * RECV, csecond = NT == 16 * G && tid < 4 * RECV;
+    const uint4* csrc = eabove + (size_t)ck * wrecv + crem;             // chunk 0
+    unsigned cdst = sm0 + P::stage + ck * 8 * REC + crem * 16;
+    unsigned cdstm = sm0 + P::stagemin + (unsigned)(tid - (NT - 4)) * 16u;
+    auto stage_chunk = [&](int c4) {                                    // records c4 .. c4+3 of the band above
+        if (cvalid && c4 + cr < w1) {
+            cp16(cdst, csrc);
+            if (csecond) cp16(cdst + 16 * REC, csrc + 2 * (size_t)wrecv);
+        }
+        if (tid >= NT - 4 && c4 + (tid - (NT - 4)) < w1) cp16(cdstm, eabove_min + c4 + (tid - (NT - 4)));
+        cp_async_arrive(sbar);
+        csrc += 4 * RECV;
+        cdst ^= 4u * REC;
+        cdstm ^= 64u;
     };
     int known = 0;                                                     // thread 0: last progress value seen
     auto wait_progress = [&](int need) {
@@ -276,6 +275,7 @@ k_wave8(const SgbmEff e, const WaveArgs a)
         __syncthreads();
         stage_chunk(0);
     }
+    unsigned sphase = 0;                                               // parity of the stage barrier (first row's warp)
 
     const uint32_t p1x2 = (uint32_t)e.P1 * 0x10001u;
     const uint32_t p2m1x2 = (uint32_t)(e.P2 - e.P1) * 0x10001u;
@@ -303,22 +303,18 @@ k_wave8(const SgbmEff e, const WaveArgs a)
         if (FAST || t > 0) { mbar_wait(bar_addr, phase); phase ^= 1u; }      // every warp finished step t-1's ring stores
         const int xs = t - 2 * g;
         const bool act = FAST || (rowact && (unsigned)xs < (unsigned)w1);
-        if ((J & 1) == 0) {
-            if (J == 2 && has_below) {
+        if (J == 2) {
+            if (has_below) {
                 // the band's last row finished xdone pixels before this step; one release store is cumulative over the
                 // edge stores its warp made before it arrived (xdone == w1 is published after the loop)
                 const int xdone = t - 2 * gl;
                 if (tid == pubthread && xdone > 0 && (xdone % PUBW) == 0 && xdone < w1) publish_progress(a.progress + eitem, xdone);
             }
-            if (has_above) {
-                // records t+2, t+3 (first read at step t+2) replace t-2, t-1, which every warp has left behind
-                if (t + 2 < w1) stage_chunk(t + 2);
-                // the warp of the band's first row reads records t, t+1 from now on: their chunk (staged two steps ago) landed?
-                if (tid < 32 && t < w1) mbar_wait(sbar + ((t & 2) ? 8u : 0u), ((unsigned)t >> 2) & 1u);
-            }
-        } else if (has_above && tid == 0 && t + 3 < w1) {
-            wait_progress(min(t + 6, w1));            // for the chunk staged at t+1: records t+3, t+4 hold pixels <= t+5
+            if (has_above && t + 2 < w1) stage_chunk(t + 2);                  // records t+2 .. t+5, first read at step t+2
         }
+        if (J == 1 && has_above && tid == 0 && t + 3 < w1) wait_progress(min(t + 8, w1));     // for the chunk staged at t+1
+        // the warp of the band's first row reads records t .. t+3 from now on: their chunk (staged two steps ago) landed?
+        if (J == 0 && has_above && tid < 32 && t < w1) { mbar_wait(sbar, sphase); sphase ^= 1u; }
 
         // ---- operands of the row above (issued first: their latency hides behind the global loads) ---------
         uint32_t Lv[3][8], m0, m1, m2;
@@ -327,13 +323,13 @@ k_wave8(const SgbmEff e, const WaveArgs a)
             if (FAST) {
                 lds_rec(rA + J * REC, Lv[0], CSB);
                 lds_rec(rB + J * REC, Lv[1], CSB);
-                lds_rec(rC + (J & 1) * REC + ((J & 2) ? togC2 : 0u), Lv[2], CSB);
+                lds_rec(rC + (J & 1) * REC, Lv[2], CSB);
                 lds128(rM + J * 16, mx, m0, m1, m2);
             } else {
                 const bool p0 = (unsigned)(xs - 1) < (unsigned)w1, p1 = (unsigned)xs < (unsigned)w1, p2 = (unsigned)(xs + 1) < (unsigned)w1;
                 lds_rec(p0 ? rA + J * REC : zrec, Lv[0], CSB);
                 lds_rec(p1 ? rB + J * REC : zrec, Lv[1], CSB);
-                lds_rec(p2 ? rC + (J & 1) * REC + ((J & 2) ? togC2 : 0u) : zrec, Lv[2], CSB);
+                lds_rec(p2 ? rC + (J & 1) * REC : zrec, Lv[2], CSB);
                 lds128(rM + J * 16, mx, m0, m1, m2);
                 if (!p0) m0 = 0u;
                 if (!p1) m1 = 0u;
@@ -373,17 +369,17 @@ k_wave8(const SgbmEff e, const WaveArgs a)
 
         // ---- the three directions that come from the row above --------------------------------------------
         const uint32_t mn0 = step<8, G, false, true>(Lv[0], Cc, lane, p1x2, p2m1x2, m0, nopad);
-        if (act && ringrow) sts_rec(wA + ((J + 3) & 3) * REC, Lv[0], CSB);
+        if (act) sts_rec(wA + ((J + 3) & 3) * REC, Lv[0], CSB);
         const uint32_t mn1 = step<8, G, false, true>(Lv[1], Cc, lane, p1x2, p2m1x2, m1, nopad);
-        if (act && ringrow) sts_rec(wB + ((J + 2) & 3) * REC, Lv[1], CSB);
+        if (act) sts_rec(wB + ((J + 2) & 3) * REC, Lv[1], CSB);
         const uint32_t mn2 = step<8, G, false, true>(Lv[2], Cc, lane, p1x2, p2m1x2, m2, nopad);
-        if (act && ringrow) sts_rec(wC + ((J + 1) & 1) * REC, Lv[2], CSB);
+        if (act) sts_rec(wC + ((J + 1) & 1) * REC, Lv[2], CSB);
         // lane minima of two directions per butterfly; the horizontal direction of the previous step rides along
         const uint32_t r12 = group_min_x2<G>(__vminu2(__byte_perm(mn0, mn1, 0x5410), __byte_perm(mn0, mn1, 0x7632)));
         const uint32_t r3h = group_min_x2<G>(__vminu2(__byte_perm(mn2, mnh, 0x5410), __byte_perm(mn2, mnh, 0x7632)));
         const uint32_t o0 = __byte_perm(r12, 0u, 0x1010), o1 = __byte_perm(r12, 0u, 0x3232), o2 = __byte_perm(r3h, 0u, 0x1010);
         minh = __byte_perm(r3h, 0u, 0x3232);
-        if (act && ringrow && lane == 0) {
+        if (act && lane == 0) {
             sts32(wM + ((J + 3) & 3) * 16 + 4, o0);
             sts32(wM + ((J + 2) & 3) * 16 + 8, o1);
             sts32(wM + ((J + 1) & 3) * 16 + 12, o2);
@@ -434,6 +430,8 @@ k_wave8(const SgbmEff e, const WaveArgs a)
         }
         vcur += (unsigned)(XS * RECV);
         pix += (unsigned)XS;
+        if (J == 1) rC ^= togC2;
+        if (J == 3) { rA ^= togA; rB ^= togA; rC ^= togC0; rM ^= togM; }
     };
 
     // steps at which all rows of this warp are interior (see `fast` above)

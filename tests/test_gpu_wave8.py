@@ -94,3 +94,32 @@ def test_wave8_batch_equals_singles_and_is_deterministic():
     single = sm.StereoSGBM_create(**kw)
     for i, (l, r) in enumerate(pairs):
         assert np.array_equal(out[i], single.compute(l, r)), "pair %d" % i
+
+
+# ---- k_cost_fast2 (two columns per thread; D = 128, blockSize <= 5): strips of 64 - (blockSize - 1) output columns ----
+COST2_CASES = [(w1, bs, minD, cn) for w1 in (3, 19, 55, 56, 59, 60, 61, 63, 64, 65, 119, 120, 121, 181) for bs, minD, cn in
+               ((5, 0, 1), (3, 0, 1), (1, 0, 1))] + [(61, 5, -37, 1), (120, 3, 11, 1), (75, 5, 0, 3), (121, 3, -128, 3), (60, 1, 0, 3)]
+
+
+@pytest.mark.parametrize("w1,bs,minD,cn", COST2_CASES, ids=["w%d-bs%d-m%d-c%d" % c for c in COST2_CASES])
+def test_cost2_volume_matches_oracle(w1, bs, minD, cn, port):
+    """Raw block cost C and aggregated S against the restatement around every strip edge of the two-column cost kernel
+    (first / last strip clamp their window on the cropped axis), gray and colour, shifted and negative ranges."""
+    from vectors import color_pair
+    D, h = 128, 13
+    w = w1 + max(D + minD, 0) - min(minD, 0)
+    assert w - max(D + minD, 0) + min(minD, 0) == w1
+    kw = _kw(D, 1, blockSize=bs, minDisparity=minD, P1=8 * bs * bs, P2=32 * bs * bs)
+    if w1 <= bs // 2:
+        pytest.skip("cv2 rejects this width")
+    l, r = (synth_pair(w, h, max(D + minD, 8), seed=w1 + bs) if cn == 1 else color_pair(w, h, max(D + minD, 8), w1 + bs))
+    _, Cw, Sw, _ = port.sgbm_compute(l, r, want_volumes=True, **kw)
+    m = sm.StereoSGBM_create(**kw)
+    m.keep_volumes(True)
+    got = m.compute(torch.from_numpy(l).cuda(), torch.from_numpy(r).cuda()).cpu().numpy()
+    cost, S, g = m.debug_volumes(1, h, w)
+    assert g["width1"] == w1
+    cost = cost[0, :, :, :D].cpu().numpy().astype(np.int32) & 0xffff
+    assert np.array_equal(cost + g["P2"], Cw.astype(np.int32)), "%d cost cells differ" % (cost + g["P2"] != Cw).sum()
+    assert np.array_equal(S[0, :, :, :D].cpu().numpy(), Sw)
+    assert np.array_equal(got, port.sgbm_compute(l, r, **kw))
