@@ -158,6 +158,40 @@ k_descriptor_planes8(const uint8_t* __restrict__ img, int H, int W, int ftzero, 
     }
 }
 
+// The same once more for k_cost_fast2, PACKED: every descriptor component is 8 bits wide, so one u32 holds two components
+// of the pixel pair (ri, ri + 8) -- three planes instead of six, half the shared-memory wavefronts in the cost kernel,
+// which unpacks a word into two u16x2 operands with one PRMT each:
+//   plane 0 = (g.v, g.v8, g.lo, g.lo8)   plane 1 = (g.hi, g.hi8, r.v, r.v8)   plane 2 = (r.lo, r.lo8, r.hi, r.hi8)
+// (g: Sobel channel, r: raw channel, v/lo/hi: value and half-pixel interval, "8": the pixel eight columns to the left)
+__global__ void __launch_bounds__(256)
+k_descriptor_planes8b(const uint8_t* __restrict__ img, int H, int W, int ftzero, int PW, uint32_t* __restrict__ planes)
+{
+    constexpr int N = B2S_PLANE_EPB;
+    __shared__ uint16_t sv[N + 8 + 4];
+    __shared__ uint2 sd[N + 8];
+    const int ri0 = blockIdx.x * N;
+    const int y = blockIdx.y;
+    const size_t b = blockIdx.z;
+    const int xfirst = W - 1 - (ri0 - B2S_RPAD);
+    row_values(img + b * (size_t)H * W, xfirst, -1, N + 8, y, H, W, ftzero, sv);
+    __syncthreads();
+    for (int i = threadIdx.x; i < N + 8; i += 256) {
+        const int x = xfirst - i;
+        sd[i] = (x >= 0 && x < W && ri0 + i < PW) ? desc_from(sv[i + 2], sv[i + 1], sv[i], x, W) : make_uint2(0u, 0u);
+    }
+    __syncthreads();
+    uint32_t* row = planes + ((b * H + y) * 3) * (size_t)PW + ri0;
+#pragma unroll
+    for (int j = 0; j < N / 256; j++) {
+        const int k = threadIdx.x + 256 * j;
+        if (ri0 + k >= PW) break;
+        const uint2 a = sd[k], c = sd[k + 8];                 // descriptor word = value | lo << 8 | hi << 16
+        row[k] = __byte_perm(a.x, c.x, 0x5140);
+        row[(size_t)PW + k] = __byte_perm(__byte_perm(a.x, c.x, 0x0062), __byte_perm(a.y, c.y, 0x0040), 0x5410);
+        row[2 * (size_t)PW + k] = __byte_perm(a.y, c.y, 0x6251);
+    }
+}
+
 // ---------------------------------------------------------------------------
 // BT cost of a disparity pair (d0, d0+1) in packed u16x2, biased by 0x0100 per half so
 // that plain 32-bit adds/subs never borrow across halves.
@@ -368,6 +402,15 @@ template <int MAXW, int WIN = 32> struct CostPlan {
     static constexpr int total = bars + 2 * NSTG * 8;
 };
 
+// k_cost_fast2: 64 window columns, three packed u32 planes per image row
+template <int MAXW> struct CostPlan2 {
+    static constexpr int NSTG = B2S_COST_NSTG;
+    static constexpr int NELP = (64 + 8 * MAXW + 16 + 63) / 64 * 64 + 32;   // u32 elements per staged plane
+    static constexpr int STAGE = 3 * NELP * 4;
+    static constexpr int bars = NSTG * STAGE;
+    static constexpr int total = bars + 2 * NSTG * 8;
+};
+
 // P8: the records are the wavefront kernel's interleaved ones (b2s_cell_pos, swz): a packed pair is (d, d + 8), warp
 // o owns the cells {16q + 4s + w, 16q + 4s + w + 8 : w < 4} with q = o / 2, s = o % 2, and the staged planes hold one
 // u32 (value(x), value(x - 8)) per element instead of two shifted u16 copies.
@@ -533,7 +576,7 @@ __global__ void __launch_bounds__(32 * MAXW, 1)
 k_cost_fast2(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap tmap, SgbmEff e, int TR,
              uint16_t* __restrict__ cost, int* __restrict__ overflow_flag)
 {
-    using P = CostPlan<MAXW, 64>;
+    using P = CostPlan2<MAXW>;
     constexpr int SW2 = BS / 2, TW = 64 - (BS - 1), NSTG = P::NSTG, NELP = P::NELP;
     extern __shared__ __align__(128) unsigned char smem_c[];
     const unsigned sm0 = (unsigned)__cvta_generic_to_shared(smem_c);
@@ -586,7 +629,7 @@ k_cost_fast2(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMa
         const unsigned full = sm0 + P::bars + st * 8, dst = sm0 + st * P::STAGE;
         if (q >= NSTG) cmbar_wait(sm0 + P::bars + (NSTG + st) * 8, (unsigned)((q / NSTG) - 1) & 1u);
         cmbar_expect_tx(full, (unsigned)P::STAGE);
-        const int row = (int)((rowbase + (unsigned)(c * e.Hsrc + yr)) * 6u);
+        const int row = (int)((rowbase + (unsigned)(c * e.Hsrc + yr)) * 3u);
         asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
                      ::"r"(dst), "l"(&tmap), "r"(0), "r"(gal8), "r"(row), "r"(full) : "memory");
     };
@@ -613,24 +656,33 @@ k_cost_fast2(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMa
     // border strips: window column c takes the pixel cost of column min(max(c, clo), chi)
     const int ca = min(max(2 * lane, clo), chi), cb = min(max(2 * lane + 1, clo), chi);
 
-    // BT cost of the two columns against one channel's three planes (value, lo, hi): PAR selects where the needed
-    // five words sit among the six fetched ones (slot 1: PAR .. PAR + 3, slot 0: PAR + 1 .. PAR + 4)
-    auto channel = [&](auto parc, unsigned base, uint32_t wordA, uint32_t wordB, uint32_t (&ca4)[4], uint32_t (&cb4)[4]) {
+    // BT cost of the two columns, both channels, against the three packed planes: PAR selects where the needed five
+    // words sit among the six fetched ones (slot 1: PAR .. PAR + 3, slot 0: PAR + 1 .. PAR + 4); every word is
+    // unpacked into two u16x2 operands (bytes 0, 1 and bytes 2, 3) with one PRMT each
+    auto costs = [&](auto parc, unsigned base, const uint2 wordA, const uint2 wordB, uint32_t (&pa4)[4], uint32_t (&pb4)[4]) {
         constexpr int PAR = decltype(parc)::value;
-        uint32_t V[6], LO[6], HI[6];
+        uint32_t W0[6], W1[6], W2[6];
 #pragma unroll
         for (int k = 0; k < 3; k++) {
-            lds64(base + 8 * k, V[2 * k], V[2 * k + 1]);
-            lds64(base + NELP * 4 + 8 * k, LO[2 * k], LO[2 * k + 1]);
-            lds64(base + 2 * NELP * 4 + 8 * k, HI[2 * k], HI[2 * k + 1]);
+            lds64(base + 8 * k, W0[2 * k], W0[2 * k + 1]);
+            lds64(base + NELP * 4 + 8 * k, W1[2 * k], W1[2 * k + 1]);
+            lds64(base + 2 * NELP * 4 + 8 * k, W2[2 * k], W2[2 * k + 1]);
         }
-        const uint32_t ua = __byte_perm(wordA, 0, 0x4040), loa = __byte_perm(wordA, 0, 0x4141), hia = __byte_perm(wordA, 0, 0x4242);
-        const uint32_t ub = __byte_perm(wordB, 0, 0x4040), lob = __byte_perm(wordB, 0, 0x4141), hib = __byte_perm(wordB, 0, 0x4242);
+        const uint32_t uga = __byte_perm(wordA.x, 0, 0x4040), loga = __byte_perm(wordA.x, 0, 0x4141), higa = __byte_perm(wordA.x, 0, 0x4242);
+        const uint32_t ura = __byte_perm(wordA.y, 0, 0x4040), lora = __byte_perm(wordA.y, 0, 0x4141), hira = __byte_perm(wordA.y, 0, 0x4242);
+        const uint32_t ugb = __byte_perm(wordB.x, 0, 0x4040), logb = __byte_perm(wordB.x, 0, 0x4141), higb = __byte_perm(wordB.x, 0, 0x4242);
+        const uint32_t urb = __byte_perm(wordB.y, 0, 0x4040), lorb = __byte_perm(wordB.y, 0, 0x4141), hirb = __byte_perm(wordB.y, 0, 0x4242);
+        uint32_t cgp = 0, crp = 0;                         // slot 0 of word j uses the same plane words as slot 1 of word j + 1
 #pragma unroll
-        for (int w = 0; w < 4; w++) {
-            ca4[w] = bt2(ua, loa, hia, V[w + PAR + 1], LO[w + PAR + 1], HI[w + PAR + 1]);
-            cb4[w] = bt2(ub, lob, hib, V[w + PAR], LO[w + PAR], HI[w + PAR]);
+        for (int j = 0; j < 5; j++) {
+            const uint32_t w0 = W0[j + PAR], w1 = W1[j + PAR], w2 = W2[j + PAR];
+            const uint32_t gv = __byte_perm(w0, 0, 0x4140), glo = __byte_perm(w0, 0, 0x4342), ghi = __byte_perm(w1, 0, 0x4140);
+            const uint32_t rv = __byte_perm(w1, 0, 0x4342), rlo = __byte_perm(w2, 0, 0x4140), rhi = __byte_perm(w2, 0, 0x4342);
+            // (cr - bias) >> 2 == ((cr >> 2) & 0x7f) - 0x40 per half
+            if (j < 4) pb4[j] += bt2(ugb, logb, higb, gv, glo, ghi) + ((bt2(urb, lorb, hirb, rv, rlo, rhi) >> 2) & 0x007f007fu) - (B2S_BIAS + 0x00400040u);
+            if (j > 0) pa4[j - 1] += bt2(uga, loga, higa, gv, glo, ghi) + ((bt2(ura, lora, hira, rv, rlo, rhi) >> 2) & 0x007f007fu) - (B2S_BIAS + 0x00400040u);
         }
+        (void)cgp; (void)crp;
     };
 
     for (int r0 = 0; r0 < nrows; r0 += BS) {
@@ -649,20 +701,8 @@ k_cost_fast2(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMa
                 const unsigned st = (unsigned)(q & (NSTG - 1));
                 cmbar_wait(sm0 + P::bars + st * 8, (unsigned)(q / NSTG) & 1u);
                 const unsigned rb = sm0 + st * P::STAGE + roff;
-                uint32_t ga[4], gb[4], ra[4], rbv[4];
-                if (par) {
-                    channel(std::integral_constant<int, 1>{}, rb, wa.x, wb.x, ga, gb);
-                    channel(std::integral_constant<int, 1>{}, rb + 3 * NELP * 4, wa.y, wb.y, ra, rbv);
-                } else {
-                    channel(std::integral_constant<int, 0>{}, rb, wa.x, wb.x, ga, gb);
-                    channel(std::integral_constant<int, 0>{}, rb + 3 * NELP * 4, wa.y, wb.y, ra, rbv);
-                }
-#pragma unroll
-                for (int w = 0; w < 4; w++) {
-                    // (cr - bias) >> 2 == ((cr >> 2) & 0x7f) - 0x40 per half
-                    pa[w] += ga[w] + ((ra[w] >> 2) & 0x007f007fu) - (B2S_BIAS + 0x00400040u);
-                    pb[w] += gb[w] + ((rbv[w] >> 2) & 0x007f007fu) - (B2S_BIAS + 0x00400040u);
-                }
+                if (par) costs(std::integral_constant<int, 1>{}, rb, wa, wb, pa, pb);
+                else costs(std::integral_constant<int, 0>{}, rb, wa, wb, pa, pb);
                 __syncwarp();
                 if (lane == 0) cmbar_arrive(sm0 + P::bars + (NSTG + st) * 8);  // this warp is done with the stage
             }
@@ -766,7 +806,7 @@ static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const S
 template <int BS, int MAXW, int CN>
 static int launch_cost_fast2(const uint2* descL, const uint16_t* planesR, const SgbmEff& e, uint16_t* cost, int* flag, cudaStream_t st)
 {
-    using P = CostPlan<MAXW, 64>;
+    using P = CostPlan2<MAXW>;
     constexpr int TW = 64 - (BS - 1);
     int TR = 125;
     for (const int cand : { 125, 75, 47, 25 }) {
@@ -780,9 +820,9 @@ static int launch_cost_fast2(const uint2* descL, const uint16_t* planesR, const 
     if (!enc) { b2s_set_error("cuTensorMapEncodeTiled is not available from this driver"); return B2S_E_CUDA; }
     CUtensorMap tmap;
     const cuuint64_t rowu16 = 2 * (cuuint64_t)PW;
-    const cuuint64_t gdim[3] = { 8, rowu16 / 8, (cuuint64_t)(e.batch / e.nst) * CN * e.Hsrc * 6 };
+    const cuuint64_t gdim[3] = { 8, rowu16 / 8, (cuuint64_t)(e.batch / e.nst) * CN * e.Hsrc * 3 };      // three packed planes per row
     const cuuint64_t gstr[2] = { 16, rowu16 * 2 };
-    const cuuint32_t box[3] = { 8, (cuuint32_t)(2 * P::NELP) / 8, 6 };
+    const cuuint32_t box[3] = { 8, (cuuint32_t)(2 * P::NELP) / 8, 3 };
     const cuuint32_t estr[3] = { 1, 1, 1 };
     CUresult cr = enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, (void*)planesR, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                       CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -798,14 +838,19 @@ static bool cost2_enabled()
     static const bool on = [] { const char* s = getenv("B2S_COST2"); return !(s && s[0] == '0'); }();
     return on;
 }
+// k_cost_fast2 (and with it the packed format of the right descriptor planes): interleaved records, every cell real,
+// 16 warps (Dp = 128), blockSize <= 5.  (1024-thread CTAs are capped at 64 registers and large blocks need BS * 8
+// registers for the vertical ring: both would spill in the two-column kernel.)
+static bool cost_uses_fast2(const SgbmEff& e)
+{
+    return e.swz && e.D == e.Dp && e.Dp == 128 && 2 * e.SW2 + 1 <= 5 && cost2_enabled();
+}
 
 template <int BS, int MAXW>
 static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const SgbmEff& e, uint16_t* cost, int* flag, cudaStream_t st)
 {
-    // (1024-thread CTAs are capped at 64 registers and large blocks need BS * 8 registers for the vertical ring: both
-    //  would spill in the two-column kernel)
     if constexpr (MAXW == 16 && BS <= 5) {
-        if (e.swz && e.D == e.Dp && cost2_enabled())
+        if (cost_uses_fast2(e))
             return e.cn == 3 ? launch_cost_fast2<BS, MAXW, 3>(descL, planesR, e, cost, flag, st)
                              : launch_cost_fast2<BS, MAXW, 1>(descL, planesR, e, cost, flag, st);
     }
@@ -834,7 +879,8 @@ int b2s_launch_descriptors_right(const uint8_t* img, const SgbmEff& e, void* des
     if (!cost_is_fast(e)) return b2s_launch_descriptors(img, e, (uint2*)desc, st);
     const int PW = plane_pitch(e.W);
     dim3 grid(b2s_cdiv(PW, B2S_PLANE_EPB), e.H, e.batch);
-    if (e.swz) k_descriptor_planes8<<<grid, 256, 0, st>>>(img, e.H, e.W, e.ftzero, PW, (uint32_t*)desc);
+    if (cost_uses_fast2(e)) k_descriptor_planes8b<<<grid, 256, 0, st>>>(img, e.H, e.W, e.ftzero, PW, (uint32_t*)desc);
+    else if (e.swz) k_descriptor_planes8<<<grid, 256, 0, st>>>(img, e.H, e.W, e.ftzero, PW, (uint32_t*)desc);
     else k_descriptor_planes<<<grid, 256, 0, st>>>(img, e.H, e.W, e.ftzero, PW, (uint16_t*)desc);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
