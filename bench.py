@@ -387,7 +387,7 @@ def run_b200(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    stage_sum = {}
+    stage_sum, sweep_sum = {}, [0.0, 0.0]
     launches0 = lib.b2s_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -396,6 +396,9 @@ def run_b200(args):
         chain(Ld, Rd)
         for k, v in matcher.stage_ms().items():       # waits for this step's last stage event
             stage_sum[k] = stage_sum.get(k, 0.0) + v
+        s1, s2 = matcher.sweep_ms()
+        sweep_sum[0] += s1
+        sweep_sum[1] += s2
     e1.record()
     barrier()
     ms_total = max_over_ranks(e0.elapsed_time(e1))
@@ -541,6 +544,11 @@ def run_b200(args):
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes_step / nl,
                 "avg_launch_ms": agg_ms / nl, "traffic": traffic, "traffic_source": traffic_src,
+                # the two launches apart (an event between them): the forward sweep, and the mirrored one with the fused WTA
+                "per_sweep": [{"launch": name, "ms": ms / args.steps, "achieved": alg_bytes_step / nl / (ms / args.steps / 1e3) / 1e9,
+                               "frac": alg_bytes_step / nl / (ms / args.steps / 1e3) / 1e9 / peak}
+                              for name, ms in (("k_wave8<FINAL=false>: 4 directions, writes S1", sweep_sum[0]),
+                                               ("k_wave8<FINAL=true>: 4 directions + S1, winner-take-all", sweep_sum[1])) if ms > 0],
                 "stage_ms_per_step": {k: v / args.steps for k, v in stage_sum.items()},
                 "stage_share_of_step": {k: v / args.steps / (ms_total / args.steps) for k, v in stage_sum.items()}}
 

@@ -149,6 +149,10 @@ B2S_API int b2s_sgbm_overflow_flag(b2s_handle h, int* flag_host);
 #define B2S_NSTAGES 6
 B2S_API int b2s_sgbm_enable_timing(b2s_handle h, int on);
 B2S_API int b2s_sgbm_stage_ms(b2s_handle h, float* ms_host);
+/* The "aggregate" stage split into its two sweep launches (forward sweep; mirrored sweep with the fused winner-take-all):
+   two durations in milliseconds to a HOST array.  Same conditions as b2s_sgbm_stage_ms; both values are 0 when the
+   matcher ran the one-launch-per-direction fallback (numDisparities > 512). */
+B2S_API int b2s_sgbm_sweep_ms(b2s_handle h, float* ms2_host);
 
 /* ---- StereoBM ------------------------------------------------------------ */
 B2S_API int b2s_bm_create(const b2s_bm_params* params, b2s_handle* out);

@@ -60,6 +60,7 @@ PROTOTYPES = {
     "b2s_sgbm_overflow_flag": (_i, [_vp, C.POINTER(_i)]),
     "b2s_sgbm_enable_timing": (_i, [_vp, _i]),
     "b2s_sgbm_stage_ms": (_i, [_vp, C.POINTER(C.c_float)]),
+    "b2s_sgbm_sweep_ms": (_i, [_vp, C.POINTER(C.c_float)]),
     "b2s_bm_create": (_i, [C.POINTER(BmParams), C.POINTER(_vp)]),
     "b2s_bm_compute": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _vp]),
     "b2s_destroy": (None, [_vp]),

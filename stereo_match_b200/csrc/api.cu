@@ -43,6 +43,8 @@ struct b2s_matcher {
     bool keep_volumes = false;   // debug tap: the fused WTA pass also writes the full S volume
     bool timing = false;
     cudaEvent_t ev[B2S_NSTAGES + 1] = {};
+    cudaEvent_t ev_mid = nullptr;   // between the two aggregation sweeps
+    bool mid_valid = false;
     bool ev_valid = false;
 };
 
@@ -272,7 +274,7 @@ extern "C" int b2s_sgbm_compute_cn(b2s_handle h, const uint8_t* left, const uint
     uint32_t* key = (uint32_t*)(ws + l.key);
 
     B2S_CUDA_CHECK(cudaMemsetAsync(h->flag, 0, sizeof(int), st));
-    h->ev_valid = false;
+    h->ev_valid = false; h->mid_valid = false;
 #define B2S_MARK(i) do { if (h->timing) B2S_CUDA_CHECK(cudaEventRecord(h->ev[i], st)); } while (0)
     B2S_MARK(0);
     SgbmEff ed = e;                              // descriptors: every colour channel is a gray image of its own
@@ -306,7 +308,8 @@ extern "C" int b2s_sgbm_compute_cn(b2s_handle h, const uint8_t* left, const uint
     if (uses_wave(e)) {
         // two fused sweeps; the second one ends in the winner-take-all (stage 2 = both sweeps)
         Sfull = h->keep_volumes ? (uint16_t*)(ws + l.Sdbg) : nullptr;
-        if ((rc = b2s_launch_wave(v, cost, S, Sfull, ws + l.edge, (uint2*)(ws + l.rec), key, st))) return rc;
+        if ((rc = b2s_launch_wave(v, cost, S, Sfull, ws + l.edge, (uint2*)(ws + l.rec), key, st, h->timing ? h->ev_mid : nullptr))) return rc;
+        h->mid_valid = h->timing;
         B2S_MARK(3);
         if ((rc = b2s_launch_finish_rec(v, (const uint2*)(ws + l.rec), key, rawv, st))) return rc;
     } else {
@@ -437,7 +440,10 @@ extern "C" int b2s_sgbm_enable_timing(b2s_handle h, int on)
 {
     if (!h || h->kind != 0) { b2s_set_error("enable_timing: bad handle"); return B2S_E_INVALID; }
     if (on && !h->ev[0])
+    {
         for (int i = 0; i <= B2S_NSTAGES; i++) B2S_CUDA_CHECK(cudaEventCreate(&h->ev[i]));
+        B2S_CUDA_CHECK(cudaEventCreate(&h->ev_mid));
+    }
     h->timing = on != 0;
     h->ev_valid = false;
     return B2S_OK;
@@ -449,6 +455,18 @@ extern "C" int b2s_sgbm_stage_ms(b2s_handle h, float* ms_host)
     if (!h->ev_valid) { b2s_set_error("stage_ms: no timed compute on this handle (call b2s_sgbm_enable_timing first)"); return B2S_E_INVALID; }
     B2S_CUDA_CHECK(cudaEventSynchronize(h->ev[B2S_NSTAGES]));
     for (int i = 0; i < B2S_NSTAGES; i++) B2S_CUDA_CHECK(cudaEventElapsedTime(&ms_host[i], h->ev[i], h->ev[i + 1]));
+    return B2S_OK;
+}
+
+extern "C" int b2s_sgbm_sweep_ms(b2s_handle h, float* ms2_host)
+{
+    if (!h || h->kind != 0 || !ms2_host) { b2s_set_error("sweep_ms: bad argument"); return B2S_E_INVALID; }
+    if (!h->ev_valid) { b2s_set_error("sweep_ms: no timed compute on this handle (call b2s_sgbm_enable_timing first)"); return B2S_E_INVALID; }
+    ms2_host[0] = ms2_host[1] = 0.f;
+    if (!h->mid_valid) return B2S_OK;
+    B2S_CUDA_CHECK(cudaEventSynchronize(h->ev[3]));
+    B2S_CUDA_CHECK(cudaEventElapsedTime(&ms2_host[0], h->ev[2], h->ev_mid));
+    B2S_CUDA_CHECK(cudaEventElapsedTime(&ms2_host[1], h->ev_mid, h->ev[3]));
     return B2S_OK;
 }
 
@@ -483,6 +501,7 @@ extern "C" void b2s_destroy(b2s_handle h)
 {
     if (!h) return;
     for (int i = 0; i <= B2S_NSTAGES; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    if (h->ev_mid) cudaEventDestroy(h->ev_mid);
     if (h->ws) cudaFree(h->ws);
     if (h->flag) cudaFree(h->flag);
     delete h;

@@ -64,7 +64,7 @@ static int launch_pass(const SgbmEff& e, const WaveArgs& a, int vert, int final,
 
 // cost -> (S1) -> WTA records + disp2 keys.  S holds S1 after the call; S_dbg (optional) the full S.
 int b2s_launch_wave(const SgbmEff& e, const uint16_t* cost, uint16_t* S, uint16_t* S_dbg, void* edge_ws,
-                    uint2* rec, uint32_t* disp2key, cudaStream_t st)
+                    uint2* rec, uint32_t* disp2key, cudaStream_t st, cudaEvent_t between_sweeps)
 {
     const EdgeLayout l = edge_layout(e);
     char* ws = (char*)edge_ws;
@@ -88,6 +88,7 @@ int b2s_launch_wave(const SgbmEff& e, const uint16_t* cost, uint16_t* S, uint16_
     B2S_CUDA_CHECK(cudaMemsetAsync(a.progress, 0, (items + 1) * sizeof(int), st));
     a.flip = 0;
     if ((rc = launch_pass(e, a, 1, 0, st))) return rc;
+    if (between_sweeps) B2S_CUDA_CHECK(cudaEventRecord(between_sweeps, st));     // opt-in stage timing (b2s_sgbm_sweep_ms)
     a.flip = 1;
     a.S_out = S_dbg;
     if (e.ndirs == 8 || e.ndirs == 4) {   // MODE_HH: the mirrored sweep adds <- , up-left, up, up-right (MODE_HH4: <- , up)

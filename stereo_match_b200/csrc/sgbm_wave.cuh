@@ -53,7 +53,7 @@ int b2s_wave_threads(const SgbmEff& e);
 int b2s_wave_rows_per_band(const SgbmEff& e);
 size_t b2s_wave_edge_bytes(const SgbmEff& e);       // edge + edge_min + progress + ticket
 int b2s_launch_wave(const SgbmEff& e, const uint16_t* cost, uint16_t* S, uint16_t* S_dbg, void* edge_ws,
-                    uint2* rec, uint32_t* disp2key, cudaStream_t st);
+                    uint2* rec, uint32_t* disp2key, cudaStream_t st, cudaEvent_t between_sweeps = nullptr);
 int b2s_launch_wave_g8(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st);        // 256 threads
 int b2s_launch_wave_g8s(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st);       // 128 threads
 int b2s_launch_wave_g16(const SgbmEff& e, const WaveArgs& a, int vert, int final, cudaStream_t st);

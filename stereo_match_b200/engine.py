@@ -156,6 +156,12 @@ class StereoSGBM(_Matcher):
         _lib.check(_lib.load().b2s_sgbm_stage_ms(self._h, ms))
         return dict(zip(self.STAGES, [float(v) for v in ms]))
 
+    def sweep_ms(self):
+        """(forward sweep, mirrored sweep + winner-take-all) of the last timed compute, in milliseconds."""
+        ms = (C.c_float * 2)()
+        _lib.check(_lib.load().b2s_sgbm_sweep_ms(self._h, ms))
+        return float(ms[0]), float(ms[1])
+
     def keep_volumes(self, on=True):
         """Debug tap: make the following computes also write the full S volume."""
         _lib.check(_lib.load().b2s_sgbm_keep_volumes(self._h, int(bool(on))))

@@ -27,6 +27,8 @@ KERNELS = [
     ("sgbm_wave_g8.o", r"k_wave<4, 8, 256, false, false, true, false, true>", "k_wave_R4_G8_sgbm_last"),
     ("sgbm_wave_g8.o", r"k_wave<8, 8, 256, false, true, true, false, false>", "k_wave_R8_G8_hh4_pass2_wta"),
     ("wls.o", r"k_wls_solve", "k_wls_solve"),
+    ("sgbm_cost.o", r"k_cost_fast2<5, 16, 1>", "k_cost_fast2_BS5"),
+    ("sgbm_cost.o", r"k_descriptor_planes8b", "k_descriptor_planes8b"),
     ("sgbm_cost.o", r"k_cost_fast<5, 16, false, true, 1>", "k_cost_fast_BS5"),
     ("sgbm_cost.o", r"k_cost_fast<5, 16, false, true, 3>", "k_cost_fast_BS5_color"),
     ("cloud.o", r"k_cloud_write<short>", "k_cloud_write_i16"),
