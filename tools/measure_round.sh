@@ -11,7 +11,7 @@ mkdir -p $O
 want() { [ "$PART" = everything ] || [ "$PART" = "$1" ]; }
 if want bench; then
 python bench.py > $O/bench_$TAG.json 2> $O/bench_$TAG.err
-python bench.py --impl reference --steps 5 --warmup 1 > $O/bench_ref_$TAG.json 2>> $O/bench_$TAG.err
+python bench.py --impl reference --steps 20 --warmup 5 > $O/bench_ref_$TAG.json 2>> $O/bench_$TAG.err
 python tools/bench_configs.py > $O/configs_$TAG.jsonl 2>> $O/bench_$TAG.err
 fi
 NCU="ncu --clock-control none"
