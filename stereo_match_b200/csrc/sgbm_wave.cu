@@ -81,6 +81,10 @@ int b2s_launch_wave(const SgbmEff& e, const uint16_t* cost, uint16_t* S, uint16_
     a.nbands = l.nbands;
     a.diag = wave_diag(e);
     a.zero = 0u;
+    // A band trails the one above by the publication interval plus the row skew.  When all work items are resident at
+    // once (small batches: the latency of the band chain is what the caller sees) publish every 8 pixels; otherwise
+    // every 32 -- each publication costs the publishing warp a gpu-scope release (+1.5 % per 128 pairs at 8)
+    a.pubw = (items < 2 * 148) ? 8 : 32;
     a.fastacc = wave_fastacc(e);
     int rc;
     B2S_CUDA_CHECK(cudaMemsetAsync(disp2key, 0xff, (size_t)e.batch * e.H * e.W * sizeof(uint32_t), st));

@@ -42,6 +42,7 @@ struct WaveArgs {
     int nbands;
     int diag;               // 1: the sweeps carry the two diagonal directions (MODE_SGBM / MODE_HH), 0: MODE_HH4
     unsigned int zero;      // always 0, opaque to the compiler (see `dep` in k_wave)
+    int pubw;               // k_wave8: pixels between two publications of a band's progress (a power of two)
 };
 
 // Threads per CTA of the wavefront kernel (a CTA owns threads / G rows): small CTAs keep the per-step barrier cheap

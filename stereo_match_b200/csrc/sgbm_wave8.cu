@@ -36,7 +36,7 @@ template <int V> struct Jc { __device__ constexpr operator int() const { return 
 struct Jr { int v; __device__ operator int() const { return v; } };
 
 constexpr int PFD = 6;       // L2 prefetch distance in steps
-constexpr int PUBW = 32;     // pixels between two publications of a band's progress
+// (pixels between two publications of a band's progress: WaveArgs::pubw, a power of two chosen on the host)
 
 template <int G, int NT, bool FINAL>
 struct Plan {
@@ -308,7 +308,7 @@ k_wave8(const SgbmEff e, const WaveArgs a)
                 // the band's last row finished xdone pixels before this step; one release store is cumulative over the
                 // edge stores its warp made before it arrived (xdone == w1 is published after the loop)
                 const int xdone = t - 2 * gl;
-                if (tid == pubthread && xdone > 0 && (xdone % PUBW) == 0 && xdone < w1) publish_progress(a.progress + eitem, xdone);
+                if (tid == pubthread && xdone > 0 && (xdone & (a.pubw - 1)) == 0 && xdone < w1) publish_progress(a.progress + eitem, xdone);
             }
             if (has_above && t + 2 < w1) stage_chunk(t + 2);                  // records t+2 .. t+5, first read at step t+2
         }
@@ -484,11 +484,12 @@ bool b2s_wave8_ok(const SgbmEff& e, const WaveArgs& a, int vert)
            e.width1 >= 16 && e.uqle == 0;
 }
 
-// rows per band (= threads / G).  G = 8: 16 rows (four CTAs of four warps per SM); B2S_WAVE8_ROWS=32 selects the
-// 32-row variant (half the edge traffic, two CTAs of eight warps per SM) for A/B measurements
+// rows per band (= threads / G).  G = 8: 32 rows (two CTAs of eight warps per SM, half the edge traffic of 16-row bands
+// and half as many bands in a pair's pipeline); measured per 128 KITTI pairs 16.54 ms against 16.9 ms for 16 rows, and
+// 4.44 against 4.64 ms for a single pair.  B2S_WAVE8_ROWS=16 selects the 16-row variant for A/B measurements.
 static int wave8_rows8()
 {
-    static const int rows = [] { const char* s = getenv("B2S_WAVE8_ROWS"); return (s && atoi(s) == 32) ? 32 : 16; }();
+    static const int rows = [] { const char* s = getenv("B2S_WAVE8_ROWS"); return (s && atoi(s) == 16) ? 16 : 32; }();
     return rows;
 }
 int b2s_wave8_rows_per_band(const SgbmEff& e) { return e.G == 8 ? wave8_rows8() : 16; }

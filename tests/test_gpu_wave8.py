@@ -1,7 +1,8 @@
 """GPU parity of the lean wavefront kernel (stereo_match_b200/csrc/sgbm_wave8.cu): its domain is numDisparities = 128
 (8 lanes per pixel) and 256 (16 lanes), MODE_HH (both sweeps) and MODE_SGBM (first sweep), sums that cannot overflow.
 Checked bit-exactly against live cv2 4.13.0 and, for the aggregated volume, against the C restatement.  Shapes are
-chosen around the kernel's own edges: heights below / at / just above one and two 16-row bands, widths that are not
+chosen around the kernel's own edges: heights below / at / just above one, two and three bands (32 rows by default, 16 in
+the variant the last test runs in a subprocess), widths that are not
 multiples of the 4-pixel chunks of the band pipeline, rows shorter than the prefetch distance, batches.
 """
 import numpy as np
@@ -23,9 +24,9 @@ def _kw(D, mode, **over):
 
 CASES = []
 for D in (128, 256):
-    for h in (1, 2, 15, 16, 17, 31, 32, 33, 49, 70):
+    for h in (1, 2, 15, 16, 17, 31, 32, 33, 49, 63, 64, 65, 70, 97):
         for dw in (16, 17, 18, 19, 23, 37, 64, 131):
-            if (h * 7 + dw) % 3 == 0 or h in (17, 33):            # a third of the grid, every band edge
+            if (h * 7 + dw) % 3 == 0 or h in (17, 33, 65):        # a third of the grid, every band edge (16- and 32-row bands)
                 CASES.append((D, h, D + dw + 3, 1 if (h + dw) % 2 else 0))
 
 
@@ -94,6 +95,35 @@ def test_wave8_batch_equals_singles_and_is_deterministic():
     single = sm.StereoSGBM_create(**kw)
     for i, (l, r) in enumerate(pairs):
         assert np.array_equal(out[i], single.compute(l, r)), "pair %d" % i
+
+
+_ROWS16_WORKER = r"""
+import sys
+sys.path.insert(0, %r)
+import numpy as np, cv2
+import stereo_match_b200 as sm
+from stereo_match_b200.synth import synth_pair
+ok = True
+for (h, w, mode) in ((15, 160, 1), (16, 147, 1), (17, 190, 1), (33, 211, 0), (49, 150, 1), (70, 165, 1)):
+    kw = dict(minDisparity=0, numDisparities=128, blockSize=5, P1=600, P2=2400, disp12MaxDiff=1, preFilterCap=63,
+              uniquenessRatio=15, speckleWindowSize=0, speckleRange=2, mode=mode)
+    l, r = synth_pair(w, h, 128, seed=h + w)
+    ok = ok and np.array_equal(sm.StereoSGBM_create(**kw).compute(l, r), cv2.StereoSGBM_create(**kw).compute(l, r))
+print("ROWS16_OK" if ok else "ROWS16_DIFFERS")
+"""
+
+
+def test_wave8_sixteen_row_variant(tmp_path):
+    """B2S_WAVE8_ROWS=16 (128-thread CTAs, 16-row bands: the A/B variant) is read once per process: run it in its own."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = tmp_path / "rows16.py"
+    script.write_text(_ROWS16_WORKER % root)
+    out = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=600,
+                         env=dict(os.environ, B2S_WAVE8_ROWS="16"))
+    assert "ROWS16_OK" in out.stdout, (out.stdout[-1000:], out.stderr[-2000:])
 
 
 # ---- k_cost_fast2 (two columns per thread; D = 128, blockSize <= 5): strips of 64 - (blockSize - 1) output columns ----

@@ -18,6 +18,9 @@ TAG = sys.argv[1] if len(sys.argv) > 1 else "r02"
 # (object file, regex on the demangled kernel name, output name)
 KERNELS = [
     # the headline sweeps: the lean kernel, 128 threads (the instantiation bench.py and the ncu captures run)
+    # the headline sweeps: the lean kernel with 32-row bands (256 threads), the instantiation bench.py and ncu run
+    ("sgbm_wave8.o", r"k_wave8<8, 256, false>", "k_wave8_G8_256_pass1"),
+    ("sgbm_wave8.o", r"k_wave8<8, 256, true>", "k_wave8_G8_256_pass2_wta"),
     ("sgbm_wave8.o", r"k_wave8<8, 128, false>", "k_wave8_G8_128_pass1"),
     ("sgbm_wave8.o", r"k_wave8<8, 128, true>", "k_wave8_G8_128_pass2_wta"),
     ("sgbm_wave8.o", r"k_wave8<16, 256, true>", "k_wave8_G16_256_pass2_wta"),
