@@ -3,7 +3,7 @@ line), normalised per warp-step of the wavefront kernels, next to its stall-reas
 
     python tools/ncu_opcodes.py gpurun_out/wave_r02.ncu-rep <kernel index> <warp-steps per launch> > profiles/opcodes_...txt
 
-warp-steps per launch of the cfg3 sweeps at batch 128: pairs * bands * warps * steps = 128 * 24 * 4 * 1144 = 14057472.
+warp-steps per launch of the cfg3 sweeps at batch 128: pairs * bands * warps * steps = 128 * 12 * 8 * 1176 = 14450688 (32-row bands; 16-row bands: 128 * 24 * 4 * 1144 = 14057472).
 """
 import collections
 import csv
