@@ -17,7 +17,7 @@
 // [2R*j, 2R*j + 2R) as packed u16x2.  Rows are skewed by two pixels per row: at step t the
 // group of row g is at x = t - 2g, so the three predecessors in the row above, (x-1), (x),
 // (x+1), were finished 3, 2 and 1 steps earlier.  They travel through small shared-memory rings;
-// the horizontal direction never leaves the registers.  One __syncthreads per step.
+// the horizontal direction never leaves the registers.  One split-phase mbarrier per step (a warp arrives as soon as its ring stores are done, waits at the start of the next step).
 // Bands of the same pair run concurrently as a pipeline: the last row of a band streams its
 // three vertical L_r vectors to an HBM edge buffer, the next band stages them into shared
 // memory chunk-wise with cp.async, gated by a release/acquire progress counter.  Bands are
