@@ -42,6 +42,21 @@ for i in (0, 1, 3):
                                   setters.get("uniquenessRatio", 15)], np.int32)
     out["bm%d_d" % i] = m.compute(l, r)
 
+# StereoBM beyond the defaults (round 2): speckle filter (range unscaled, negative range = off) and minDisparity != 0
+# (the right-view matcher of cv2.ximgproc.createRightMatcher).  Parameters as a fixed-order int array.
+BMX_KEYS = ("preFilterCap", "textureThreshold", "uniquenessRatio", "speckleWindowSize", "speckleRange", "minDisparity", "disp12MaxDiff")
+BMX_DEFAULTS = dict(preFilterCap=31, textureThreshold=10, uniquenessRatio=15, speckleWindowSize=0, speckleRange=0, minDisparity=0,
+                    disp12MaxDiff=-1)
+for i in range(11, len(BM_VECTORS)):
+    w, h, D, bs, setters = BM_VECTORS[i]
+    l, r = synth_pair(w, h, D, seed=200 + i)
+    m = cv2.StereoBM_create(numDisparities=D, blockSize=bs)
+    for k, val in setters.items():
+        getattr(m, "set" + k[0].upper() + k[1:])(val)
+    out["bmx%d_l" % i], out["bmx%d_r" % i] = l, r
+    out["bmx%d_p" % i] = np.array([D, bs] + [setters.get(k, BMX_DEFAULTS[k]) for k in BMX_KEYS], np.int32)
+    out["bmx%d_d" % i] = m.compute(l, r)
+
 rng = np.random.default_rng(42)
 d16 = rng.integers(-16, 1024, (24, 40)).astype(np.int16)
 d16[0, :3] = 0

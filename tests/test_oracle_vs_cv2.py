@@ -155,3 +155,15 @@ def test_bm_port_random_sweep(seed, port, cv2ref):
     from random_cases import random_bm_case
     D, bs, setters, l, r = random_bm_case(seed)
     assert np.array_equal(port.bm_compute(l, r, D, bs, **setters), cv2ref.bm_compute(l, r, D, bs, **setters)), (D, bs, setters, l.shape)
+
+
+def test_golden_bm_ranges_and_speckle(port, gold):
+    """StereoBM with the speckle filter and with minDisparity != 0 (the right-view matcher's range) against committed
+    cv2 4.13.0 outputs: works without cv2."""
+    keys = ("preFilterCap", "textureThreshold", "uniquenessRatio", "speckleWindowSize", "speckleRange", "minDisparity", "disp12MaxDiff")
+    ids = sorted(int(k[3:-2]) for k in gold.files if k.startswith("bmx") and k.endswith("_d"))
+    assert len(ids) >= 6
+    for i in ids:
+        p = [int(x) for x in gold["bmx%d_p" % i]]
+        got = port.bm_compute(gold["bmx%d_l" % i], gold["bmx%d_r" % i], p[0], p[1], **dict(zip(keys, p[2:])))
+        assert np.array_equal(got, gold["bmx%d_d" % i]), "golden BM vector %d" % i
