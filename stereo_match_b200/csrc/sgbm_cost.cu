@@ -571,18 +571,20 @@ k_cost_fast(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap
 // Columns outside the cropped image (cv2 clamps the window on the cropped axis) are computed on whatever lies there
 // and then replaced by the border column's pixel cost with shuffles, in the first and the last strip only.
 // ---------------------------------------------------------------------------
-template <int BS, int MAXW, int CN>
+// NH > 1 (Dp = 128 * NH): a strip's disparities are split over NH CTAs of 16 warps, blockIdx.y = band * NH + part
+template <int BS, int MAXW, int CN, int NH>
 __global__ void __launch_bounds__(32 * MAXW, 1)
 k_cost_fast2(const uint2* __restrict__ descL, const __grid_constant__ CUtensorMap tmap, SgbmEff e, int TR,
              uint16_t* __restrict__ cost, int* __restrict__ overflow_flag)
 {
-    using P = CostPlan2<MAXW>;
+    using P = CostPlan2<MAXW * NH>;
     constexpr int SW2 = BS / 2, TW = 64 - (BS - 1), NSTG = P::NSTG, NELP = P::NELP;
     extern __shared__ __align__(128) unsigned char smem_c[];
     const unsigned sm0 = (unsigned)__cvta_generic_to_shared(smem_c);
     const int Dp = e.Dp;
-    const int lane = threadIdx.x & 31, oct = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const int x0 = blockIdx.x * TW, yb = blockIdx.y * TR;
+    const int lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    const int oct = (int)(threadIdx.x >> 5) + MAXW * (int)(blockIdx.y % NH);      // this warp's slot among the Dp / 8 of a strip
+    const int x0 = blockIdx.x * TW, yb = (int)(blockIdx.y / NH) * TR;
     const unsigned b = blockIdx.z;
     const int yend = min(yb + TR, e.H);
     const int nrows = yend - yb + 2 * SW2;
@@ -803,18 +805,18 @@ static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const S
 }
 
 // two columns per thread (k_cost_fast2): interleaved records with every cell real; B2S_COST2=0 falls back (A/B runs)
-template <int BS, int MAXW, int CN>
+template <int BS, int MAXW, int CN, int NH>
 static int launch_cost_fast2(const uint2* descL, const uint16_t* planesR, const SgbmEff& e, uint16_t* cost, int* flag, cudaStream_t st)
 {
-    using P = CostPlan2<MAXW>;
+    using P = CostPlan2<MAXW * NH>;
     constexpr int TW = 64 - (BS - 1);
     int TR = 125;
     for (const int cand : { 125, 75, 47, 25 }) {
         TR = cand;
-        if ((long long)b2s_cdiv(e.width1, TW) * b2s_cdiv(e.H, TR) * e.batch >= 4 * 148) break;
+        if ((long long)b2s_cdiv(e.width1, TW) * b2s_cdiv(e.H, TR) * e.batch * NH >= 4 * 148) break;
     }
-    dim3 grid(b2s_cdiv(e.width1, TW), b2s_cdiv(e.H, TR), e.batch);
-    const int nthreads = 32 * (e.Dp / 8);
+    dim3 grid(b2s_cdiv(e.width1, TW), b2s_cdiv(e.H, TR) * NH, e.batch);
+    const int nthreads = 32 * MAXW;
     const int PW = plane_pitch(e.W);
     tmap_encode_fn enc = tmap_encoder();
     if (!enc) { b2s_set_error("cuTensorMapEncodeTiled is not available from this driver"); return B2S_E_CUDA; }
@@ -827,8 +829,8 @@ static int launch_cost_fast2(const uint2* descL, const uint16_t* planesR, const 
     CUresult cr = enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, (void*)planesR, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                       CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) { b2s_set_error("cuTensorMapEncodeTiled failed (%d)", (int)cr); return B2S_E_CUDA; }
-    B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast2<BS, MAXW, CN>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
-    k_cost_fast2<BS, MAXW, CN><<<grid, nthreads, P::total, st>>>(descL, tmap, e, TR, cost, flag);
+    B2S_CUDA_CHECK(cudaFuncSetAttribute(k_cost_fast2<BS, MAXW, CN, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize, P::total));
+    k_cost_fast2<BS, MAXW, CN, NH><<<grid, nthreads, P::total, st>>>(descL, tmap, e, TR, cost, flag);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
 }
@@ -839,20 +841,21 @@ static bool cost2_enabled()
     return on;
 }
 // k_cost_fast2 (and with it the packed format of the right descriptor planes): interleaved records, every cell real,
-// 16 warps (Dp = 128), blockSize <= 5.  (1024-thread CTAs are capped at 64 registers and large blocks need BS * 8
-// registers for the vertical ring: both would spill in the two-column kernel.)
+// Dp = 128 or 256 (CTAs of 16 warps; 256 disparities are split over two CTAs per strip, 1024-thread CTAs would be capped
+// at 64 registers), blockSize <= 5 (larger blocks need BS * 8 registers for the vertical ring and spill).
 static bool cost_uses_fast2(const SgbmEff& e)
 {
-    return e.swz && e.D == e.Dp && e.Dp == 128 && 2 * e.SW2 + 1 <= 5 && cost2_enabled();
+    return e.swz && e.D == e.Dp && (e.Dp == 128 || e.Dp == 256) && 2 * e.SW2 + 1 <= 5 && cost2_enabled();
 }
 
 template <int BS, int MAXW>
 static int launch_cost_fast(const uint2* descL, const uint16_t* planesR, const SgbmEff& e, uint16_t* cost, int* flag, cudaStream_t st)
 {
-    if constexpr (MAXW == 16 && BS <= 5) {
+    if constexpr (BS <= 5) {
+        constexpr int NH = MAXW / 16;                      // Dp = 256: two CTAs of 16 warps per strip
         if (cost_uses_fast2(e))
-            return e.cn == 3 ? launch_cost_fast2<BS, MAXW, 3>(descL, planesR, e, cost, flag, st)
-                             : launch_cost_fast2<BS, MAXW, 1>(descL, planesR, e, cost, flag, st);
+            return e.cn == 3 ? launch_cost_fast2<BS, 16, 3, NH>(descL, planesR, e, cost, flag, st)
+                             : launch_cost_fast2<BS, 16, 1, NH>(descL, planesR, e, cost, flag, st);
     }
     if (e.cn == 3)
         return e.swz ? launch_cost_fast<BS, MAXW, true, 3>(descL, planesR, e, cost, flag, st)

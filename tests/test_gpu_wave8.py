@@ -131,12 +131,21 @@ COST2_CASES = [(w1, bs, minD, cn) for w1 in (3, 19, 55, 56, 59, 60, 61, 63, 64, 
                ((5, 0, 1), (3, 0, 1), (1, 0, 1))] + [(61, 5, -37, 1), (120, 3, 11, 1), (75, 5, 0, 3), (121, 3, -128, 3), (60, 1, 0, 3)]
 
 
+COST2_CASES_256 = [(19, 5, 0, 1), (59, 5, 0, 1), (60, 3, 0, 1), (61, 5, 0, 1), (121, 1, 0, 1), (75, 5, -100, 1), (64, 3, 0, 3)]
+
+
+@pytest.mark.parametrize("w1,bs,minD,cn", COST2_CASES_256, ids=["w%d-bs%d-m%d-c%d" % c for c in COST2_CASES_256])
+def test_cost2_volume_matches_oracle_d256(w1, bs, minD, cn, port):
+    """numDisparities = 256: the strip's disparities are split over two CTAs of the two-column kernel."""
+    test_cost2_volume_matches_oracle(w1, bs, minD, cn, port, D=256)
+
+
 @pytest.mark.parametrize("w1,bs,minD,cn", COST2_CASES, ids=["w%d-bs%d-m%d-c%d" % c for c in COST2_CASES])
-def test_cost2_volume_matches_oracle(w1, bs, minD, cn, port):
+def test_cost2_volume_matches_oracle(w1, bs, minD, cn, port, D=128):
     """Raw block cost C and aggregated S against the restatement around every strip edge of the two-column cost kernel
     (first / last strip clamp their window on the cropped axis), gray and colour, shifted and negative ranges."""
     from vectors import color_pair
-    D, h = 128, 13
+    h = 13
     w = w1 + max(D + minD, 0) - min(minD, 0)
     assert w - max(D + minD, 0) + min(minD, 0) == w1
     kw = _kw(D, 1, blockSize=bs, minDisparity=minD, P1=8 * bs * bs, P2=32 * bs * bs)
