@@ -18,6 +18,8 @@
 //   * the winner-take-all builds half of its keys and its whole uniqueness mask on the fma pipe
 //     (IMAD with a power of two) and tests S >= T with one VIADDMNMX.S16x2.RELU per register.
 // Steps at which a warp touches the image border run a guarded copy of the same body.
+// Bands are 32 rows with 8 lanes per pixel (two 256-thread CTAs per SM) and 16 rows with 16 lanes; a band publishes its
+// progress every WaveArgs::pubw pixels (32, or 8 when every work item is resident: small batches).
 #include "sgbm_wave_impl.cuh"
 #include <cstdlib>
 
