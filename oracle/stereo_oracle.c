@@ -230,7 +230,11 @@ static const int DIRS[8][2] = {
 /* ------------------------------------------------------------------ */
 /* WTA + uniqueness + disp2 + sub-pixel + LR check.     */
 /* ------------------------------------------------------------------ */
-/* le != 0: MODE_SGBM_3WAY's uniqueness rule (rejects on equality too, and not at all for ratio 0) */
+/* le != 0: MODE_SGBM_3WAY (cv2 4.13.0 works on 8 int16 SIMD lanes there; probed, tests/test_oracle_vs_cv2.py):    */
+/*   - winner: lane j keeps the LAST minimum among its disparities d = j (mod 8), the lanes are then merged to  */
+/*     the SMALLEST position -- differs from "first minimum" only when the minimum is tied;                    */
+/*   - uniqueness: 16-bit compare S(d) < (int16)(100 * minS / (100 - ratio) + 1), the threshold wrapping       */
+/*     (rejects on equality too; not at all for ratio 0).                                                      */
 static void wta_rows_ex(const int16_t* S, int H, int W, const eff_t* e, int le, int16_t* disp)
 {
     const int D = e->D, w1 = e->width1, INV = e->INVALID;
@@ -243,10 +247,21 @@ static void wta_rows_ex(const int16_t* S, int H, int W, const eff_t* e, int le, 
             const int16_t* Sp = S + ((size_t)y * w1 + x) * D;
             int best = 0, minS = Sp[0];
             for (int d = 1; d < D; d++) if (Sp[d] < minS) { minS = Sp[d]; best = d; }
+            if (le) {
+                int last[8], j;
+                for (j = 0; j < 8; j++) last[j] = -1;
+                for (int d = 0; d < D; d++) if (Sp[d] == minS) last[d & 7] = d;
+                best = D;
+                for (j = 0; j < 8; j++) if (last[j] >= 0 && last[j] < best) best = last[j];
+            }
+            /* every S saturated: cv2's search starts at (MAX_COST, bestDisp = -1) with a strict compare, finds nothing */
+            /* and writes (-1 + minD) * 16 = INVALID, disp2 untouched (3WAY's non-strict lanes do find a winner)      */
+            if (!le && minS >= 32767) continue;
             int d;
+            const int thr16 = le && e->uniq > 0 ? wrap16(minS * 100 / (100 - e->uniq) + 1) : 0;
             for (d = 0; d < D; d++) {
                 int lhs = Sp[d] * (100 - e->uniq), rhs = minS * 100;
-                if ((le ? (e->uniq > 0 && lhs <= rhs) : lhs < rhs) && abs(best - d) > 1) break;
+                if ((le ? (e->uniq > 0 && Sp[d] < thr16) : lhs < rhs) && abs(best - d) > 1) break;
             }
             if (d < D) continue;
             int x2 = x + e->minX1 - best - e->minD;

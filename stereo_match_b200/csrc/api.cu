@@ -81,7 +81,7 @@ static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, Sgb
     e.width1 = e.maxX1 - e.minX1;
     e.invalid = (e.minD - 1) * 16;
     e.ndirs = p.mode == B2S_MODE_HH ? 8 : (p.mode == B2S_MODE_HH4 ? 4 : (p.mode == B2S_MODE_SGBM_3WAY ? 3 : 5));
-    e.cn = 1; e.Hsrc = H; e.nst = 1; e.sz = e.ov = 0; e.uqle = 0;
+    e.cn = 1; e.Hsrc = H; e.nst = 1; e.sz = e.ov = 0; e.uqle = 0; e.way3 = 0;
     // cv2 4.13.0 stereosgbm.cpp:511 raises cv2.error on this condition
     if (!(W - maxD > e.SW2)) {
         b2s_set_error("StereoSGBM: Your input images are too small for your window size and max disparity "
@@ -119,6 +119,7 @@ static SgbmEff volume_geometry(const SgbmEff& e, int cn)
         v.H = v.sz + v.ov < e.H ? v.sz + v.ov : e.H;
         v.batch = e.batch * 4;
         v.uqle = e.uniq > 0 ? 1 : 0;
+        v.way3 = 1;
     }
     return v;
 }

@@ -24,8 +24,36 @@ struct SgbmEff {
     int Hsrc;                 // rows of the source images
     int nst, sz, ov;          // MODE_SGBM_3WAY: the volumes hold batch = pairs * nst "stripe images" of H rows; stripe
                               // st of a pair starts at source row b2s_stripe_start() and clamps its block sum there
-    int uqle;                 // 1: the uniqueness test rejects on equality as well (MODE_SGBM_3WAY)
+    int uqle;                 // 1: the uniqueness test rejects on equality as well (MODE_SGBM_3WAY with a ratio > 0), in
+                              // 16 bits: S < (int16)(floor(100 * minS / (100 - ratio)) + 1), the threshold wrapping
+    int way3;                 // 1: MODE_SGBM_3WAY's winner rule (b2s_tie8_*) ; 0: first minimum, and a pixel whose S are
+                              // all saturated (minS = 32767) has no winner at all (cv2 starts from bestDisp = -1)
 };
+
+#ifdef __CUDACC__
+// MODE_SGBM_3WAY of cv2 4.13.0 searches the minimum on 8 int16 SIMD lanes: lane j keeps the LAST minimum among its
+// disparities d = j (mod 8), the lanes are then merged to the SMALLEST position (probed; oracle/stereo_oracle.c
+// wta_rows_ex).  One byte per lane class: (d >> 3) + 1 of the last tied minimum (0: none), d < 1024.
+__device__ __forceinline__ unsigned long long b2s_tie8_one(int d)
+{
+    return (unsigned long long)((d >> 3) + 1) << ((d & 7) * 8);
+}
+__device__ __forceinline__ unsigned long long b2s_tie8_merge(unsigned long long a, unsigned long long b)
+{
+    const unsigned lo = __vmaxu4((unsigned)a, (unsigned)b), hi = __vmaxu4((unsigned)(a >> 32), (unsigned)(b >> 32));
+    return ((unsigned long long)hi << 32) | lo;
+}
+__device__ __forceinline__ int b2s_tie8_best(unsigned long long w)
+{
+    int best = 1 << 30;
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+        const int v = (int)((w >> (8 * c)) & 0xffull);
+        if (v) best = min(best, ((v - 1) << 3) | c);
+    }
+    return best;
+}
+#endif
 
 // first source row of stripe st (cv2 4.13.0 computeDisparity3WAY: range.start * stripe_sz - stripe_overlap, clamped)
 __host__ __device__ inline int b2s_stripe_start(const SgbmEff& e, int st)

@@ -58,13 +58,36 @@ k_wta(const uint16_t* __restrict__ S, SgbmEff e, int16_t* __restrict__ disp, uin
     }
 #pragma unroll
     for (int o = G / 2; o > 0; o >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, o));
-    const int best = (int)(key & 0xffffu);
+    int best = (int)(key & 0xffffu);
     const int minS = (int)(key >> 16);
+    if (e.way3) {                              // MODE_SGBM_3WAY: a tied minimum goes to cv2's 8-lane winner (common.cuh)
+        bool tie = false;
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            const int d0 = dbase + 2 * i;
+            tie = tie || ((int)(v[i] & 0xffffu) == minS && d0 != best && d0 < e.D) || ((int)(v[i] >> 16) == minS && d0 + 1 != best && d0 + 1 < e.D);
+        }
+        if (__any_sync(0xffffffffu, tie)) {
+            unsigned long long w8 = 0ull;
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                const int d0 = dbase + 2 * i;
+                if ((int)(v[i] & 0xffffu) == minS && d0 < e.D) w8 = b2s_tie8_merge(w8, b2s_tie8_one(d0));
+                if ((int)(v[i] >> 16) == minS && d0 + 1 < e.D) w8 = b2s_tie8_merge(w8, b2s_tie8_one(d0 + 1));
+            }
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) w8 = b2s_tie8_merge(w8, __shfl_xor_sync(0xffffffffu, w8, o));
+            best = b2s_tie8_best(w8);
+        }
+    }
 
     // uniqueness + neighbours of the winner
-    const int thr = minS * 100 + e.uqle;       // uqle (MODE_SGBM_3WAY): reject on equality too
     const int mul = 100 - e.uniq;
-    uint32_t bad = 0, sm1 = 0, sp1 = 0;
+    // S * mul < minS * 100 ; MODE_SGBM_3WAY (uqle): S < (int16)(floor(minS * 100 / mul) + 1), cv2's 16-bit compare, wrapping
+    const int thr = minS * 100;
+    const int thr16 = (e.uqle && mul > 0) ? (int)(int16_t)(uint16_t)((thr / mul + 1) & 0xffff) : 0;
+    uint32_t bad = (minS >= 32767 && !e.way3) ? 1u : 0u;       // every S saturated: cv2 finds no winner (bestDisp = -1 -> INVALID)
+    uint32_t sm1 = 0, sp1 = 0;
 #pragma unroll
     for (int i = 0; i < R; i++) {
 #pragma unroll
@@ -73,7 +96,7 @@ k_wta(const uint16_t* __restrict__ S, SgbmEff e, int16_t* __restrict__ disp, uin
             int val = h ? (int)(v[i] >> 16) : (int)(v[i] & 0xffffu);
             if (d < e.D) {
                 int ad = d - best;
-                if ((ad > 1 || ad < -1) && val * mul < thr) bad = 1;
+                if ((ad > 1 || ad < -1) && (e.uqle ? val < thr16 : val * mul < thr)) bad = 1;
                 if (ad == -1) sm1 = (uint32_t)val;
                 if (ad == 1) sp1 = (uint32_t)val;
             }

@@ -156,8 +156,11 @@ __device__ __forceinline__ void wta8(const uint32_t (&Sv)[8], int lane, const Sg
         const unsigned ap = (dp & 0xf0u) + ((dp & 4u) ? G * 16u : 0u) + ((dp & 3u) << 2) + ((dp >> 2) & 2u);
         const uint32_t sm1 = best > 0u ? lds16(scr + am) : 0u;
         const uint32_t sp1 = best < (unsigned)e.D - 1u ? lds16(scr + ap) : 0u;
-        rec[pix] = make_uint2(minS | (bad ? 0xffff0000u : best << 16), sm1 | (sp1 << 16));
-        if (!bad && minS < 32767u)           // cv2: disp2cost starts at SHRT_MAX and is only replaced by a smaller cost
+        // every S saturated (minS = 32767): cv2's search starts from bestDisp = -1 with a strict compare, finds no winner,
+        // writes INVALID and leaves disp2 alone (its disp2cost starts at SHRT_MAX and only a smaller cost replaces it)
+        const bool keep = !bad && minS < 32767u;
+        rec[pix] = make_uint2(minS | (keep ? best << 16 : 0xffff0000u), sm1 | (sp1 << 16));
+        if (keep)
             atomicMin(disp2key + (pix - best - (unsigned)e.minD), (minS << 16) | (uint32_t)xcode);
     }
     __syncwarp();

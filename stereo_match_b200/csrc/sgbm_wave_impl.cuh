@@ -236,8 +236,30 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
     key += dbase;                                                  // cell -> disparity index
 #pragma unroll
     for (int o = G / 2; o > 0; o >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, o));
-    const int best = (int)(key & 0xffffu);                         // first minimum (lowest d on ties)
+    int best = (int)(key & 0xffffu);                               // first minimum (lowest d on ties)
     const int minS = (int)(key >> 16);
+    if (e.way3) {
+        // MODE_SGBM_3WAY: a tied minimum goes to cv2's 8-lane winner (b2s_tie8_*, common.cuh).  Rare: the whole warp
+        // takes the slow path when any of its pixels has a tie (it gives the first minimum again where there is none).
+        bool tie = false;
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            const int d0 = dbase + (IL ? i : 2 * i), d1 = dbase + (IL ? R + i : 2 * i + 1);
+            tie = tie || ((int)(Sv[i] & 0xffffu) == minS && d0 != best && d0 < e.D) || ((int)(Sv[i] >> 16) == minS && d1 != best && d1 < e.D);
+        }
+        if (__any_sync(0xffffffffu, tie)) {
+            unsigned long long w8 = 0ull;
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                const int d0 = dbase + (IL ? i : 2 * i), d1 = dbase + (IL ? R + i : 2 * i + 1);
+                if ((int)(Sv[i] & 0xffffu) == minS && d0 < e.D) w8 = b2s_tie8_merge(w8, b2s_tie8_one(d0));
+                if ((int)(Sv[i] >> 16) == minS && d1 < e.D) w8 = b2s_tie8_merge(w8, b2s_tie8_one(d1));
+            }
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) w8 = b2s_tie8_merge(w8, __shfl_xor_sync(0xffffffffu, w8, o));
+            best = b2s_tie8_best(w8);
+        }
+    }
 
     // uniqueness: exists d, |d - best| > 1, S(d) * (100 - uniq) < minS * 100
     const int mul = 100 - e.uniq;
@@ -247,6 +269,7 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
         // (MODE_SGBM_3WAY, e.uqle: S * mul <= minS * 100  <=>  S < floor(minS * 100 / mul) + 1)
         const unsigned a = (unsigned)(minS * 100 + mul - 1 + e.uqle);
         unsigned T = (unsigned)(((unsigned long long)a * magic) >> 40);
+        if (e.uqle) T = (T & 0x8000u) ? 0u : (T & 0xffffu);        // cv2's 3WAY compares against (int16)T: wraps, <= 0 rejects nothing
         T = min(T, 0x8000u);
         const uint32_t K = (0x8000u - T) * 0x10001u;               // S + K has bit 15 set  <=>  S >= T
         uint32_t acc = 0;
@@ -292,7 +315,8 @@ __device__ __forceinline__ void wta(const uint32_t (&Sv)[R], int lane, const Sgb
     }
     const unsigned gshift = (threadIdx.x & 31) & ~(G - 1);
     const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << (G & 31)) - 1u) << gshift);
-    const bool bad = (__ballot_sync(0xffffffffu, bad_lane) & gmask) != 0;
+    // every S saturated: cv2's search (strict compare from bestDisp = -1) has no winner and writes INVALID; not MODE_SGBM_3WAY
+    const bool bad = (__ballot_sync(0xffffffffu, bad_lane) & gmask) != 0 || (minS >= 32767 && !e.way3);
 
     // neighbours of the winner through the group's scratch row
     st_regs<R, CSB>(scr + (CSB == 16 ? dbase : lane * 8), Sv);

@@ -14,7 +14,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 sys.path.insert(0, os.path.dirname(HERE))
 
-from vectors import SGBM_VECTORS, SGBM_COLOR_VECTORS, BM_VECTORS, sgbm_kwargs, sgbm_pair, color_pair   # noqa: E402
+from vectors import (SGBM_VECTORS, SGBM_COLOR_VECTORS, SGBM_SOAK_VECTORS, BM_VECTORS, sgbm_kwargs, sgbm_pair, color_pair,   # noqa: E402
+                     soak_pair)
 from stereo_match_b200.synth import synth_pair, KITTI_Q                # noqa: E402
 
 assert cv2.__version__ == "4.13.0", cv2.__version__
@@ -26,6 +27,11 @@ for i in (0, 1, 3, 5, 6, 7, 11, 13, 26, 27, 30, 36, 37, 40):   # 26.. : MODE_HH4
     out["sgbm%d_l" % i], out["sgbm%d_r" % i] = l, r
     out["sgbm%d_v" % i] = np.array(v, np.int32)
     out["sgbm%d_d" % i] = cv2.StereoSGBM_create(**sgbm_kwargs(v)).compute(l, r)
+for i, v in enumerate(SGBM_SOAK_VECTORS):                   # the cv2 rules the randomised soaks found (ties, 16-bit wrap, saturation)
+    l, r = soak_pair(v)
+    out["soak%d_l" % i], out["soak%d_r" % i] = l, r
+    out["soak%d_v" % i] = np.array(v[1:], np.int32)
+    out["soak%d_d" % i] = cv2.StereoSGBM_create(**sgbm_kwargs(v[2:])).compute(l, r)
 for i, seed in SGBM_COLOR_VECTORS[:4]:                      # 3-channel input
     v = SGBM_VECTORS[i]
     l, r = color_pair(v[0], v[1], max(v[2] + v[3], 8), seed)

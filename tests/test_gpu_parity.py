@@ -10,8 +10,8 @@ import torch
 
 import stereo_match_b200 as sm
 from stereo_match_b200.synth import synth_pair, KITTI_Q
-from vectors import (SGBM_VECTORS, SGBM_ERROR_VECTORS, SGBM_UNPINNED_VECTORS, SGBM_COLOR_VECTORS, BM_VECTORS, sgbm_kwargs,
-                     sgbm_pair, color_pair)
+from vectors import (SGBM_VECTORS, SGBM_ERROR_VECTORS, SGBM_UNPINNED_VECTORS, SGBM_COLOR_VECTORS, SGBM_SOAK_VECTORS, BM_VECTORS,
+                     sgbm_kwargs, sgbm_pair, color_pair, soak_pair)
 
 pytestmark = pytest.mark.gpu
 
@@ -30,6 +30,25 @@ def test_sgbm_matches_oracle(i, v, port, cv2ref):
     got = m.compute(l, r)
     assert got.dtype == np.int16 and got.shape == l.shape
     assert np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
+
+
+@pytest.mark.parametrize("v", SGBM_SOAK_VECTORS, ids=["%s%d-" % v[:2] + "-".join(str(x) for x in v[2:7]) + "-m%d" % v[12] for v in SGBM_SOAK_VECTORS])
+def test_sgbm_soak_regressions(v, port, cv2ref):
+    """The cv2 rules the randomised soaks found (tests/vectors.py SGBM_SOAK_VECTORS): MODE_SGBM_3WAY's 8-lane winner on tied
+    minima and its wrapping 16-bit uniqueness threshold; a pixel whose S are all saturated has no winner.  A batch of the
+    pair and its row-reversed copy checks the warp-wide slow path against pixels of another image next to it."""
+    l, r = soak_pair(v)
+    kw = sgbm_kwargs(v[2:])
+    want = cv2ref.sgbm_compute(l, r, **kw)
+    assert np.array_equal(port.sgbm_compute(l, r, **kw), want), "oracle port disagrees with cv2"
+    m = sm.StereoSGBM_create(**kw)
+    got = m.compute(l, r)
+    assert not m.overflowed()
+    assert np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
+    l2, r2 = np.ascontiguousarray(l[::-1]), np.ascontiguousarray(r[::-1])
+    out = m.compute(torch.from_numpy(np.stack([l, l2])).cuda(), torch.from_numpy(np.stack([r, r2])).cuda()).cpu().numpy()
+    assert np.array_equal(out[0], want)
+    assert np.array_equal(out[1], cv2ref.sgbm_compute(l2, r2, **kw))
 
 
 @pytest.mark.parametrize("i,seed", SGBM_COLOR_VECTORS)

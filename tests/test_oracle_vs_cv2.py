@@ -5,8 +5,8 @@ import os
 import numpy as np
 import pytest
 
-from vectors import (SGBM_VECTORS, SGBM_ERROR_VECTORS, SGBM_COLOR_VECTORS, BM_VECTORS, sgbm_kwargs, sgbm_pair,
-                     color_pair)
+from vectors import (SGBM_VECTORS, SGBM_ERROR_VECTORS, SGBM_COLOR_VECTORS, SGBM_SOAK_VECTORS, BM_VECTORS, sgbm_kwargs,
+                     sgbm_pair, color_pair, soak_pair)
 from stereo_match_b200.synth import synth_pair, KITTI_Q
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cv2_4_13_0.npz")
@@ -25,6 +25,16 @@ def _ids(vs):
 def test_sgbm_port_equals_cv2(i, v, port, cv2ref):
     l, r = sgbm_pair(i, v)
     kw = sgbm_kwargs(v)
+    got, want = port.sgbm_compute(l, r, **kw), cv2ref.sgbm_compute(l, r, **kw)
+    assert np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
+
+
+@pytest.mark.parametrize("v", SGBM_SOAK_VECTORS, ids=["%s%d-" % v[:2] + "-".join(str(x) for x in v[2:7]) + "-m%d" % v[12] for v in SGBM_SOAK_VECTORS])
+def test_sgbm_port_soak_regressions(v, port, cv2ref):
+    """cv2 rules found by the randomised soaks: 3WAY's 8-lane winner on tied minima, its 16-bit wrapping uniqueness
+    threshold, and "every S saturated -> no winner".  Each vector failed before the rule was restated."""
+    l, r = soak_pair(v)
+    kw = sgbm_kwargs(v[2:])
     got, want = port.sgbm_compute(l, r, **kw), cv2ref.sgbm_compute(l, r, **kw)
     assert np.array_equal(got, want), "%d pixels differ" % (got != want).sum()
 
@@ -108,6 +118,16 @@ def test_golden_sgbm(port, gold):
         assert v == SGBM_VECTORS[i]
         got = port.sgbm_compute(gold["sgbm%d_l" % i], gold["sgbm%d_r" % i], **sgbm_kwargs(v))
         assert np.array_equal(got, gold["sgbm%d_d" % i]), "golden sgbm vector %d" % i
+
+
+def test_golden_sgbm_soak(port, gold):
+    ids = sorted(int(k[4:-2]) for k in gold.files if k.startswith("soak") and k.endswith("_d"))
+    assert len(ids) == len(SGBM_SOAK_VECTORS)
+    for i in ids:
+        v = SGBM_SOAK_VECTORS[i]
+        assert tuple(int(x) for x in gold["soak%d_v" % i]) == v[1:]
+        got = port.sgbm_compute(gold["soak%d_l" % i], gold["soak%d_r" % i], **sgbm_kwargs(v[2:]))
+        assert np.array_equal(got, gold["soak%d_d" % i]), "golden soak vector %d" % i
 
 
 def test_golden_sgbm_color(port, gold):

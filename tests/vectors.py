@@ -88,6 +88,49 @@ SGBM_UNPINNED_VECTORS = [
 ]
 
 
+# Found by the randomised soaks (tests/soak_oracle_vs_cv2.py, tools/soak_parity.py) in round 2: three cv2 4.13.0 rules the
+# vectors above never reached.  (pair kind, seed) + the 13 fields of SGBM_VECTORS.
+#   ties  : MODE_SGBM_3WAY picks a tied minimum on 8 SIMD lanes (last minimum of each lane, smallest position over lanes)
+#   wrap  : MODE_SGBM_3WAY compares S against (int16)(100 * minS / (100 - ratio) + 1): wraps for a large ratio / large costs
+#   sat   : every S of a pixel saturated at 32767 -> cv2's strict search finds no winner -> INVALID
+SGBM_SOAK_VECTORS = [
+    ("synth", 12, 159, 1, 0, 128, 1, 37, 47, 100000, 63, 0, 2, 0, 0),        # ties, one row, R = 8
+    ("synth", 1, 150, 9, 0, 64, 1, 3, 8, 1, 63, 0, 2, 0, 0),                 # ties, R = 4
+    ("synth", 21, 70, 9, 0, 16, 1, 3, 8, 1, 63, 0, 2, 0, 0),                 # ties, R = 2
+    ("synth", 41, 140, 9, 0, 96, 1, 3, 8, 1, 15, 0, 2, 0, 0),                # ties, R = 6
+    ("synth", 339, 313, 8, 0, 256, 1, 3, 7, 1, 15, 0, 2, 0, 0),              # ties, 16 lanes
+    ("synth", 50, 330, 9, 0, 272, 1, 3, 7, 1, 15, 0, 2, 0, 0),               # ties, 32 lanes, padded D
+    ("synth", 5, 560, 9, 0, 528, 1, 3, 7, 1, 15, 0, 2, 0, 0),                # ties, D > 512: k_wta
+    ("synth", 7, 272, 26, 7, 128, 5, 2000, 5309, 1, 63, 99, 2, 0, 0),        # wrap, R = 8
+    ("synth", 8, 150, 30, 0, 48, 5, 1500, 5000, 1, 63, 99, 2, 0, 0),         # wrap, R = 4 padded
+    ("synth", 10, 580, 12, 0, 528, 5, 1500, 5000, 1, 63, 99, 2, 0, 0),       # wrap, k_wta
+    ("synth", 4, 342, 74, -60, 128, 1, 68, 229, -1, 15, 99, 2, 60, 2),       # wrap and ties, negative range, speckle filter
+    ("synth", 535, 157, 98, 0, 128, 7, 3337, 4540, 50, 63, 0, 1, 0, 0),      # sat, MODE_HH, R = 8 (saturating accumulation)
+    ("synth", 101, 120, 60, 0, 48, 7, 3337, 4540, 50, 63, 0, 1, 0, 0),       # sat, R = 4
+    ("ramp", 3, 100, 40, 0, 48, 9, 10, 100, 50, 63, 0, 1, 0, 0),             # sat: half of the image has no winner at all
+    ("ramp", 3, 180, 40, 0, 128, 9, 10, 100, 50, 63, 0, 1, 0, 0),
+    ("ramp", 3, 100, 40, 0, 48, 9, 10, 100, 50, 63, 10, 1, 30, 2),
+    ("ramp", 3, 180, 40, 0, 128, 9, 10, 100, 50, 63, 0, 2, 0, 0),            # 3WAY on the same pair: it does find winners
+    ("ramp", 4, 620, 24, 0, 528, 9, 10, 100, 50, 63, 0, 1, 0, 0),            # sat, per-direction kernels + k_wta
+]
+
+
+def soak_pair(v):
+    """The image pair of one SGBM_SOAK_VECTORS entry.  "ramp": the lower half is a bright rising saw-tooth against a dark
+    falling one, a large cost at EVERY disparity; the upper half an ordinary matching pair."""
+    import numpy as np
+    kind, seed, w, h, minD, D = v[:6]
+    if kind == "synth":
+        return synth_pair(w, h, max(D + minD, 8), seed=seed)
+    rng = np.random.default_rng(9000 + seed)
+    x, y = np.arange(w)[None, :], np.arange(h)[:, None]
+    l = (192 + ((9 * x + 2 * y) % 64) + rng.integers(0, 3, (h, w)) - 1).clip(0, 255).astype(np.uint8)
+    r = (63 - ((9 * x + 3 * y) % 64) + rng.integers(0, 3, (h, w)) + 1).clip(0, 255).astype(np.uint8)
+    a, b = synth_pair(w, h, 8, seed=seed)
+    l[:h // 2], r[:h // 2] = a[:h // 2], b[:h // 2]
+    return l, r
+
+
 def sgbm_kwargs(v):
     w, h, minD, D, bs, P1, P2, lr, cap, uq, mode, spw, spr = v
     return dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=P1, P2=P2, disp12MaxDiff=lr,
