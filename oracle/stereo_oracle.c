@@ -604,7 +604,8 @@ ORC_API void orc_reproject(const float* disp, int H, int W, const double* Q, int
             double d = (double)disp[(size_t)y * W + x];
             double P[4];
             for (int k = 0; k < 4; k++)
-                P[k] = Q[4 * k + 0] * x + Q[4 * k + 1] * y + Q[4 * k + 2] * d + Q[4 * k + 3];
+                /* cv2's Matx product: s = 0; s += q * v for the four terms in order (the +0 start turns a leading -0 into +0) */
+                P[k] = 0.0 + Q[4 * k + 0] * x + Q[4 * k + 1] * y + Q[4 * k + 2] * d + Q[4 * k + 3];
             double iw = 1.0 / P[3];
             float* o = xyz + ((size_t)y * W + x) * 3;
             for (int k = 0; k < 3; k++) o[k] = (float)((double)(float)P[k] * iw);

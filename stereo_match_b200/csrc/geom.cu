@@ -25,7 +25,9 @@ k_reproject(const T* __restrict__ disp, int H, int W, QMat Q, float scale, int h
     double P[4];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        double a = __dmul_rn(Q.q[4 * k + 0], (double)x);
+        // cv2's Matx product starts its accumulator at +0.0 (s = 0; s += a*b): a leading -0 product (negative or -0 entry
+        // of Q at x = 0) becomes +0, which decides the sign of a zero / infinite result
+        double a = __dadd_rn(0.0, __dmul_rn(Q.q[4 * k + 0], (double)x));
         a = __dadd_rn(a, __dmul_rn(Q.q[4 * k + 1], (double)y));
         a = __dadd_rn(a, __dmul_rn(Q.q[4 * k + 2], d));
         P[k] = __dadd_rn(a, Q.q[4 * k + 3]);

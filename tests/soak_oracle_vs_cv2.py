@@ -1,5 +1,6 @@
 """Randomised soak of the CPU restatement (oracle/) against live cv2, far beyond the committed vectors: every mode,
-tiny and saturating penalties, uniquenessRatio up to 99, fully negative ranges, colour, blockSize 1-11.  Not collected by
+tiny and saturating penalties, uniquenessRatio up to 99, fully negative ranges, colour, blockSize 1-11; StereoBM with any
+window / range / filter; remap / cvtColor / medianBlur / filterSpeckles / reprojectImageTo3D (generators: tools/soak_cases.py, shared with the engine's soak tools/soak_parity.py).  Not collected by
 pytest (a script: it takes minutes); tests/test_oracle_vs_cv2.py holds the cases it found as fixed regressions.
 
     python tests/soak_oracle_vs_cv2.py [n_cases] [seed0] [workers]
@@ -15,41 +16,58 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
-def draw(k):
-    from stereo_match_b200.synth import synth_pair
-    from vectors import color_pair
-    rng = np.random.default_rng(777000 + k)
-    D = int(rng.choice([16, 32, 48, 64, 96, 128, 128, 256]))
-    bs = int(rng.choice([1, 1, 3, 5, 7, 9, 11]))
-    cn = 3 if rng.random() < 0.15 and bs <= 5 else 1
-    cap = int(rng.choice([1, 15, 31, 63]))
-    cmax = bs * bs * (2 * (max(cap, 15) | 1) + 63) * cn
-    hi = (32767 - 2 * cmax) // 3
-    if hi < 16:
-        return None
-    regime = int(rng.integers(0, 3))                       # tiny / ordinary / as large as the 16-bit domain allows
-    P2 = int(rng.integers(3, 120)) if regime == 0 else int(rng.integers(8, min(hi, 3000) + 1)) if regime == 1 else int(rng.integers(hi // 2, hi + 1))
-    P1 = int(rng.integers(1, max(P2, 2)))
-    minD = int(rng.choice([0, 0, 0, 7, -9, -D // 2, -D]))
-    w1 = int(rng.choice([rng.integers(bs, 30), rng.integers(30, 120)]))
-    w = w1 + max(D + minD, 0) - min(minD, 0)
-    h = int(rng.choice([rng.integers(1, 12), rng.integers(12, 50)]))
-    kw = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=P1, P2=P2, disp12MaxDiff=int(rng.choice([-1, 0, 1, 2, 50, 100000])),
-              preFilterCap=cap, uniquenessRatio=int(rng.choice([0, 1, 5, 15, 40, 60, 90, 99])), speckleWindowSize=int(rng.choice([0, 0, 30])),
-              speckleRange=int(rng.choice([1, 2])), mode=int(rng.integers(0, 4)))
-    maxd = max(D + minD, 8)
-    l, r = synth_pair(w, h, maxd, seed=k) if cn == 1 else color_pair(w, h, maxd, k)
-    if rng.random() < 0.2:                                  # flat, mismatching halves: every path cost saturates
-        l = l.copy(); r = r.copy()
-        l[:, w // 2:] = 255 - l[:, w // 2:] // 8
-        r[:, w // 2:] = r[:, w // 2:] // 8
-    return kw, l, r
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+
+
+class _OracleOps:
+    """The restatement's stage operators under the engine's (= cv2's) names, for soak_cases.ops_failures."""
+    @staticmethod
+    def remap(src, mx, my, interpolation):
+        from oracle import port
+        return port.remap(src, mx, my)
+
+    @staticmethod
+    def cvtColor(src, code):
+        from oracle import port
+        return port.bgr2gray(src)
+
+    @staticmethod
+    def medianBlur(d, k):
+        from oracle import port
+        return port.median3(d)
+
+    @staticmethod
+    def filterSpeckles(img, newVal, size, diff):
+        from oracle import port
+        return port.filter_speckles(img, newVal, size, diff), None
+
+    @staticmethod
+    def reprojectImageTo3D(d, Q, handleMissingValues=False):
+        from oracle import port
+        return port.reproject(d, Q, handleMissingValues)
+
+
+def one_ops(k):
+    import cv2
+    from soak_cases import ops_failures
+    f = ops_failures(k, _OracleOps, cv2)
+    return (k, len(f), f, "ops") if f else None
 
 
 def one(k):
+    """k >= 0: StereoSGBM case k of tools/soak_cases.gen_wide ; k < 0: StereoBM case -k-1 of gen_bm"""
     import cv2
-    from oracle import port
-    c = draw(k)
+    from oracle import port, cv2ref
+    from soak_cases import gen_wide, gen_bm
+    if k < 0:
+        D, bs, setters, l, r = gen_bm(-k - 1)
+        want = cv2ref.bm_compute(l, r, D, bs, **setters)
+        if "speckleWindowSize" in setters and not (want != (setters["minDisparity"] - 1) * 16).any():
+            return None           # cv2 returns uninitialised memory when nothing is valid and a speckle window is set
+        got = port.bm_compute(l, r, D, bs, **setters)
+        n = int((got != want).sum())
+        return (k, n, (D, bs, setters), l.shape) if n else None
+    c = gen_wide(k)
     if c is None:
         return None
     kw, l, r = c
@@ -67,8 +85,9 @@ if __name__ == "__main__":
     s0 = int(sys.argv[2]) if len(sys.argv) > 2 else 0
     nw = int(sys.argv[3]) if len(sys.argv) > 3 else max(1, (os.cpu_count() or 2) // 2)
     with mp.get_context("fork").Pool(nw) as pool:
-        res = [x for x in pool.imap_unordered(one, range(s0, s0 + n), chunksize=4) if x]
+        res = [x for x in pool.imap_unordered(one, list(range(s0, s0 + n)) + [-1 - i for i in range(s0, s0 + n)], chunksize=4) if x]
+        res += [x for x in pool.imap_unordered(one_ops, range(s0, s0 + n), chunksize=4) if x]
     for k, npx, kw, shape in sorted(res):
         print("FAIL case %d: %d pixels differ %r %r" % (k, npx, kw, shape))
-    print("oracle soak: %d cases, %d failures" % (n, len(res)))
+    print("oracle soak: %d StereoSGBM + %d StereoBM + %d stage-operator cases, %d failures" % (n, n, n, len(res)))
     sys.exit(1 if res else 0)

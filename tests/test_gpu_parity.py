@@ -219,6 +219,18 @@ def test_reproject_bitwise(cv2ref):
                 assert np.all(np.abs(got[fin] - want[fin]) <= 1e-5 * np.maximum(np.abs(want[fin]), 1e-30))
 
 
+def test_reproject_dense_q_signed_zeros(cv2ref):
+    """Dense Q matrices with zeros of both signs (tests/vectors.py reproject_q_cases): bitwise, signs of 0 / inf included."""
+    from vectors import reproject_q_cases
+    for Q, d in reproject_q_cases():
+        for Qm in (Q, Q.astype(np.float32)):
+            for dd in (d, d.astype(np.float32) / 16, (d & 0xff).astype(np.uint8)):
+                for hm in (False, True):
+                    want, got = cv2ref.reproject(dd, Qm, hm), sm.reprojectImageTo3D(dd, Qm, handleMissingValues=hm)
+                    nan = np.isnan(want) & np.isnan(got)
+                    assert np.array_equal(np.where(nan, 0, got.view(np.uint32)), np.where(nan, 0, want.view(np.uint32)))
+
+
 def test_project_points_3d_matches_reference_semantics(cv2ref):
     """stereo_vision.py:203-209: /16 then reprojectImageTo3D with a float32 Q."""
     rng = np.random.default_rng(5)

@@ -109,6 +109,18 @@ def test_stage_ports_equal_cv2(port, cv2ref):
     assert np.array_equal(port.bgr2gray(src), cv2ref.bgr2gray(src))
 
 
+def test_reproject_dense_q_signed_zeros(port, cv2ref):
+    """Bitwise, the sign of zeros and infinities included (NaN payloads excepted), for Q matrices beyond the reference's."""
+    from vectors import reproject_q_cases
+    for Q, d in reproject_q_cases():
+        for Qm in (Q, Q.astype(np.float32)):
+            for dd in (d, d.astype(np.float32) / 16, (d & 0xff).astype(np.uint8)):
+                for hm in (False, True):
+                    want, got = cv2ref.reproject(dd, Qm, hm), port.reproject(dd, Qm, hm)
+                    nan = np.isnan(want) & np.isnan(got)
+                    assert np.array_equal(np.where(nan, 0, got.view(np.uint32)), np.where(nan, 0, want.view(np.uint32)))
+
+
 # ---- committed golden fixtures (no cv2 needed) ----------------------------------------------
 def test_golden_sgbm(port, gold):
     ids = sorted(int(k[4:-2]) for k in gold.files if k.startswith("sgbm") and k.endswith("_d"))

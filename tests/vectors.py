@@ -173,3 +173,21 @@ CFG3 = dict(w=1242, h=375, seed=1, kw=dict(minDisparity=0, numDisparities=128, b
             disp12MaxDiff=1, uniquenessRatio=15, speckleWindowSize=100, speckleRange=2, preFilterCap=63, mode=1))
 CFG4 = dict(w=2864, h=1988, seed=4, kw=dict(minDisparity=0, numDisparities=256, blockSize=5, P1=600, P2=2400,
             disp12MaxDiff=1, uniquenessRatio=15, speckleWindowSize=100, speckleRange=2, preFilterCap=63, mode=1))
+
+
+# reprojectImageTo3D with dense Q matrices holding zeros of BOTH signs and negative first-column entries (found by the
+# operator soak): cv2's 4x4 product starts its accumulator at +0.0, which decides the sign of a zero or infinite result
+def reproject_q_cases():
+    import numpy as np
+    rng = np.random.default_rng(8)
+    out = []
+    for k in range(6):
+        Q = rng.standard_normal((4, 4)) * rng.choice([1.0, 100.0, 1e-3], (4, 4)) * (rng.random((4, 4)) < 0.6)
+        if k == 0:
+            Q = np.array([[42.3, 161.9, 109.6, -0.0], [-44.7, 1.14, 6.84, -0.087], [-0.0, -7.8e-4, -0.0, -0.0], [8.3e-4, 18.6, -0.0, -1.29]])
+        if k == 1:
+            Q = np.array([[-1.4e-3, -0.97, -0.71, -0.0], [-92.6, 0.33, -8.4e-4, -1.1e-4], [9.19, -0.0, 1.9, 151.4], [-8.2e-4, -2.04, -0.0, -0.0]])
+        d = (rng.integers(-1, 60, (23, 41)) * 8).astype(np.int16)
+        d[rng.random(d.shape) < 0.3] = -16
+        out.append((Q, d))
+    return out

@@ -35,3 +35,110 @@ def gen(k, seed0=0):
     l, r = synth_pair(w, h, maxd, seed=k) if cn == 1 else color_pair(w, h, maxd, k)
     B = int(rng.choice([1, 1, 3]))
     return kw, l, r, cn, B
+
+
+def gen_wide(k):
+    """Every StereoSGBM regime: any numDisparities / blockSize, tiny, ordinary and as-large-as-the-domain-allows penalties,
+    ratios up to 99, flat mismatching halves (saturating costs).  -> (kw, left, right) or None."""
+    rng = np.random.default_rng(777000 + k)
+    D = int(rng.choice([16, 32, 48, 64, 96, 128, 128, 256]))
+    bs = int(rng.choice([1, 1, 3, 5, 7, 9, 11]))
+    cn = 3 if rng.random() < 0.15 and bs <= 5 else 1
+    cap = int(rng.choice([1, 15, 31, 63]))
+    cmax = bs * bs * (2 * (max(cap, 15) | 1) + 63) * cn
+    hi = (32767 - 2 * cmax) // 3
+    if hi < 16:
+        return None
+    regime = int(rng.integers(0, 3))
+    P2 = int(rng.integers(3, 120)) if regime == 0 else int(rng.integers(8, min(hi, 3000) + 1)) if regime == 1 else int(rng.integers(hi // 2, hi + 1))
+    P1 = int(rng.integers(1, max(P2, 2)))
+    minD = int(rng.choice([0, 0, 0, 7, -9, -D // 2, -D]))
+    w1 = int(rng.choice([rng.integers(bs, 30), rng.integers(30, 120)]))
+    w = w1 + max(D + minD, 0) - min(minD, 0)
+    h = int(rng.choice([rng.integers(1, 12), rng.integers(12, 50)]))
+    kw = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=P1, P2=P2, disp12MaxDiff=int(rng.choice([-1, 0, 1, 2, 50, 100000])),
+              preFilterCap=cap, uniquenessRatio=int(rng.choice([0, 1, 5, 15, 40, 60, 90, 99])), speckleWindowSize=int(rng.choice([0, 0, 30])),
+              speckleRange=int(rng.choice([1, 2])), mode=int(rng.integers(0, 4)))
+    maxd = max(D + minD, 8)
+    l, r = synth_pair(w, h, maxd, seed=k) if cn == 1 else color_pair(w, h, maxd, k)
+    if rng.random() < 0.2:
+        l, r = l.copy(), r.copy()
+        l[:, w // 2:] = 255 - l[:, w // 2:] // 8
+        r[:, w // 2:] = r[:, w // 2:] // 8
+    return kw, l, r
+
+
+def gen_bm(k):
+    """StereoBM: any window 5..31, numDisparities 16..256, minDisparity <= 0 (what createRightMatcher sets; cv2 itself leaks
+    stray pixels for positive ones), every filter.  -> (numDisparities, blockSize, setters, left, right)."""
+    rng = np.random.default_rng(555000 + k)
+    D = 16 * int(rng.choice([1, 2, 3, 4, 6, 8, 10, 16]))
+    bs = int(rng.choice([5, 7, 9, 11, 15, 17, 21, 23, 31]))
+    minD = int(rng.choice([0, 0, 0, -1, -7, -D + 1, -D, -D - 9]))
+    setters = dict(preFilterCap=int(rng.integers(1, 64)), textureThreshold=int(rng.choice([0, 1, 10, 100, 1000, 5000])),
+                   uniquenessRatio=int(rng.choice([0, 1, 5, 15, 50, 90])), minDisparity=minD)
+    if rng.random() < 0.4:
+        setters["speckleWindowSize"] = int(rng.choice([5, 40, 300]))
+        setters["speckleRange"] = int(rng.choice([-1, 0, 1, 4, 40]))
+    w = max(D + minD, 0) - min(minD, 0) + bs + int(rng.choice([rng.integers(1, 20), rng.integers(20, 160)]))
+    h = int(rng.choice([rng.integers(bs + 1, bs + 8), rng.integers(bs + 8, 120)]))
+    l, r = synth_pair(w, h, max(D + minD, 8), seed=12000 + k)
+    return D, bs, setters, l, r
+
+
+def gen_ops(k):
+    """Nasty inputs of the stage operators: map coordinates exactly on pixels / on the 1/32 grid of cv2's fixed-point weights /
+    far outside, sparse-to-dense random Q matrices with signed zeros, disparity maps with holes.
+    -> dict(src, mx, my, d, size, diff, Q)"""
+    rng = np.random.default_rng(424200 + k)
+    sh, sw = int(rng.integers(1, 120)), int(rng.integers(1, 200))
+    H, W = int(rng.integers(1, 90)), int(rng.integers(1, 160))
+    src = rng.integers(0, 256, (sh, sw, 3), dtype=np.uint8)
+    mx = (rng.random((H, W)) * (sw + 8) - 4).astype(np.float32)
+    my = (rng.random((H, W)) * (sh + 8) - 4).astype(np.float32)
+    kind = rng.integers(0, 5, (H, W))
+    mx = np.where(kind == 1, np.round(mx), mx)
+    my = np.where(kind == 1, np.round(my), my)
+    mx = np.where(kind == 2, np.round(mx * 32) / 32, mx)
+    my = np.where(kind == 2, np.floor(my) + 0.5, my)
+    mx = np.where(kind == 3, mx * float(rng.choice([30.0, -30.0, 1e4, 1e6])), mx)
+    my = np.where(kind == 3, my * float(rng.choice([1.0, -50.0, 1e6])), my)
+    d = (rng.integers(-1, int(rng.choice([3, 60, 2000])), (H, W)) * int(rng.integers(1, 17))).astype(np.int16)
+    d[rng.random((H, W)) < float(rng.choice([0.0, 0.3, 0.8]))] = -16
+    size, diff = int(rng.choice([0, 1, 7, 50, 400, 100000])), int(rng.choice([0, 1, 16, 32, 1000]))
+    Q = rng.standard_normal((4, 4)) * rng.choice([1.0, 100.0, 1e-3], (4, 4)) * (rng.random((4, 4)) < 0.7)    # zeros of both signs
+    return dict(src=src, mx=mx.astype(np.float32), my=my.astype(np.float32), d=d, size=size, diff=diff, Q=Q)
+
+
+def ops_failures(k, ops, cv2):
+    """Runs every stage operator of `ops` (the engine: stereo_match_b200; or an oracle adapter with the same names) against
+    cv2 on gen_ops(k) -> names of the operators that differ (bitwise; NaN payloads excepted)."""
+    c = gen_ops(k)
+    src, mx, my, d, Q = c["src"], c["mx"], c["my"], c["d"], c["Q"]
+    g = np.ascontiguousarray(src[..., 1])
+    fails = []
+    if not np.array_equal(ops.remap(src, mx, my, cv2.INTER_LINEAR), cv2.remap(src, mx, my, cv2.INTER_LINEAR)):
+        fails.append("remap3")
+    if not np.array_equal(ops.remap(g, mx, my, cv2.INTER_LINEAR), cv2.remap(g, mx, my, cv2.INTER_LINEAR)):
+        fails.append("remap1")
+    if hasattr(ops, "remap_gray") and not np.array_equal(
+            ops.remap_gray(src, mx, my), cv2.cvtColor(cv2.remap(src, mx, my, cv2.INTER_LINEAR), cv2.COLOR_BGR2GRAY)):
+        fails.append("remap_gray")
+    if not np.array_equal(ops.cvtColor(src, cv2.COLOR_BGR2GRAY), cv2.cvtColor(src, cv2.COLOR_BGR2GRAY)):
+        fails.append("cvtColor")
+    if not np.array_equal(ops.medianBlur(d, 3), cv2.medianBlur(d, 3)):
+        fails.append("median")
+    a, b = d.copy(), d.copy()
+    a = ops.filterSpeckles(a, -16, c["size"], c["diff"])[0]
+    cv2.filterSpeckles(b, -16, c["size"], c["diff"])
+    if not np.array_equal(a, b):
+        fails.append("speckles")
+    for Qm in (Q, Q.astype(np.float32)):
+        for dd in (d, d.astype(np.float32) / 16, d.astype(np.int32), (d & 0xff).astype(np.uint8)):
+            for hm in (False, True):
+                want = cv2.reprojectImageTo3D(dd, Qm, handleMissingValues=hm)
+                got = ops.reprojectImageTo3D(dd, Qm, handleMissingValues=hm)
+                nan = np.isnan(got) & np.isnan(want)
+                if not np.array_equal(np.where(nan, 0, got.view(np.uint32)), np.where(nan, 0, want.view(np.uint32))):
+                    fails.append("reproject %s Q%s hm%d" % (dd.dtype, Qm.dtype, hm))
+    return fails

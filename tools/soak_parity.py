@@ -1,6 +1,8 @@
 """Randomised parity soak of the engine against live cv2: many more shapes / parameters than the test suite (numDisparities 128 /
 256, every mode, ratios up to 99, penalties up to the edge of the 16-bit domain, fully negative ranges, colour, batches).
-usage: python tools/soak_parity.py [n_cases] [seed0]      (GPU box; prints failures, exits 1 on any)
+usage: python tools/soak_parity.py [n_cases] [seed0] [sgbm|wide|bm|ops]      (GPU box; prints failures, exits 1 on any)
+sgbm: the numDisparities 128 / 256 kernels (soak_cases.gen); wide: every regime (gen_wide); bm: StereoBM (gen_bm); ops: remap, cvtColor,
+medianBlur, filterSpeckles, reprojectImageTo3D.
 
 Round 2: 600 cases found 25 mismatches, all three of them cv2 rules the restatement did not have (tests/vectors.py
 SGBM_SOAK_VECTORS); 0 of 600 after."""
@@ -12,17 +14,44 @@ import cv2
 import numpy as np
 import torch
 
-from soak_cases import gen
+from soak_cases import gen, gen_wide, gen_bm, ops_failures
 
 import stereo_match_b200 as sm
 
 n, seed0 = (int(sys.argv[1]) if len(sys.argv) > 1 else 300), (int(sys.argv[2]) if len(sys.argv) > 2 else 0)
-bad = 0
-for k in range(n):
-    c = gen(k, seed0)
+which = sys.argv[3] if len(sys.argv) > 3 else "sgbm"
+bad = ran = 0
+
+
+for k in range(seed0, seed0 + n):
+    if which == "ops":
+        f = ops_failures(k, sm, cv2)
+        ran += 1
+        if f:
+            bad += 1
+            print("FAIL ops case %d: %s" % (k, ", ".join(f)))
+        continue
+    if which == "bm":
+        D, bs, setters, l, r = gen_bm(k)
+        ref = cv2.StereoBM_create(numDisparities=D, blockSize=bs)
+        m = sm.StereoBM_create(numDisparities=D, blockSize=bs)
+        for name, val in setters.items():
+            getattr(ref, "set" + name[0].upper() + name[1:])(val)
+            getattr(m, "set" + name[0].upper() + name[1:])(val)
+        want = ref.compute(l, r)
+        if "speckleWindowSize" in setters and not (want != (setters["minDisparity"] - 1) * 16).any():
+            continue              # cv2 returns uninitialised memory when nothing is valid and a speckle window is set
+        got = m.compute(l, r)
+        ran += 1
+        if not np.array_equal(got, want):
+            bad += 1
+            print("FAIL bm case %d: %d pixels differ, D %d bs %d %r shape %r" % (k, int((got != want).sum()), D, bs, setters, l.shape))
+        continue
+    c = gen(k) if which == "sgbm" else gen_wide(k)
     if c is None:
         continue
-    kw, l, r, cn, B = c
+    kw, l, r = c[:3]
+    cn, B = (c[3], c[4]) if which == "sgbm" else (l.ndim == 3 and 3 or 1, 1 + 2 * (k % 3 == 0))
     try:
         want = cv2.StereoSGBM_create(**kw).compute(l, r)
     except cv2.error:
@@ -40,8 +69,9 @@ for k in range(n):
             bad += 1
     if m.overflowed():
         continue
+    ran += 1
     if not np.array_equal(got, want):
         bad += 1
         print("FAIL case %d: %d pixels differ, %r shape %r cn %d batch %d" % (k, int((got != want).sum()), kw, l.shape, cn, B))
-print("soak: %d cases, %d failures" % (n, bad))
+print("soak %s: %d cases run, %d failures" % (which, ran, bad))
 sys.exit(1 if bad else 0)
