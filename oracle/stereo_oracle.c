@@ -83,6 +83,8 @@ static inline int bt(int u, int v, int lo1, int hi1, int lo2, int hi2)
 /* effective parameters, SURVEY.md A.0 */
 typedef struct {
     int minD, D, maxD, SW2, SH2, P1, P2, uniq, lrmax, ftzero, minX1, maxX1, width1, INVALID;
+    int chkSW2;    /* half window of the size check */
+    int rawbs;     /* blockSize as given (MODE_SGBM_3WAY's stripe overlap uses it without the fallback) */
 } eff_t;
 
 static eff_t effective(const orc_sgbm_params* p, int W)
@@ -91,6 +93,10 @@ static eff_t effective(const orc_sgbm_params* p, int W)
     e.minD = p->minDisparity; e.D = p->numDisparities; e.maxD = e.minD + e.D;
     int bs = p->blockSize > 0 ? p->blockSize : 5;
     e.SW2 = e.SH2 = bs / 2;
+    e.chkSW2 = bs / 2;                /* the "image too small" test is common code: always the 5-pixel fallback */
+    e.rawbs = p->blockSize;
+    /* MODE_SGBM_3WAY has its own fallback: blockSize <= 0 means a 3-pixel window there (probed against cv2 4.13.0) */
+    if (p->mode == 2 && p->blockSize <= 0) e.SW2 = e.SH2 = 1;
     e.P1 = p->P1 > 0 ? p->P1 : 2;
     e.P2 = imax(p->P2 > 0 ? p->P2 : 5, e.P1 + 1);
     e.uniq = p->uniquenessRatio >= 0 ? p->uniquenessRatio : 10;
@@ -185,8 +191,15 @@ static void cost_volume(const uint8_t* L, const uint8_t* R, int H, int W, int cn
 /* to pixel, i.e. q = p - (dx,dy).  Adds L_r into Ssum (int32).        */
 /* Lout (optional) receives L_r as int16, same layout as C.            */
 /* ------------------------------------------------------------------ */
-static void aggregate_dir(const int16_t* Cvol, int H, int w1, int D, int P1, int P2,
-                          int dx, int dy, int32_t* Ssum, int16_t* Lout)
+/* tail0 > 0: MODE_SGBM_3WAY with D not a multiple of 8 (probed against cv2 4.13.0, tests/test_oracle_vs_cv2.py).   */
+/* cv2 runs d < tail0 = 8 * (D / 8) on SIMD lanes and the rest in a scalar tail whose FIRST element takes its      */
+/* d - 1 neighbour from the wrong place in the two paths it updates in place:                                      */
+/*   tailmode 1 (down): from the buffer the SIMD loop has just stored to -- the NEW L_r(p, tail0 - 1) of this      */
+/*                      pixel instead of the predecessor's;                                                        */
+/*   tailmode 2 (<-)  : from element tail0 itself (L_r(q, tail0) + P1, which can never win: the neighbour is lost). */
+/* The -> path keeps its previous pixel in a second buffer and is unaffected.  D < 8 has no SIMD part: no quirk.   */
+static void aggregate_dir_ex(const int16_t* Cvol, int H, int w1, int D, int P1, int P2,
+                             int dx, int dy, int tail0, int tailmode, int32_t* Ssum, int16_t* Lout)
 {
     size_t rowsz = (size_t)w1 * D;
     int16_t* Lbuf = (int16_t*)malloc((size_t)H * rowsz * sizeof(int16_t));
@@ -207,6 +220,7 @@ static void aggregate_dir(const int16_t* Cvol, int H, int w1, int D, int P1, int
             for (int d = 0; d < D; d++) {
                 int a = inside ? Lq[d] : 0;
                 int b = inside ? (d > 0 ? Lq[d - 1] : 32767) + P1 : 0 + P1;
+                if (tail0 > 0 && d == tail0) b = (tailmode == 1 ? Lp[d - 1] : (inside ? Lq[d] : 0)) + P1;
                 int c = inside ? (d < D - 1 ? Lq[d + 1] : 32767) + P1 : 0 + P1;
                 /* outside: L_r(q,.)=0, minL=0 -> min(0, P1, P1, P2) = 0 */
                 int v = Cp[d] + imin(imin(a, b), imin(c, delta)) - delta;
@@ -219,6 +233,12 @@ static void aggregate_dir(const int16_t* Cvol, int H, int w1, int D, int P1, int
         }
     if (Lout) memcpy(Lout, Lbuf, (size_t)H * rowsz * sizeof(int16_t));
     free(minL); free(Lbuf);
+}
+
+static void aggregate_dir(const int16_t* Cvol, int H, int w1, int D, int P1, int P2,
+                          int dx, int dy, int32_t* Ssum, int16_t* Lout)
+{
+    aggregate_dir_ex(Cvol, H, w1, D, P1, P2, dx, dy, 0, 0, Ssum, Lout);
 }
 
 static const int DIRS[8][2] = {
@@ -247,12 +267,18 @@ static void wta_rows_ex(const int16_t* S, int H, int W, const eff_t* e, int le, 
             const int16_t* Sp = S + ((size_t)y * w1 + x) * D;
             int best = 0, minS = Sp[0];
             for (int d = 1; d < D; d++) if (Sp[d] < minS) { minS = Sp[d]; best = d; }
+            const int simdD = le ? ((D % 8) ? 8 * (D / 8) : D) : 0;   /* 3WAY: d < simdD on SIMD lanes, a scalar tail after */
             if (le) {
                 int last[8], j;
+                minS = 32767; best = 0;
+                for (int d = 0; d < simdD; d++) if (Sp[d] < minS) minS = Sp[d];
                 for (j = 0; j < 8; j++) last[j] = -1;
-                for (int d = 0; d < D; d++) if (Sp[d] == minS) last[d & 7] = d;
-                best = D;
-                for (j = 0; j < 8; j++) if (last[j] >= 0 && last[j] < best) best = last[j];
+                for (int d = 0; d < simdD; d++) if (Sp[d] == minS) last[d & 7] = d;
+                if (simdD > 0) {
+                    best = D;
+                    for (j = 0; j < 8; j++) if (last[j] >= 0 && last[j] < best) best = last[j];
+                }
+                for (int d = simdD; d < D; d++) if (Sp[d] < minS) { minS = Sp[d]; best = d; }   /* tail: strict, first */
             }
             /* every S saturated: cv2's search starts at (MAX_COST, bestDisp = -1) with a strict compare, finds nothing */
             /* and writes (-1 + minD) * 16 = INVALID, disp2 untouched (3WAY's non-strict lanes do find a winner)      */
@@ -261,7 +287,8 @@ static void wta_rows_ex(const int16_t* S, int H, int W, const eff_t* e, int le, 
             const int thr16 = le && e->uniq > 0 ? wrap16(minS * 100 / (100 - e->uniq) + 1) : 0;
             for (d = 0; d < D; d++) {
                 int lhs = Sp[d] * (100 - e->uniq), rhs = minS * 100;
-                if ((le ? (e->uniq > 0 && Sp[d] < thr16) : lhs < rhs) && abs(best - d) > 1) break;
+                /* 3WAY: the scalar tail d >= simdD uses the exact 32-bit rule of the other modes */
+                if ((le ? (e->uniq > 0 && (d < simdD ? Sp[d] < thr16 : lhs < rhs)) : lhs < rhs) && abs(best - d) > 1) break;
             }
             if (d < D) continue;
             int x2 = x + e->minX1 - best - e->minD;
@@ -342,9 +369,11 @@ static void wta_rows(const int16_t* S, int H, int W, const eff_t* e, int16_t* di
 /* unless the early start was clamped: then rows shift, as in cv2).                                             */
 /* hs: horizontal sums [H][width1][D]; raw: H*W before the median.                                              */
 /* ------------------------------------------------------------------ */
-static void sgbm_3way(const int32_t* hs, int H, int W, const eff_t* e, int16_t* raw)
+static int sgbm_3way(const int32_t* hs, int H, int W, const eff_t* e, int16_t* raw)
 {
-    const int sz = (H + 3) / 4, ov = e->SH2 + 1 + (sz + 9) / 10;       /* ceil(0.1*sz) */
+    /* the overlap takes blockSize as given, NOT the effective one (0 or negative: C division, -3 / 2 = -1) */
+    const int sz = (H + 3) / 4, ov = e->rawbs / 2 + 1 + (sz + 9) / 10;   /* + ceil(0.1*sz) */
+    if (ov < 0) return -1;                         /* blockSize far below zero: cv2 itself runs out of bounds */
     const size_t rowsz = (size_t)e->width1 * e->D;
     int16_t* buf = (int16_t*)malloc((size_t)4 * (sz + ov) * W * sizeof(int16_t));
     for (size_t i = 0; i < (size_t)4 * (sz + ov) * W; i++) buf[i] = (int16_t)e->INVALID;
@@ -359,9 +388,10 @@ static void sgbm_3way(const int32_t* hs, int H, int W, const eff_t* e, int16_t* 
                 for (int k = -e->SH2; k <= e->SH2; k++) v += hs[(size_t)iclamp(y + k, s0, H - 1) * rowsz + i];
                 Cv[(size_t)(y - s0) * rowsz + i] = wrap16(v);
             }
+        const int tail0 = (e->D % 8) ? 8 * (e->D / 8) : 0;
         aggregate_dir(Cv, hst, e->width1, e->D, e->P1, e->P2, 1, 0, Ssum, NULL);
-        aggregate_dir(Cv, hst, e->width1, e->D, e->P1, e->P2, 0, 1, Ssum, NULL);
-        aggregate_dir(Cv, hst, e->width1, e->D, e->P1, e->P2, -1, 0, Ssum, NULL);
+        aggregate_dir_ex(Cv, hst, e->width1, e->D, e->P1, e->P2, 0, 1, tail0, 1, Ssum, NULL);
+        aggregate_dir_ex(Cv, hst, e->width1, e->D, e->P1, e->P2, -1, 0, tail0, 2, Ssum, NULL);
         int16_t* S = Cv;                                                /* reuse */
         for (size_t i = 0; i < (size_t)hst * rowsz; i++) S[i] = sat16(Ssum[i]);
         int16_t* r = (int16_t*)malloc((size_t)hst * W * sizeof(int16_t));
@@ -375,6 +405,7 @@ static void sgbm_3way(const int32_t* hs, int H, int W, const eff_t* e, int16_t* 
     for (int i = 0; i < H; i++)
         memcpy(raw + (size_t)i * W, buf + ((size_t)(i / sz) * (sz + ov) + ov + i % sz) * W, W * sizeof(int16_t));
     free(buf);
+    return 0;
 }
 
 /* ------------------------------------------------------------------ */
@@ -399,14 +430,15 @@ ORC_API int orc_sgbm_compute_cn(const uint8_t* left, const uint8_t* right, int H
     size_t n = (size_t)H * W;
     /* cv2 4.13.0 (stereosgbm.cpp:511) raises cv2.error unless
        width - (minDisparity + numDisparities) > SADWindowSize/2 */
-    if (!(W - e.maxD > e.SW2)) return -2;
+    if (!(W - e.maxD > e.chkSW2)) return -2;
     if (e.width1 <= 0) { for (size_t i = 0; i < n; i++) disp[i] = (int16_t)e.INVALID; return 0; }
     int16_t* tmp = (int16_t*)malloc(n * sizeof(int16_t));
     if (p->mode == 2) {
         if (Cout || Sout) { free(tmp); return -1; }
         int32_t* hs = hsum_volume(left, right, H, W, cn, &e);
-        sgbm_3way(hs, H, W, &e, tmp);
+        int rc3 = sgbm_3way(hs, H, W, &e, tmp);
         free(hs);
+        if (rc3) { free(tmp); return rc3; }
     } else {
         size_t vol = (size_t)H * e.width1 * e.D;
         int16_t* Cvol = (int16_t*)malloc(vol * sizeof(int16_t));

@@ -69,6 +69,10 @@ static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, Sgb
     e.minD = p.minDisparity; e.D = p.numDisparities;
     const int bs = p.blockSize > 0 ? p.blockSize : 5;
     e.SW2 = bs / 2;
+    const int chk_sw2 = bs / 2;          // the size test below is common code in cv2: always the 5-pixel fallback
+    // MODE_SGBM_3WAY has its own fallback: blockSize <= 0 means a 3-pixel window there (probed against cv2 4.13.0)
+    if (p.mode == B2S_MODE_SGBM_3WAY && p.blockSize <= 0) e.SW2 = 1;
+    e.ov_raw = p.blockSize / 2 + 1;
     e.P1 = p.P1 > 0 ? p.P1 : 2;
     const int p2 = p.P2 > 0 ? p.P2 : 5;
     e.P2 = p2 > e.P1 + 1 ? p2 : e.P1 + 1;
@@ -83,10 +87,10 @@ static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, Sgb
     e.ndirs = p.mode == B2S_MODE_HH ? 8 : (p.mode == B2S_MODE_HH4 ? 4 : (p.mode == B2S_MODE_SGBM_3WAY ? 3 : 5));
     e.cn = 1; e.Hsrc = H; e.nst = 1; e.sz = e.ov = 0; e.uqle = 0; e.way3 = 0;
     // cv2 4.13.0 stereosgbm.cpp:511 raises cv2.error on this condition
-    if (!(W - maxD > e.SW2)) {
+    if (!(W - maxD > chk_sw2)) {
         b2s_set_error("StereoSGBM: Your input images are too small for your window size and max disparity "
                       "(expected: 'width - (params.minDisparity + params.numDisparities) > "
-                      "params.calcSADWindowSize().width/2'), where %d must be greater than %d", W - maxD, e.SW2);
+                      "params.calcSADWindowSize().width/2'), where %d must be greater than %d", W - maxD, chk_sw2);
         return B2S_E_INVALID;
     }
     if (e.ftzero > 127) { b2s_set_error("StereoSGBM: preFilterCap must be <= 127"); return B2S_E_UNSUPPORTED; }
@@ -101,8 +105,16 @@ static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, Sgb
     if (!e.G) for (int r : { 12, 16 }) if (64 * r >= e.D) { e.G = 32; e.R = r; break; }
     if (!e.G) { b2s_set_error("StereoSGBM: numDisparities > 1024 is not supported"); return B2S_E_UNSUPPORTED; }
     // (measured on B200 at D = 128: G=8/R=8 195 us per pair; G=4/R=16 287 us; G=16/R=4 237 us)
+    e.simdD = e.D;
+    if (p.mode == B2S_MODE_SGBM_3WAY && e.D % 8 != 0) {
+        // cv2's 3WAY handles the last D % 8 disparities in a scalar tail with rules of its own: those
+        // numDisparities run the per-direction kernels (sgbm_agg.cu) and k_wta, 32 lanes per pixel, natural cell order
+        e.simdD = 8 * (e.D / 8);
+        e.G = 32;
+        for (int r : { 2, 4, 8, 12, 16 }) if (64 * r >= e.D) { e.R = r; break; }
+    }
     e.Dp = 2 * e.R * e.G;
-    e.swz = (e.R == 8) ? 1 : 0;          // wavefront path with two 16-byte chunks per lane: permuted records
+    e.swz = (e.R == 8 && e.simdD == e.D) ? 1 : 0;   // wavefront path with two 16-byte chunks per lane: permuted records
     return B2S_OK;
 }
 
@@ -115,7 +127,7 @@ static SgbmEff volume_geometry(const SgbmEff& e, int cn)
     if (e.ndirs == 3) {
         v.nst = 4;
         v.sz = (e.H + 3) / 4;
-        v.ov = e.SW2 + 1 + (v.sz + 9) / 10;                 // SADWindowSize/2 + 1 + ceil(0.1 * stripe_sz)
+        v.ov = e.ov_raw + (v.sz + 9) / 10;                  // SADWindowSize/2 + 1 + ceil(0.1 * stripe_sz), SADWindowSize as given
         v.H = v.sz + v.ov < e.H ? v.sz + v.ov : e.H;
         v.batch = e.batch * 4;
         v.uqle = e.uniq > 0 ? 1 : 0;
@@ -126,7 +138,7 @@ static SgbmEff volume_geometry(const SgbmEff& e, int cn)
 
 struct SgbmLayout { size_t planar, descL, descR, cost, S, Sdbg, raw, rawv, key, rec, edge, labels, counts, total; };
 
-static bool uses_wave(const SgbmEff& e) { return e.R <= 8; }
+static bool uses_wave(const SgbmEff& e) { return e.R <= 8 && e.simdD == e.D; }
 
 // e: the images (batch pairs of H rows); v: volume_geometry(e, cn)
 static SgbmLayout sgbm_layout(const SgbmEff& e, const SgbmEff& v, bool speckle, bool keep_volumes)
@@ -249,6 +261,11 @@ extern "C" int b2s_sgbm_compute_cn(b2s_handle h, const uint8_t* left, const uint
     rc = sgbm_effective(h->sp, H, W, batch, e);
     if (rc) return rc;
     const SgbmEff v = volume_geometry(e, cn);          // the cost / S volumes (stripe images for MODE_SGBM_3WAY)
+    if (v.nst > 1 && v.ov < 0) {
+        b2s_set_error("StereoSGBM: MODE_SGBM_3WAY with blockSize %d makes cv2's stripe overlap negative (cv2 itself runs out of "
+                      "bounds there)", h->sp.blockSize);
+        return B2S_E_UNSUPPORTED;
+    }
     if ((long long)batch * cn * H * W >= (1ll << 31) || (long long)v.batch * v.H * W >= (1ll << 31)) {
         b2s_set_error("StereoSGBM: batch*channels*H*W must be < 2^31");
         return B2S_E_UNSUPPORTED;

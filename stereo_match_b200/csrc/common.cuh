@@ -26,6 +26,9 @@ struct SgbmEff {
                               // st of a pair starts at source row b2s_stripe_start() and clamps its block sum there
     int uqle;                 // 1: the uniqueness test rejects on equality as well (MODE_SGBM_3WAY with a ratio > 0), in
                               // 16 bits: S < (int16)(floor(100 * minS / (100 - ratio)) + 1), the threshold wrapping
+    int simdD;                // MODE_SGBM_3WAY with D % 8 != 0: cv2 runs d < simdD = 8 * (D / 8) on SIMD lanes and the rest in
+                              // a scalar tail with its own rules (sgbm_agg.cu TM, k_wta); D otherwise
+    int ov_raw;               // MODE_SGBM_3WAY's stripe overlap takes blockSize AS GIVEN: blockSize / 2 + 1 (C division)
     int way3;                 // 1: MODE_SGBM_3WAY's winner rule (b2s_tie8_*) ; 0: first minimum, and a pixel whose S are
                               // all saturated (minS = 32767) has no winner at all (cv2 starts from bestDisp = -1)
 };

@@ -1,5 +1,6 @@
 // sgbm_agg.cu -- SGBM path aggregation, one direction per launch: the generic path for
-// 512 < numDisparities <= 1024 (everything else runs the fused wavefront in sgbm_wave*.cu).
+// 512 < numDisparities <= 1024 and for MODE_SGBM_3WAY with numDisparities % 8 != 0 (cv2's scalar-tail rules, TM below);
+// everything else runs the fused wavefront in sgbm_wave*.cu.
 // Replaces the L_r recurrence inside cv2.StereoSGBM.compute (MODE_SGBM: 5 paths,
 // MODE_HH: 8 paths; reference call site stereo_vision/stereo_vision.py:178).
 //
@@ -84,10 +85,16 @@ __device__ __forceinline__ uint32_t group_min(uint32_t v)
 }
 
 // One aggregation step for a lane: Lp (in/out), C (cost), returns the lane-local packed min.
-template <int R, int G, bool PAD>
+//
+// TM (MODE_SGBM_3WAY with numDisparities % 8 != 0; cv2 4.13.0, probed -- oracle/stereo_oracle.c aggregate_dir_ex): cv2 runs
+// d < t0 = 8 * (D / 8) on SIMD lanes and the rest in a scalar tail whose FIRST element t0 takes its d - 1 neighbour from
+// the wrong place in the two paths cv2 updates in place.  qm[i] = 0xffff where register i's low cell is t0 (t0 is even).
+//   TM = 1 (down): the NEW L_r(p, t0 - 1) of this pixel (the SIMD loop has already stored it) instead of L_r(q, t0 - 1)
+//   TM = 2 (<-)  : L_r(q, t0) itself: + P1 it can never win, the neighbour is lost
+template <int R, int G, bool PAD, int TM>
 __device__ __forceinline__ uint32_t agg_step(uint32_t (&L)[R], const uint32_t (&C)[R], int lane,
                                              uint32_t p1x2, uint32_t deltax2, uint32_t minx2,
-                                             const uint32_t (&padm)[R])
+                                             const uint32_t (&padm)[R], const uint32_t (&qm)[R])
 {
     // neighbours across lanes: d-1 of my first cell, d+1 of my last cell
     uint32_t up = __shfl_up_sync(0xffffffffu, L[R - 1], 1, G);
@@ -102,6 +109,7 @@ __device__ __forceinline__ uint32_t agg_step(uint32_t (&L)[R], const uint32_t (&
         uint32_t next = (i + 1 < R) ? L[i + 1] : dn;
         uint32_t dm1 = __byte_perm(prev, cur, 0x5432);    // (d-1) for both halves
         uint32_t dp1 = __byte_perm(cur, next, 0x5432);    // (d+1) for both halves
+        if (TM == 2) dm1 = (dm1 & ~qm[i]) | (cur & qm[i]);
         uint32_t m = __vminu2(dm1, dp1);
         uint32_t t = __viaddmin_u16x2(m, p1x2, deltax2);  // min(m + P1, minL + P2)
         uint32_t u = __vminu2(cur, t);
@@ -114,8 +122,58 @@ __device__ __forceinline__ uint32_t agg_step(uint32_t (&L)[R], const uint32_t (&
     return mn;
 }
 
+// TM = 1: the down path of the scalar-tail case.  With its d - 1 neighbour taken from the CURRENT pixel, L_r(p, t0) can
+// fall below zero (cv2 and the restatement keep it as a signed int16; every other cell stays >= its cost), so this path
+// runs cell by cell in signed 32-bit arithmetic -- it is a corner of a corner, not a hot path.  Returns the lane's
+// signed minimum; minprev is the signed minimum of the predecessor.
+template <int R, int G, bool PAD>
+__device__ __forceinline__ int agg_step_tail_down(uint32_t (&L)[R], const uint32_t (&C)[R], int lane, int P1, int P2,
+                                                  int minprev, int D, int t0)
+{
+    const uint32_t up = __shfl_up_sync(0xffffffffu, L[R - 1], 1, G);
+    const uint32_t dn = __shfl_down_sync(0xffffffffu, L[0], 1, G);
+    const int vm1 = lane == 0 ? 32767 : (int)(int16_t)(up >> 16);
+    const int vp = lane == G - 1 ? 32767 : (int)(int16_t)(dn & 0xffffu);
+    const int delta = minprev + P2, dbase = lane * 2 * R;
+    int v[2 * R], nv[2 * R];
+#pragma unroll
+    for (int i = 0; i < R; i++) { v[2 * i] = (int)(int16_t)(L[i] & 0xffffu); v[2 * i + 1] = (int)(int16_t)(L[i] >> 16); }
+#pragma unroll
+    for (int c = 0; c < 2 * R; c++) {
+        const int cost = (int)((C[c >> 1] >> (16 * (c & 1))) & 0xffffu);
+        int b = (c > 0 ? v[c > 0 ? c - 1 : 0] : vm1) + P1;
+        if (c > 0 && dbase + c == t0) b = nv[c > 0 ? c - 1 : 0] + P1;              // the new value of this pixel
+        const int cc = (c < 2 * R - 1 ? v[c < 2 * R - 1 ? c + 1 : c] : vp) + P1;
+        int l = cost + min(min(v[c], b), min(cc, delta)) - minprev;
+        if (PAD && dbase + c >= D) l = 32767;
+        nv[c] = (int)(int16_t)l;
+    }
+    // t0 is the first cell of this lane: its neighbour is the previous lane's new last cell
+    const int nup = __shfl_up_sync(0xffffffffu, nv[2 * R - 1], 1, G);
+    if (dbase == t0 && lane > 0) {
+        const int cost = (int)(C[0] & 0xffffu);
+        const int cc = (2 * R > 1 ? v[1] : vp) + P1;
+        nv[0] = (int)(int16_t)(cost + min(min(v[0], nup + P1), min(cc, delta)) - minprev);
+    }
+    int mn = 32767;
+#pragma unroll
+    for (int i = 0; i < R; i++) {
+        L[i] = ((uint32_t)nv[2 * i] & 0xffffu) | ((uint32_t)nv[2 * i + 1] << 16);
+        mn = min(mn, min(nv[2 * i], nv[2 * i + 1]));
+    }
+    return mn;
+}
+
+// signed saturating S + L per half (the scalar-tail paths: S may hold the negative L of the down path)
+__device__ __forceinline__ uint32_t sat_add_s16x2(uint32_t a, uint32_t b)
+{
+    const int lo = max(-32768, min(32767, (int)(int16_t)(a & 0xffffu) + (int)(int16_t)(b & 0xffffu)));
+    const int hi = max(-32768, min(32767, (int)(int16_t)(a >> 16) + (int)(int16_t)(b >> 16)));
+    return ((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16);
+}
+
 #define AGG_NT 256
-template <int R, int G, bool PAD, bool FIRST>
+template <int R, int G, bool PAD, bool FIRST, int TM>
 __global__ void __launch_bounds__(AGG_NT)
 k_aggregate(const uint16_t* __restrict__ cost, uint16_t* __restrict__ S, SgbmEff e, int dx, int dy)
 {
@@ -143,6 +201,9 @@ k_aggregate(const uint16_t* __restrict__ cost, uint16_t* __restrict__ S, SgbmEff
         int d0 = lane * 2 * R + 2 * i;
         padm[i] = PAD ? ((d0 >= e.D ? 0x7fffu : 0u) | (d0 + 1 >= e.D ? 0x7fff0000u : 0u)) : 0u;
     }
+    uint32_t qm[R];
+#pragma unroll
+    for (int i = 0; i < R; i++) qm[i] = (TM != 0 && lane * 2 * R + 2 * i == e.simdD) ? 0xffffu : 0u;
     const uint32_t p1x2 = (uint32_t)e.P1 * 0x10001u;
     const uint32_t p2x2 = (uint32_t)e.P2 * 0x10001u;
 
@@ -150,6 +211,7 @@ k_aggregate(const uint16_t* __restrict__ cost, uint16_t* __restrict__ S, SgbmEff
 #pragma unroll
     for (int i = 0; i < R; i++) { L[i] = 0; Sv[i] = 0; Sn[i] = 0; }
     uint32_t minx2 = 0;
+    int minprev = 0;                               // TM = 1: signed
 
     size_t off = ((size_t)y * e.width1 + x) * e.Dp;
     load_regs<R>(cb + off, C);
@@ -168,19 +230,30 @@ k_aggregate(const uint16_t* __restrict__ cost, uint16_t* __restrict__ S, SgbmEff
             load_regs<R>(cb + offn, Cn);
             if (!FIRST) load_regs_rw<R>(sb + offn, Sn);
         }
-        uint32_t mn = agg_step<R, G, PAD>(L, C, lane, p1x2, minx2 + p2x2, minx2, padm);
-        // S accumulate
+        if (TM == 1) {
+            int mn = agg_step_tail_down<R, G, PAD>(L, C, lane, e.P1, e.P2, minprev, e.D, e.simdD);
 #pragma unroll
-        for (int i = 0; i < R; i++)
-            Sv[i] = FIRST ? L[i] : __viaddmin_u16x2(Sv[i], L[i], 0x7fff7fffu);
-        if (active) store_regs<R>(sb + off, Sv);
-        uint32_t m16 = min(mn & 0xffffu, mn >> 16);
-        m16 = group_min<G>(m16);
-        minx2 = m16 * 0x10001u;
+            for (int o = G / 2; o > 0; o >>= 1) mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+            minprev = mn;
+#pragma unroll
+            for (int i = 0; i < R; i++) Sv[i] = sat_add_s16x2(Sv[i], L[i]);
+            if (active) store_regs<R>(sb + off, Sv);
+        } else {
+            uint32_t mn = agg_step<R, G, PAD, TM>(L, C, lane, p1x2, minx2 + p2x2, minx2, padm, qm);
+            // S accumulate
+#pragma unroll
+            for (int i = 0; i < R; i++)
+                Sv[i] = FIRST ? L[i] : (TM == 2 ? sat_add_s16x2(Sv[i], L[i]) : __viaddmin_u16x2(Sv[i], L[i], 0x7fff7fffu));
+            if (active) store_regs<R>(sb + off, Sv);
+            uint32_t m16 = min(mn & 0xffffu, mn >> 16);
+            m16 = group_min<G>(m16);
+            minx2 = m16 * 0x10001u;
+        }
         if (wrap) {                                // the path enters from the image side
 #pragma unroll
             for (int i = 0; i < R; i++) L[i] = 0;
             minx2 = 0;
+            minprev = 0;
         }
 #pragma unroll
         for (int i = 0; i < R; i++) { C[i] = Cn[i]; Sv[i] = Sn[i]; }
@@ -197,12 +270,20 @@ static int launch_agg_rg(const uint16_t* cost, uint16_t* S, const SgbmEff& e, in
     const long long nlines = (dy == 0 ? e.H : e.width1) * (long long)e.batch;
     const int grid = b2s_cdiv(nlines * G, AGG_NT);
     const bool pad = e.D != e.Dp;
-    if (pad) {
-        if (first) k_aggregate<R, G, true, true><<<grid, AGG_NT, 0, st>>>(cost, S, e, dx, dy);
-        else       k_aggregate<R, G, true, false><<<grid, AGG_NT, 0, st>>>(cost, S, e, dx, dy);
+    // cv2's scalar tail of MODE_SGBM_3WAY (numDisparities % 8 != 0, at least one SIMD group): down = dir 2, <- = dir 4
+    const int tm = (e.simdD != e.D && e.simdD > 0) ? (dir == 2 ? 1 : (dir == 4 ? 2 : 0)) : 0;
+    if (tm == 1) {
+        if (pad) k_aggregate<R, G, true, false, 1><<<grid, AGG_NT, 0, st>>>(cost, S, e, dx, dy);
+        else     k_aggregate<R, G, false, false, 1><<<grid, AGG_NT, 0, st>>>(cost, S, e, dx, dy);
+    } else if (tm == 2) {
+        if (pad) k_aggregate<R, G, true, false, 2><<<grid, AGG_NT, 0, st>>>(cost, S, e, dx, dy);
+        else     k_aggregate<R, G, false, false, 2><<<grid, AGG_NT, 0, st>>>(cost, S, e, dx, dy);
+    } else if (pad) {
+        if (first) k_aggregate<R, G, true, true, 0><<<grid, AGG_NT, 0, st>>>(cost, S, e, dx, dy);
+        else       k_aggregate<R, G, true, false, 0><<<grid, AGG_NT, 0, st>>>(cost, S, e, dx, dy);
     } else {
-        if (first) k_aggregate<R, G, false, true><<<grid, AGG_NT, 0, st>>>(cost, S, e, dx, dy);
-        else       k_aggregate<R, G, false, false><<<grid, AGG_NT, 0, st>>>(cost, S, e, dx, dy);
+        if (first) k_aggregate<R, G, false, true, 0><<<grid, AGG_NT, 0, st>>>(cost, S, e, dx, dy);
+        else       k_aggregate<R, G, false, false, 0><<<grid, AGG_NT, 0, st>>>(cost, S, e, dx, dy);
     }
     B2S_LAUNCH_CHECK();
     return B2S_OK;
@@ -212,7 +293,8 @@ int b2s_launch_aggregate(const uint16_t* cost, uint16_t* S, const SgbmEff& e, in
                          cudaStream_t st)
 {
 #define AGG_CASE(RR, GG) if (e.R == RR && e.G == GG) return launch_agg_rg<RR, GG>(cost, S, e, dir, first, st);
-    AGG_CASE(12, 32) AGG_CASE(16, 32)          // D > 512 only; smaller D runs sgbm_wave
+    AGG_CASE(12, 32) AGG_CASE(16, 32)          // D > 512; smaller D runs sgbm_wave, except
+    AGG_CASE(2, 32) AGG_CASE(4, 32) AGG_CASE(8, 32)   // MODE_SGBM_3WAY with numDisparities % 8 != 0 (api.cu sgbm_effective)
 #undef AGG_CASE
     b2s_set_error("no aggregation kernel for R=%d G=%d (numDisparities=%d)", e.R, e.G, e.D);
     return B2S_E_UNSUPPORTED;

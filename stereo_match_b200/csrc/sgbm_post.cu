@@ -27,7 +27,7 @@ __device__ __forceinline__ void load_regs_s(const uint16_t* p, uint32_t (&r)[R])
 // ---------------------------------------------------------------------------
 // WTA: one G-lane group per computed pixel.  Writes the pre-LR-check disparity and
 // scatters (cost, x) into the per-row disp2 key array with atomicMin:
-//   key = minS << 16 | (0xffff - x)   ->  lowest cost wins, ties go to the largest x,
+//   key = (minS + 0x8000) << 16 | (0xffff - x)   ->  lowest (signed) cost wins, ties go to the largest x,
 // which is cv2's "strict > while x runs downward" rule, independent of thread order.
 // ---------------------------------------------------------------------------
 #define WTA_NT 256
@@ -47,38 +47,52 @@ k_wta(const uint16_t* __restrict__ S, SgbmEff e, int16_t* __restrict__ disp, uin
     load_regs_s<R>(S + (size_t)pid * e.Dp + (size_t)lane * 2 * R, v);
 
     const int dbase = lane * 2 * R;
-    uint32_t key = 0xffffffffu;
+    // S cells are SIGNED int16: they are >= 0 everywhere except in MODE_SGBM_3WAY's scalar-tail case (sgbm_agg.cu TM = 1),
+    // where one cell of the down path can go negative, as it does in cv2.  Keys order signed values through the 0x8000 bias.
+    // MODE_SGBM_3WAY: disparities below simdD are searched on cv2's 8 SIMD lanes (b2s_tie8_*), the rest (numDisparities % 8
+    // != 0 only) by a scalar tail that continues with a strict compare; every other mode: one strict search from d = 0
+    const int simdD = e.way3 ? e.simdD : e.D;
+    uint32_t key = 0xffffffffu, keyt = 0xffffffffu;
 #pragma unroll
     for (int i = 0; i < R; i++) {
         int d0 = dbase + 2 * i;
-        uint32_t k0 = ((v[i] & 0xffffu) << 16) | (uint32_t)d0;
-        uint32_t k1 = (v[i] & 0xffff0000u) | (uint32_t)(d0 + 1);
-        if (d0 < e.D) key = min(key, k0);
-        if (d0 + 1 < e.D) key = min(key, k1);
+        uint32_t k0 = (((v[i] & 0xffffu) ^ 0x8000u) << 16) | (uint32_t)d0;
+        uint32_t k1 = ((v[i] & 0xffff0000u) ^ 0x80000000u) | (uint32_t)(d0 + 1);
+        if (d0 < simdD) key = min(key, k0); else if (d0 < e.D) keyt = min(keyt, k0);
+        if (d0 + 1 < simdD) key = min(key, k1); else if (d0 + 1 < e.D) keyt = min(keyt, k1);
     }
 #pragma unroll
-    for (int o = G / 2; o > 0; o >>= 1) key = min(key, __shfl_xor_sync(0xffffffffu, key, o));
+    for (int o = G / 2; o > 0; o >>= 1) {
+        key = min(key, __shfl_xor_sync(0xffffffffu, key, o));
+        keyt = min(keyt, __shfl_xor_sync(0xffffffffu, keyt, o));
+    }
+    if (key == 0xffffffffu) key = 0xffff0000u;         // no SIMD part (numDisparities < 8): cv2 starts from (SHRT_MAX, 0)
     int best = (int)(key & 0xffffu);
-    const int minS = (int)(key >> 16);
+    int minS = (int)(key >> 16) - 0x8000;
     if (e.way3) {                              // MODE_SGBM_3WAY: a tied minimum goes to cv2's 8-lane winner (common.cuh)
         bool tie = false;
 #pragma unroll
         for (int i = 0; i < R; i++) {
             const int d0 = dbase + 2 * i;
-            tie = tie || ((int)(v[i] & 0xffffu) == minS && d0 != best && d0 < e.D) || ((int)(v[i] >> 16) == minS && d0 + 1 != best && d0 + 1 < e.D);
+            tie = tie || ((int)(int16_t)(v[i] & 0xffffu) == minS && d0 != best && d0 < simdD) ||
+                  ((int)(int16_t)(v[i] >> 16) == minS && d0 + 1 != best && d0 + 1 < simdD);
         }
         if (__any_sync(0xffffffffu, tie)) {
             unsigned long long w8 = 0ull;
 #pragma unroll
             for (int i = 0; i < R; i++) {
                 const int d0 = dbase + 2 * i;
-                if ((int)(v[i] & 0xffffu) == minS && d0 < e.D) w8 = b2s_tie8_merge(w8, b2s_tie8_one(d0));
-                if ((int)(v[i] >> 16) == minS && d0 + 1 < e.D) w8 = b2s_tie8_merge(w8, b2s_tie8_one(d0 + 1));
+                if ((int)(int16_t)(v[i] & 0xffffu) == minS && d0 < simdD) w8 = b2s_tie8_merge(w8, b2s_tie8_one(d0));
+                if ((int)(int16_t)(v[i] >> 16) == minS && d0 + 1 < simdD) w8 = b2s_tie8_merge(w8, b2s_tie8_one(d0 + 1));
             }
 #pragma unroll
             for (int o = G / 2; o > 0; o >>= 1) w8 = b2s_tie8_merge(w8, __shfl_xor_sync(0xffffffffu, w8, o));
-            best = b2s_tie8_best(w8);
+            if (w8) best = b2s_tie8_best(w8);
         }
+    }
+    if (keyt != 0xffffffffu && (int)(keyt >> 16) - 0x8000 < minS) {       // the tail wins only strictly
+        minS = (int)(keyt >> 16) - 0x8000;
+        best = (int)(keyt & 0xffffu);
     }
 
     // uniqueness + neighbours of the winner
@@ -87,37 +101,38 @@ k_wta(const uint16_t* __restrict__ S, SgbmEff e, int16_t* __restrict__ disp, uin
     const int thr = minS * 100;
     const int thr16 = (e.uqle && mul > 0) ? (int)(int16_t)(uint16_t)((thr / mul + 1) & 0xffff) : 0;
     uint32_t bad = (minS >= 32767 && !e.way3) ? 1u : 0u;       // every S saturated: cv2 finds no winner (bestDisp = -1 -> INVALID)
-    uint32_t sm1 = 0, sp1 = 0;
+    int sm1 = 0, sp1 = 0;
 #pragma unroll
     for (int i = 0; i < R; i++) {
 #pragma unroll
         for (int h = 0; h < 2; h++) {
             int d = dbase + 2 * i + h;
-            int val = h ? (int)(v[i] >> 16) : (int)(v[i] & 0xffffu);
+            int val = h ? (int)(int16_t)(v[i] >> 16) : (int)(int16_t)(v[i] & 0xffffu);
             if (d < e.D) {
                 int ad = d - best;
-                if ((ad > 1 || ad < -1) && (e.uqle ? val < thr16 : val * mul < thr)) bad = 1;
-                if (ad == -1) sm1 = (uint32_t)val;
-                if (ad == 1) sp1 = (uint32_t)val;
+                // (3WAY's scalar tail d >= simdD uses the exact 32-bit rule of the other modes)
+                if ((ad > 1 || ad < -1) && ((e.uqle && d < simdD) ? val < thr16 : (val * mul < thr && (!e.way3 || e.uniq > 0)))) bad = 1;
+                if (ad == -1) sm1 = val;
+                if (ad == 1) sp1 = val;
             }
         }
     }
 #pragma unroll
     for (int o = G / 2; o > 0; o >>= 1) {
         bad |= __shfl_xor_sync(0xffffffffu, bad, o);
-        sm1 |= __shfl_xor_sync(0xffffffffu, sm1, o);
-        sp1 |= __shfl_xor_sync(0xffffffffu, sp1, o);
+        sm1 += __shfl_xor_sync(0xffffffffu, sm1, o);       // exactly one lane holds each neighbour, the others 0
+        sp1 += __shfl_xor_sync(0xffffffffu, sp1, o);
     }
     if (!active || lane != 0) return;
     int16_t* drow = disp + (size_t)by * e.W;
     if (bad) { drow[x + e.minX1] = (int16_t)e.invalid; return; }
     int x2 = x + e.minX1 - best - e.minD;
     // cv2: disp2cost starts at SHRT_MAX and is only replaced by a strictly smaller cost
-    if (minS < 32767) atomicMin(disp2key + (size_t)by * e.W + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
+    if (minS < 32767) atomicMin(disp2key + (size_t)by * e.W + x2, ((uint32_t)(minS + 0x8000) << 16) | (uint32_t)(0xffff - x));
     int dq = best * 16;
     if (best > 0 && best < e.D - 1) {
-        int denom2 = max((int)sm1 + (int)sp1 - 2 * minS, 1);
-        dq += (((int)sm1 - (int)sp1) * 16 + denom2) / (denom2 * 2);
+        int denom2 = max(sm1 + sp1 - 2 * minS, 1);
+        dq += ((sm1 - sp1) * 16 + denom2) / (denom2 * 2);
     }
     drow[x + e.minX1] = (int16_t)(dq + e.minD * 16);
 }
@@ -251,7 +266,8 @@ int b2s_launch_wta(const uint16_t* S, const SgbmEff& e, int16_t* disp_raw, uint3
     B2S_CUDA_CHECK(cudaMemsetAsync(disp2key, 0xff, (size_t)e.batch * e.H * e.W * sizeof(uint32_t), st));
     int rc = B2S_E_UNSUPPORTED;
 #define WTA_CASE(RR, GG) if (e.R == RR && e.G == GG) rc = launch_wta_rg<RR, GG>(S, e, disp_raw, disp2key, st);
-    WTA_CASE(12, 32) WTA_CASE(16, 32)          // D > 512 only; smaller D runs the fused wavefront WTA
+    WTA_CASE(12, 32) WTA_CASE(16, 32)          // D > 512; smaller D runs the fused wavefront WTA, except
+    WTA_CASE(2, 32) WTA_CASE(4, 32) WTA_CASE(8, 32)   // MODE_SGBM_3WAY with numDisparities % 8 != 0
 #undef WTA_CASE
     if (rc != B2S_OK) {
         if (rc == B2S_E_UNSUPPORTED) b2s_set_error("no WTA kernel for R=%d G=%d", e.R, e.G);

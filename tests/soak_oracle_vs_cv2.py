@@ -55,7 +55,7 @@ def one_ops(k):
 
 
 def one(k):
-    """k >= 0: StereoSGBM case k of tools/soak_cases.gen_wide ; k < 0: StereoBM case -k-1 of gen_bm"""
+    """k >= 0: StereoSGBM case k // 3 of tools/soak_cases.gen_wide / gen_big / gen_params (k % 3) ; k < 0: StereoBM case -k-1"""
     import cv2
     from oracle import port, cv2ref
     from soak_cases import gen_wide, gen_bm
@@ -67,15 +67,23 @@ def one(k):
         got = port.bm_compute(l, r, D, bs, **setters)
         n = int((got != want).sum())
         return (k, n, (D, bs, setters), l.shape) if n else None
-    c = gen_wide(k)
+    from soak_cases import gen_big, gen_params
+    c = (gen_wide, gen_big, gen_params)[k % 3](k // 3)
     if c is None:
         return None
     kw, l, r = c
     try:
         want = cv2.StereoSGBM_create(**kw).compute(l, r)
     except cv2.error:
-        return None
-    got = port.sgbm_compute(l, r, **kw)
+        try:
+            port.sgbm_compute(l, r, **kw)
+        except ValueError:
+            return None
+        return (k, -1, kw, l.shape)            # cv2 raised, the restatement did not
+    try:
+        got = port.sgbm_compute(l, r, **kw)
+    except ValueError as ex:
+        return (k, -2, (kw, str(ex)), l.shape)  # the restatement raised, cv2 did not
     n = int((got != want).sum())
     return (k, n, kw, l.shape) if n else None
 

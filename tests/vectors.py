@@ -112,6 +112,23 @@ SGBM_SOAK_VECTORS = [
     ("ramp", 3, 100, 40, 0, 48, 9, 10, 100, 50, 63, 10, 1, 30, 2),
     ("ramp", 3, 180, 40, 0, 128, 9, 10, 100, 50, 63, 0, 2, 0, 0),            # 3WAY on the same pair: it does find winners
     ("ramp", 4, 620, 24, 0, 528, 9, 10, 100, 50, 63, 0, 1, 0, 0),            # sat, per-direction kernels + k_wta
+    # MODE_SGBM_3WAY with numDisparities % 8 != 0 (cv2's scalar tail: the in-place paths take a wrong d - 1 neighbour at
+    # d = 8 * (D / 8), the tail continues the winner search strictly and uses the 32-bit uniqueness rule); "top" scenes
+    # put the true disparities into the last cells of the range, where the tail lives
+    ("top", 1, 52, 19, 0, 12, 3, 100, 800, 100000, 31, 0, 2, 0, 0),
+    ("top", 2, 60, 19, 0, 20, 3, 100, 800, 1, 31, 15, 2, 0, 0),
+    ("top", 3, 70, 19, 0, 30, 3, 8, 32, 1, 31, 15, 2, 0, 0),
+    ("top", 4, 45, 19, 0, 5, 3, 8, 32, 1, 31, 10, 2, 0, 0),                  # fewer than 8 disparities: no SIMD part at all
+    ("top", 5, 140, 23, 0, 100, 5, 104, 5205, 100000, 63, 0, 2, 0, 0),
+    ("top", 6, 184, 15, -50, 100, 7, 20, 2948, -1, 15, 10, 2, 0, 0),
+    ("top", 7, 340, 11, 0, 300, 3, 72, 288, 1, 63, 10, 2, 30, 2),
+    ("top", 8, 590, 15, 0, 535, 3, 8, 32, 1, 63, 0, 2, 0, 0),               # D > 512 and a tail
+    ("top", 9, 140, 23, 0, 100, 5, 104, 5205, 1, 63, 5, 1, 0, 0),            # the other modes have no such tail
+    # MODE_SGBM_3WAY: blockSize <= 0 means a 3-pixel window (5 elsewhere), and the stripe overlap takes blockSize as given
+    ("synth", 131, 212, 36, 0, 128, -3, 0, 400, -1, -5, -50, 2, 0, 0),
+    ("synth", 782, 90, 37, 0, 24, 0, 0, 2, 7, 64, 0, 2, 0, -2),
+    ("synth", 440, 108, 54, 0, 40, -3, 400, 2000, 0, 30, 33, 2, 0, 1),
+    ("synth", 441, 108, 54, 0, 40, -3, 400, 2000, 0, 30, 33, 1, 0, 1),       # MODE_HH: the 5-pixel fallback
 ]
 
 
@@ -122,6 +139,8 @@ def soak_pair(v):
     kind, seed, w, h, minD, D = v[:6]
     if kind == "synth":
         return synth_pair(w, h, max(D + minD, 8), seed=seed)
+    if kind == "top":
+        return synth_pair(w, h, max(int(2.5 * (D + minD)), 8), seed=seed)    # the middle rows sit at the top of the range
     rng = np.random.default_rng(9000 + seed)
     x, y = np.arange(w)[None, :], np.arange(h)[:, None]
     l = (192 + ((9 * x + 2 * y) % 64) + rng.integers(0, 3, (h, w)) - 1).clip(0, 255).astype(np.uint8)

@@ -10,6 +10,12 @@ from stereo_match_b200.synth import synth_pair   # noqa: E402
 from vectors import color_pair                   # noqa: E402
 
 
+def _scene_range(rng, maxD):
+    """Disparity scale of the synthetic scene relative to the matcher's range: inside it, reaching its top and beyond
+    (the winners then sit in the last disparities, where cv2's SIMD tails live), or only its bottom."""
+    return max(int(max(maxD, 8) * float(rng.choice([1.0, 1.0, 1.6, 2.2, 0.4]))), 8)
+
+
 def gen(k, seed0=0):
     """-> (kw, left, right, cn, batch) or None when the drawn block size leaves no overflow-free P2."""
     rng = np.random.default_rng(31337 + seed0 + k)
@@ -31,7 +37,7 @@ def gen(k, seed0=0):
     kw = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=P1, P2=P2, disp12MaxDiff=int(rng.choice([-1, 1, 2, 50])),
               preFilterCap=cap, uniquenessRatio=int(rng.choice([0, 5, 15, 60, 99])), speckleWindowSize=int(rng.choice([0, 60])),
               speckleRange=int(rng.choice([1, 2])), mode=mode)
-    maxd = max(D + minD, 8)
+    maxd = _scene_range(rng, D + minD)
     l, r = synth_pair(w, h, maxd, seed=k) if cn == 1 else color_pair(w, h, maxd, k)
     B = int(rng.choice([1, 1, 3]))
     return kw, l, r, cn, B
@@ -59,12 +65,58 @@ def gen_wide(k):
     kw = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=P1, P2=P2, disp12MaxDiff=int(rng.choice([-1, 0, 1, 2, 50, 100000])),
               preFilterCap=cap, uniquenessRatio=int(rng.choice([0, 1, 5, 15, 40, 60, 90, 99])), speckleWindowSize=int(rng.choice([0, 0, 30])),
               speckleRange=int(rng.choice([1, 2])), mode=int(rng.integers(0, 4)))
-    maxd = max(D + minD, 8)
+    maxd = _scene_range(rng, D + minD)
     l, r = synth_pair(w, h, maxd, seed=k) if cn == 1 else color_pair(w, h, maxd, k)
     if rng.random() < 0.2:
         l, r = l.copy(), r.copy()
         l[:, w // 2:] = 255 - l[:, w // 2:] // 8
         r[:, w // 2:] = r[:, w // 2:] // 8
+    return kw, l, r
+
+
+def gen_big(k):
+    """numDisparities 272 .. 1024 (32-lane kernels, the per-direction kernels above 512), blockSize up to 15 (generic cost
+    kernel), any numDisparities that is not a multiple of 16; few rows to keep cv2's time small.  -> (kw, left, right) or None"""
+    rng = np.random.default_rng(888000 + k)
+    D = int(rng.choice([264, 272, 300, 320, 400, 512, 520, 528, 640, 1000, 1024, 100, 136, 200]))
+    bs = int(rng.choice([1, 3, 5, 7, 9, 13, 15]))
+    cn = 3 if rng.random() < 0.2 and bs <= 7 else 1
+    cap = int(rng.choice([15, 31, 63]))
+    cmax = bs * bs * (2 * (max(cap, 15) | 1) + 63) * cn
+    hi = (32767 - 2 * cmax) // 3
+    if hi < 16:
+        return None
+    P2 = int(rng.integers(8, min(hi, 6000) + 1))
+    P1 = int(rng.integers(1, P2))
+    minD = int(rng.choice([0, 0, 11, -9, -D // 2, -D, -D - 20]))
+    w1 = int(rng.choice([rng.integers(bs, 24), rng.integers(24, 100)]))
+    w = w1 + max(D + minD, 0) - min(minD, 0)
+    h = int(rng.integers(1, 20))
+    kw = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=P1, P2=P2, disp12MaxDiff=int(rng.choice([-1, 1, 3, 100000])),
+              preFilterCap=cap, uniquenessRatio=int(rng.choice([0, 5, 15, 60, 99])), speckleWindowSize=int(rng.choice([0, 0, 30])),
+              speckleRange=int(rng.choice([1, 2])), mode=int(rng.integers(0, 4)))
+    maxd = _scene_range(rng, D + minD)
+    l, r = synth_pair(w, h, maxd, seed=k) if cn == 1 else color_pair(w, h, maxd, k)
+    return kw, l, r
+
+
+def gen_params(k):
+    """cv2's silent parameter fallbacks and odd values: zero / negative penalties, P2 <= P1, negative ratio, preFilterCap
+    0 .. 127, zero / negative / huge disp12MaxDiff, negative speckle settings, even block sizes.  -> (kw, left, right)"""
+    rng = np.random.default_rng(999000 + k)
+    D = int(rng.choice([5, 8, 12, 16, 20, 24, 30, 40, 52, 64, 90, 128]))
+    bs = int(rng.choice([-3, 0, 1, 2, 3, 4, 5, 6, 7]))
+    cap = int(rng.choice([-5, 0, 1, 14, 15, 16, 30, 63, 64, 100, 127]))
+    P1 = int(rng.choice([-7, 0, 1, 2, 50, 400]))
+    P2 = int(rng.choice([-7, 0, 1, 2, 3, 50, 51, 400, 2000]))
+    minD = int(rng.choice([0, 0, 5, -3, -D]))
+    w1 = int(rng.integers(max(abs(bs), 1) + 1, 90))
+    w = w1 + max(D + minD, 0) - min(minD, 0)
+    h = int(rng.integers(1, 40))
+    kw = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=P1, P2=P2, disp12MaxDiff=int(rng.choice([-100, -1, 0, 1, 7, 2 ** 30])),
+              preFilterCap=cap, uniquenessRatio=int(rng.choice([-50, -1, 0, 10, 33])), speckleWindowSize=int(rng.choice([-5, 0, 1, 25])),
+              speckleRange=int(rng.choice([-2, 0, 1, 3])), mode=int(rng.integers(0, 4)))
+    l, r = synth_pair(w, h, _scene_range(rng, D + minD), seed=k)
     return kw, l, r
 
 
@@ -82,7 +134,7 @@ def gen_bm(k):
         setters["speckleRange"] = int(rng.choice([-1, 0, 1, 4, 40]))
     w = max(D + minD, 0) - min(minD, 0) + bs + int(rng.choice([rng.integers(1, 20), rng.integers(20, 160)]))
     h = int(rng.choice([rng.integers(bs + 1, bs + 8), rng.integers(bs + 8, 120)]))
-    l, r = synth_pair(w, h, max(D + minD, 8), seed=12000 + k)
+    l, r = synth_pair(w, h, _scene_range(rng, D + minD), seed=12000 + k)
     return D, bs, setters, l, r
 
 

@@ -1,7 +1,8 @@
 """Randomised parity soak of the engine against live cv2: many more shapes / parameters than the test suite (numDisparities 128 /
 256, every mode, ratios up to 99, penalties up to the edge of the 16-bit domain, fully negative ranges, colour, batches).
-usage: python tools/soak_parity.py [n_cases] [seed0] [sgbm|wide|bm|ops]      (GPU box; prints failures, exits 1 on any)
-sgbm: the numDisparities 128 / 256 kernels (soak_cases.gen); wide: every regime (gen_wide); bm: StereoBM (gen_bm); ops: remap, cvtColor,
+usage: python tools/soak_parity.py [n_cases] [seed0] [sgbm|wide|big|params|bm|ops]      (GPU box; prints failures, exits 1 on any)
+sgbm: the numDisparities 128 / 256 kernels (soak_cases.gen); wide: every regime (gen_wide); big: numDisparities up to 1024,
+blocks up to 15 (gen_big); params: cv2's silent fallbacks and odd values (gen_params); bm: StereoBM (gen_bm); ops: remap, cvtColor,
 medianBlur, filterSpeckles, reprojectImageTo3D.
 
 Round 2: 600 cases found 25 mismatches, all three of them cv2 rules the restatement did not have (tests/vectors.py
@@ -14,7 +15,7 @@ import cv2
 import numpy as np
 import torch
 
-from soak_cases import gen, gen_wide, gen_bm, ops_failures
+from soak_cases import gen, gen_wide, gen_big, gen_params, gen_bm, ops_failures
 
 import stereo_match_b200 as sm
 
@@ -47,7 +48,7 @@ for k in range(seed0, seed0 + n):
             bad += 1
             print("FAIL bm case %d: %d pixels differ, D %d bs %d %r shape %r" % (k, int((got != want).sum()), D, bs, setters, l.shape))
         continue
-    c = gen(k) if which == "sgbm" else gen_wide(k)
+    c = {"sgbm": gen, "wide": gen_wide, "big": gen_big, "params": gen_params}[which](k)
     if c is None:
         continue
     kw, l, r = c[:3]
@@ -55,8 +56,20 @@ for k in range(seed0, seed0 + n):
     try:
         want = cv2.StereoSGBM_create(**kw).compute(l, r)
     except cv2.error:
+        try:
+            sm.StereoSGBM_create(**kw).compute(l, r)
+        except sm.error:
+            continue
+        bad += 1
+        print("FAIL case %d: cv2 raises, the engine does not, %r shape %r" % (k, kw, l.shape))
         continue
-    m = sm.StereoSGBM_create(**kw)
+    try:
+        m = sm.StereoSGBM_create(**kw)
+        m.compute(l, r)
+    except sm.error as ex:
+        bad += 1
+        print("FAIL case %d: the engine raises (%s), cv2 does not, %r shape %r" % (k, str(ex)[:80], kw, l.shape))
+        continue
     if B == 1:
         got = m.compute(l, r)
     else:
