@@ -43,16 +43,16 @@ k_bm_prefilter(const uint8_t* __restrict__ img, int H, int W, int ftzero, uint8_
 // One CTA: output columns [x0, x0+TW) of output rows [yb, yb+TR), all D disparities.
 // smem: col[TW+2r][D] vertical-window column SADs (u32), sad[TW][D], tcol[TW+2r].
 #define BM_NT 512
-#define BM_TW 32
+#define BM_TW 32        // widest tile; large blockSize * numDisparities use narrower ones (launch_bm_generic)
 __global__ void __launch_bounds__(BM_NT)
-k_bm(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, BmEff e, int TR, int16_t* __restrict__ disp)
+k_bm(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, BmEff e, int TR, int TW, int16_t* __restrict__ disp)
 {
     extern __shared__ uint32_t sm[];
-    const int D = e.D, r = e.r, CW = BM_TW + 2 * r;
+    const int D = e.D, r = e.r, CW = TW + 2 * r;
     uint32_t* col = sm;                       // [CW][D]
-    uint32_t* sad = col + (size_t)CW * D;     // [BM_TW][D]
-    uint32_t* tcol = sad + (size_t)BM_TW * D; // [CW]
-    const int x0 = e.xa + blockIdx.x * BM_TW;
+    uint32_t* sad = col + (size_t)CW * D;     // [TW][D]
+    uint32_t* tcol = sad + (size_t)TW * D;    // [CW]
+    const int x0 = e.xa + blockIdx.x * TW;
     const int y0 = r + blockIdx.y * TR;
     const int y1 = min(y0 + TR, e.H - r);
     const size_t base = (size_t)blockIdx.z * e.H * e.W;
@@ -91,7 +91,7 @@ k_bm(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, BmEff e, in
         }
         __syncthreads();
         if (yout >= y0) {
-            for (int it = threadIdx.x; it < BM_TW * D; it += BM_NT) {
+            for (int it = threadIdx.x; it < TW * D; it += BM_NT) {
                 int xl = it / D, d = it - xl * D;
                 uint32_t s = 0;
                 for (int k = 0; k <= 2 * r; k++) s += col[(xl + k) * D + d];
@@ -99,7 +99,7 @@ k_bm(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, BmEff e, in
             }
             __syncthreads();
             // one warp per output pixel
-            for (int xl = warp; xl < BM_TW; xl += BM_NT / 32) {
+            for (int xl = warp; xl < TW; xl += BM_NT / 32) {
                 const int x = x0 + xl;
                 if (x >= xmax) break;
                 const uint32_t* sp = sad + (size_t)xl * D;
@@ -318,17 +318,24 @@ k_fill_i16(int16_t* p, size_t n, int16_t v)
 
 static int launch_bm_generic(const uint8_t* PL, const uint8_t* PR, const BmEff& e, int16_t* disp, cudaStream_t st)
 {
-    const int CW = BM_TW + 2 * e.r;
-    size_t smem = ((size_t)CW * e.D + (size_t)BM_TW * e.D + CW) * sizeof(uint32_t);
-    if (smem > 220 * 1024) {
-        b2s_set_error("StereoBM: numDisparities*blockSize too large (needs %zu B shared memory)", smem);
+    // tile width: the widest whose column sums fit in shared memory ((TW + 2r) * D + TW * D + TW + 2r words)
+    int TW = BM_TW;
+    size_t smem = 0;
+    for (; TW >= 4; TW /= 2) {
+        const int CW = TW + 2 * e.r;
+        smem = ((size_t)CW * e.D + (size_t)TW * e.D + CW) * sizeof(uint32_t);
+        if (smem <= 220 * 1024) break;
+    }
+    if (TW < 4) {
+        b2s_set_error("StereoBM: numDisparities * blockSize too large (%d * %d needs %zu B of shared memory at a 4-column tile)",
+                      e.D, 2 * e.r + 1, smem);
         return B2S_E_UNSUPPORTED;
     }
     // the attribute belongs to the current device's context: set it before every launch (cheap), not once per process
     if (smem > 48 * 1024) B2S_CUDA_CHECK(cudaFuncSetAttribute(k_bm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int TR = 32;
-    dim3 grid(b2s_cdiv(e.xb - e.xa, BM_TW), b2s_cdiv(e.H - 2 * e.r, TR), e.batch);
-    k_bm<<<grid, BM_NT, smem, st>>>(PL, PR, e, TR, disp);
+    dim3 grid(b2s_cdiv(e.xb - e.xa, TW), b2s_cdiv(e.H - 2 * e.r, TR), e.batch);
+    k_bm<<<grid, BM_NT, smem, st>>>(PL, PR, e, TR, TW, disp);
     B2S_LAUNCH_CHECK();
     return B2S_OK;
 }

@@ -182,6 +182,8 @@ BM_VECTORS = [
     (150, 60, 48, 15, dict(minDisparity=-47)),
     (150, 60, 16, 7, dict(minDisparity=-40)),                           # range entirely negative (rofs > 0)
     (150, 60, 32, 23, dict(minDisparity=-31)),                          # generic kernel
+    (640, 64, 512, 51, {}),                                             # generic kernel, 16-column tiles (shared memory)
+    (400, 70, 320, 41, dict(uniquenessRatio=5, textureThreshold=0)),
 ]
 
 # full-size configurations of BASELINE.json

@@ -110,7 +110,9 @@ def gen_params(k):
     P1 = int(rng.choice([-7, 0, 1, 2, 50, 400]))
     P2 = int(rng.choice([-7, 0, 1, 2, 3, 50, 51, 400, 2000]))
     minD = int(rng.choice([0, 0, 5, -3, -D]))
-    w1 = int(rng.integers(max(abs(bs), 1) + 1, 90))
+    # cv2 only tests W - maxD > blockSize / 2; with a negative minDisparity a computed width W + minD - maxD <= blockSize / 2
+    # passes that test and gives NON-DETERMINISTIC output (uninitialised memory; probed): kept out of the domain
+    w1 = int(rng.integers((bs if bs > 0 else 5) // 2 + 1 + max(abs(bs), 1), 90))
     w = w1 + max(D + minD, 0) - min(minD, 0)
     h = int(rng.integers(1, 40))
     kw = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=P1, P2=P2, disp12MaxDiff=int(rng.choice([-100, -1, 0, 1, 7, 2 ** 30])),
@@ -121,11 +123,11 @@ def gen_params(k):
 
 
 def gen_bm(k):
-    """StereoBM: any window 5..31, numDisparities 16..256, minDisparity <= 0 (what createRightMatcher sets; cv2 itself leaks
+    """StereoBM: any window 5..51, numDisparities 16..512, minDisparity <= 0 (what createRightMatcher sets; cv2 itself leaks
     stray pixels for positive ones), every filter.  -> (numDisparities, blockSize, setters, left, right)."""
     rng = np.random.default_rng(555000 + k)
-    D = 16 * int(rng.choice([1, 2, 3, 4, 6, 8, 10, 16]))
-    bs = int(rng.choice([5, 7, 9, 11, 15, 17, 21, 23, 31]))
+    D = 16 * int(rng.choice([1, 2, 3, 4, 6, 8, 10, 16, 20, 32]))
+    bs = int(rng.choice([5, 7, 9, 11, 15, 17, 21, 23, 31, 41, 51]))
     minD = int(rng.choice([0, 0, 0, -1, -7, -D + 1, -D, -D - 9]))
     setters = dict(preFilterCap=int(rng.integers(1, 64)), textureThreshold=int(rng.choice([0, 1, 10, 100, 1000, 5000])),
                    uniquenessRatio=int(rng.choice([0, 1, 5, 15, 50, 90])), minDisparity=minD)
@@ -194,3 +196,40 @@ def ops_failures(k, ops, cv2):
                 if not np.array_equal(np.where(nan, 0, got.view(np.uint32)), np.where(nan, 0, want.view(np.uint32))):
                     fails.append("reproject %s Q%s hm%d" % (dd.dtype, Qm.dtype, hm))
     return fails
+
+
+def gen_chain(k):
+    """The reference's per-pair chain (disparity_calculation.py:207-208, 286-289, 302): raw pair (gray or BGR) -> remap through
+    two smooth rectification-like maps -> gray -> StereoSGBM -> reprojectImageTo3D.  -> dict or None"""
+    rng = np.random.default_rng(616000 + k)
+    c = gen_wide(3 * k + 1)
+    if c is None:
+        return None
+    kw, l, r = c
+    if l.ndim == 3:                                   # the chain converts to gray before matching
+        return None
+    H, W = l.shape
+    cn = 3 if rng.random() < 0.5 else 1
+    sH, sW = H + int(rng.integers(0, 9)), W + int(rng.integers(0, 9))
+
+    def raw(img):
+        out = rng.integers(0, 256, (sH, sW), dtype=np.uint8)
+        out[:H, :W] = img
+        if cn == 1:
+            return out
+        return np.stack([out, np.roll(out, 1, 1), 255 - out], -1)      # three different channels
+
+    def maps():
+        yy, xx = np.mgrid[0:H, 0:W].astype(np.float32)
+        a, b = rng.normal(0, 2e-3, 2)
+        mx = xx + float(rng.normal(0, 1.5)) + a * (yy - H / 2) + 1e-4 * (xx - W / 2) ** 2 / max(W, 1)
+        my = yy + float(rng.normal(0, 1.5)) + b * (xx - W / 2)
+        return mx.astype(np.float32), my.astype(np.float32)
+
+    f = float(rng.uniform(300, 1500))
+    Q = np.array([[1, 0, 0, -rng.uniform(0, W)], [0, 1, 0, -rng.uniform(0, H)], [0, 0, 0, f], [0, 0, 1 / rng.uniform(0.05, 1.0), 0]])
+    if rng.random() < 0.3:
+        Q[1, 1] = -1.0
+        Q[3, 3] = float(rng.normal(0, 0.5))
+    return dict(kw=kw, left=raw(l), right=raw(r), maps_left=maps(), maps_right=maps(), Q=Q,
+                scale=float(rng.choice([1.0 / 16.0, 1.0])), hm=bool(rng.random() < 0.5), cn=cn)
