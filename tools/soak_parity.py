@@ -1,9 +1,10 @@
 """Randomised parity soak of the engine against live cv2: many more shapes / parameters than the test suite (numDisparities 128 /
 256, every mode, ratios up to 99, penalties up to the edge of the 16-bit domain, fully negative ranges, colour, batches).
-usage: python tools/soak_parity.py [n_cases] [seed0] [sgbm|wide|big|params|bm|ops|chain]      (GPU box; prints failures, exits 1 on any)
+usage: python tools/soak_parity.py [n_cases] [seed0] [sgbm|wide|big|params|bm|ops|chain|misc]      (GPU box; prints failures, exits 1 on any)
 sgbm: the numDisparities 128 / 256 kernels (soak_cases.gen); wide: every regime (gen_wide); big: numDisparities up to 1024,
 blocks up to 15 (gen_big); params: cv2's silent fallbacks and odd values (gen_params); bm: StereoBM (gen_bm); ops: remap, cvtColor,
-medianBlur, filterSpeckles, reprojectImageTo3D; chain: the fused per-pair chain (sm.pipeline) against the separate cv2 calls.
+medianBlur, filterSpeckles, reprojectImageTo3D; chain: the fused per-pair chain (sm.pipeline) against the separate cv2 calls;
+misc: compute_disparity, project_points_3D, point_cloud, map2Dto3D.
 
 Round 2: 600 cases found 25 mismatches, all three of them cv2 rules the restatement did not have (tests/vectors.py
 SGBM_SOAK_VECTORS); 0 of 600 after."""
@@ -18,13 +19,91 @@ import torch
 from soak_cases import gen, gen_wide, gen_big, gen_params, gen_bm, gen_chain, ops_failures
 
 import stereo_match_b200 as sm
+from stereo_match_b200.synth import synth_pair
 
 n, seed0 = (int(sys.argv[1]) if len(sys.argv) > 1 else 300), (int(sys.argv[2]) if len(sys.argv) > 2 else 0)
 which = sys.argv[3] if len(sys.argv) > 3 else "sgbm"
 bad = ran = 0
 
 
+def soak_misc(k):
+    """The reference-level functions: compute_disparity (left / right maps), project_points_3D, the ordered point cloud,
+    map2Dto3D -- against cv2 and numpy directly.  -> names of what differs"""
+    rng = np.random.default_rng(838300 + k)
+    fails = []
+    # compute_disparity (stereo_vision.py:132-184): the maps of both matchers for random settings
+    D = 16 * int(rng.integers(1, 9))
+    ws = int(rng.choice([1, 3, 5]))
+    method = "BM" if rng.random() < 0.3 else "SGBM"
+    bs = int(rng.choice([5, 9, 15, 21])) if method == "BM" else int(rng.choice([1, 3, 5, 7]))
+    st = dict(window_size=ws, min_disparity=0 if method == "BM" else int(rng.choice([0, 0, 4])), num_disparities=D, block_size=bs,
+              disp12_max_diff=int(rng.choice([-1, 1, 5])), uniqueness_ratio=int(rng.choice([0, 10, 15])),
+              speckle_window_size=int(rng.choice([0, 50])), speckle_range=int(rng.choice([1, 2])), pre_filter_cap=int(rng.choice([15, 63])),
+              lmbda=80000.0, sigma=1.2, sgbm_mode=str(rng.choice(["SGBM", "HH", "HH4"])))
+    w, h = D + st["min_disparity"] + int(rng.integers(bs + 2, 120)), int(rng.integers(bs + 2, 70))
+    l, r = synth_pair(w, h, D, seed=k)
+    displ, filtered, dispr = sm.compute_disparity(l, r, st, method, return_right=True)
+    if method == "SGBM":
+        kwl = dict(minDisparity=st["min_disparity"], numDisparities=D, blockSize=bs, P1=24 * ws * ws, P2=96 * ws * ws, preFilterCap=st["pre_filter_cap"],
+                   mode={"SGBM": 0, "HH": 1, "HH4": 3}[st["sgbm_mode"]])
+        # createDisparityWLSFilter(left_matcher) switches the left matcher's own filters off (stereo_vision.py:172)
+        wl = cv2.StereoSGBM_create(disp12MaxDiff=1000000, uniquenessRatio=0, speckleWindowSize=0, speckleRange=st["speckle_range"], **kwl).compute(l, r)
+        kwr = dict(kwl, minDisparity=-(st["min_disparity"] + D) + 1)
+        wr = cv2.StereoSGBM_create(disp12MaxDiff=1000000, uniquenessRatio=0, speckleWindowSize=0, speckleRange=0, **kwr).compute(r, l)
+    else:
+        ml = cv2.StereoBM_create(numDisparities=D, blockSize=bs)
+        ml.setDisp12MaxDiff(1000000); ml.setSpeckleWindowSize(0); ml.setTextureThreshold(0); ml.setUniquenessRatio(0)
+        wl = ml.compute(l, r)
+        mr = cv2.StereoBM_create(numDisparities=D, blockSize=bs)
+        mr.setMinDisparity(-D + 1); mr.setTextureThreshold(0); mr.setUniquenessRatio(0); mr.setDisp12MaxDiff(1000000); mr.setSpeckleWindowSize(0)
+        wr = mr.compute(r, l)
+    if not np.array_equal(displ, wl):
+        fails.append("compute_disparity displ %s" % method)
+    if not np.array_equal(dispr, wr):
+        fails.append("compute_disparity dispr %s" % method)
+    if filtered.dtype != np.int16 or filtered.shape != l.shape:
+        fails.append("compute_disparity filtered shape")
+    # project_points_3D (stereo_vision.py:187-210)
+    Q = np.array([[1, 0, 0, -w / 2], [0, -1, 0, h / 2], [0, 0, 0, -float(rng.uniform(200, 1200))], [0, 0, float(rng.uniform(0.5, 5)), 0]])
+    want = cv2.reprojectImageTo3D(displ.astype(np.float32) / 16.0, Q.astype(np.float32))
+    got = sm.project_points_3D(displ, Q)
+    nan = np.isnan(got) & np.isnan(want)
+    if not np.array_equal(np.where(nan, 0, got.view(np.uint32)), np.where(nan, 0, want.view(np.uint32))):
+        fails.append("project_points_3D")
+    # the ordered point cloud (disparity_calculation.py:309-321)
+    lo, hi = float(rng.choice([-np.inf, 0, 16 * 3])), float(rng.choice([np.inf, 16 * D // 2]))
+    bgr = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    for dd in (displ, displ.astype(np.float32) / 16):
+        lo_, hi_ = (lo, hi) if dd.dtype == np.int16 else (lo / 16, hi / 16)
+        mask = np.logical_and(dd < hi_, dd > lo_)
+        pts = want[mask].copy()
+        pts[np.isnan(pts)] = 0
+        pts[np.isinf(pts)] = 0
+        v, c = sm.point_cloud(dd, want, bgr, lo_, hi_)
+        if not (np.array_equal(v.view(np.uint32), pts.view(np.uint32)) and np.array_equal(c, bgr[..., ::-1][mask])):
+            fails.append("point_cloud %s" % dd.dtype)
+    # map2Dto3D (mapTo3D.py:35-56)
+    dt = rng.choice([np.uint8, np.uint16, np.int16, np.int32, np.float32, np.float64])
+    gray = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    depth = (rng.random((h, w)) * float(rng.choice([1.0, 200.0, 30000.0]))).astype(dt)
+    cx, cy, fx, fy = float(rng.uniform(0, w)), float(rng.uniform(0, h)), float(rng.uniform(100, 900)), float(rng.uniform(100, 900))
+    rows, cols = np.where(gray > -1)
+    z = depth[gray > -1]
+    wantm = np.stack([-np.reshape((cols - cx) * z / fx, gray.shape), np.reshape((rows - cy) * z / fy, gray.shape), np.reshape(z, gray.shape)], axis=2)
+    gotm = sm.map2Dto3D(gray, depth, cx, cy, fx, fy, -1)
+    if not np.array_equal(gotm.view(np.uint64), wantm.astype(np.float64).view(np.uint64)):
+        fails.append("map2Dto3D %s" % np.dtype(dt).name)
+    return fails
+
+
 for k in range(seed0, seed0 + n):
+    if which == "misc":
+        f = soak_misc(k)
+        ran += 1
+        if f:
+            bad += 1
+            print("FAIL misc case %d: %s" % (k, ", ".join(f)))
+        continue
     if which == "ops":
         f = ops_failures(k, sm, cv2)
         ran += 1
