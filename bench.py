@@ -318,6 +318,22 @@ def run_extras(sm, torch, chain, Ld, Rd, Lh, mx, my, Q, peak):
                                                         "frac": 4.0 * 1280 * 720 * nb / (ms / 1e3) / 1e9 / peak}}
     del bm, L, R
     torch.cuda.empty_cache()
+    # the reference's whole compute_disparity (stereo_vision.py:132-184) at the cfg3 settings: left matcher, right-view
+    # matcher and the WLS filter.  No reference arm beside it: cv2.ximgproc exists on neither box (WLS parity unpinned).
+    settings = dict(window_size=5, min_disparity=0, num_disparities=SGBM_KW["numDisparities"], block_size=SGBM_KW["blockSize"],
+                    disp12_max_diff=SGBM_KW["disp12MaxDiff"], uniqueness_ratio=SGBM_KW["uniquenessRatio"],
+                    speckle_window_size=SGBM_KW["speckleWindowSize"], speckle_range=SGBM_KW["speckleRange"],
+                    pre_filter_cap=SGBM_KW["preFilterCap"], lmbda=80000.0, sigma=1.2, sgbm_mode="HH")
+    nb = min(32, int(Ld.shape[0]))
+    ms = timed(lambda: sm.compute_disparity(Ld[:nb], Rd[:nb], settings, "SGBM"), 3)
+    displ, filt = sm.compute_disparity(Ld[:1], Rd[:1], settings, "SGBM")
+    l0, r0 = Ld[0].cpu().numpy(), Rd[0].cpu().numpy()
+    ok = bool(np.array_equal(displ[0].cpu().numpy(), cv2.StereoSGBM_create(**dict(SGBM_KW, disp12MaxDiff=1000000, uniquenessRatio=0,
+                                                                                  speckleWindowSize=0)).compute(l0, r0)))
+    other["compute_disparity_cfg3_left_right_wls"] = {
+        "batch": nb, "ms_per_batch": ms, "pairs_per_s": nb / ms * 1e3, "displ_parity_ok": ok,
+        "what": "sm.compute_disparity: left SGBM + right-view SGBM + WLS filter, device-resident gray pairs",
+        "reference_arm": "none: cv2.ximgproc is not in this image (WLS parity unpinned, DESIGN.md 4.6)"}
     latency = {}
     for nb in (1, 8):
         m = sm.StereoSGBM_create(**SGBM_KW)

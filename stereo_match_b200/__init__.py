@@ -12,7 +12,7 @@ from .ops import map2Dto3D, reprojectImageTo3D, remap, cvtColor, medianBlur, fil
 from .cloud import point_cloud, write_ply
 from .wls import DisparityWLSFilter, createDisparityWLSFilter, createDisparityWLSFilterGeneric
 from . import wls as ximgproc_wls
-from .stereo_vision import (compute_disparity, project_points_3D, parse_config_file,
+from .stereo_vision import (compute_disparity, compute_disparity_cache_clear, project_points_3D, parse_config_file,
                             create_left_matcher, createRightMatcher)
 
 __all__ = [
@@ -22,7 +22,7 @@ __all__ = [
     "map2Dto3D", "reprojectImageTo3D", "remap", "cvtColor", "medianBlur", "filterSpeckles", "remap_gray", "pipeline",
     "point_cloud", "write_ply", "DisparityWLSFilter", "createDisparityWLSFilter", "createDisparityWLSFilterGeneric",
     "ximgproc",
-    "compute_disparity", "project_points_3D", "parse_config_file", "create_left_matcher", "createRightMatcher",
+    "compute_disparity", "compute_disparity_cache_clear", "project_points_3D", "parse_config_file", "create_left_matcher", "createRightMatcher",
 ]
 
 

@@ -126,6 +126,9 @@ k_wls_transpose(const float* __restrict__ a, const float* __restrict__ b, int n,
 }
 
 // m interleaved tridiagonal systems of n unknowns: element j of system s at [j * m + s]  (oracle: solve_line)
+// The recurrence is serial in j; what made it slow was one round trip to memory per step.  The operands of WLS_K steps are
+// loaded together (and the next chunk's while this one is being eliminated), the arithmetic keeps the restatement's order.
+#define WLS_K 8
 __global__ void __launch_bounds__(128)
 k_wls_solve(const float* __restrict__ w, float lam, float* __restrict__ f1, float* __restrict__ f2, float* __restrict__ ct, int n, int m)
 {
@@ -134,27 +137,72 @@ k_wls_solve(const float* __restrict__ w, float lam, float* __restrict__ f1, floa
     const size_t img = (size_t)blockIdx.y * n * m;
     w += img + s; f1 += img + s; f2 += img + s; ct += img + s;
     float cprev = 0.f, p1 = 0.f, p2 = 0.f, wprev = 0.f;
-    for (int j = 0; j < n; j++) {
-        const size_t o = (size_t)j * m;
-        const float wj = w[o];
-        const float a = j > 0 ? lam * wprev : 0.f;
-        const float c = j < n - 1 ? lam * wj : 0.f;
-        const float denom = ((1.0f - a) - c) - a * cprev;
-        cprev = c / denom;
-        ct[o] = cprev;
-        p1 = (f1[o] - a * p1) / denom;
-        p2 = (f2[o] - a * p2) / denom;
-        f1[o] = p1;
-        f2[o] = p2;
-        wprev = wj;
+    float wv[WLS_K], r1[WLS_K], r2[WLS_K], nw[WLS_K], n1[WLS_K], n2[WLS_K];
+#pragma unroll
+    for (int k = 0; k < WLS_K; k++) {
+        const bool in = k < n;
+        const size_t o = (size_t)(in ? k : 0) * m;
+        nw[k] = in ? w[o] : 0.f; n1[k] = in ? f1[o] : 0.f; n2[k] = in ? f2[o] : 0.f;
     }
-    for (int j = n - 2; j >= 0; j--) {
-        const size_t o = (size_t)j * m;
-        const float cj = ct[o];
-        p1 = f1[o] - cj * p1;
-        p2 = f2[o] - cj * p2;
-        f1[o] = p1;
-        f2[o] = p2;
+    for (int j0 = 0; j0 < n; j0 += WLS_K) {
+#pragma unroll
+        for (int k = 0; k < WLS_K; k++) { wv[k] = nw[k]; r1[k] = n1[k]; r2[k] = n2[k]; }
+#pragma unroll
+        for (int k = 0; k < WLS_K; k++) {                         // the next chunk, in flight during the elimination
+            const int j = j0 + WLS_K + k;
+            const bool in = j < n;
+            const size_t o = (size_t)(in ? j : 0) * m;
+            nw[k] = in ? w[o] : 0.f; n1[k] = in ? f1[o] : 0.f; n2[k] = in ? f2[o] : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < WLS_K; k++) {
+            const int j = j0 + k;
+            if (j < n) {
+                const size_t o = (size_t)j * m;
+                const float wj = wv[k];
+                const float a = j > 0 ? lam * wprev : 0.f;
+                const float c = j < n - 1 ? lam * wj : 0.f;
+                const float denom = ((1.0f - a) - c) - a * cprev;
+                cprev = c / denom;
+                ct[o] = cprev;
+                p1 = (r1[k] - a * p1) / denom;
+                p2 = (r2[k] - a * p2) / denom;
+                f1[o] = p1;
+                f2[o] = p2;
+                wprev = wj;
+            }
+        }
+    }
+    // back substitution from j = n - 2 down, chunks of WLS_K loaded ahead the same way
+    int jt = n - 2;
+#pragma unroll
+    for (int k = 0; k < WLS_K; k++) {
+        const int j = jt - k;
+        const bool in = j >= 0;
+        const size_t o = (size_t)(in ? j : 0) * m;
+        nw[k] = in ? ct[o] : 0.f; n1[k] = in ? f1[o] : 0.f; n2[k] = in ? f2[o] : 0.f;
+    }
+    for (; jt >= 0; jt -= WLS_K) {
+#pragma unroll
+        for (int k = 0; k < WLS_K; k++) { wv[k] = nw[k]; r1[k] = n1[k]; r2[k] = n2[k]; }
+#pragma unroll
+        for (int k = 0; k < WLS_K; k++) {
+            const int j = jt - WLS_K - k;
+            const bool in = j >= 0;
+            const size_t o = (size_t)(in ? j : 0) * m;
+            nw[k] = in ? ct[o] : 0.f; n1[k] = in ? f1[o] : 0.f; n2[k] = in ? f2[o] : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < WLS_K; k++) {
+            const int j = jt - k;
+            if (j >= 0) {
+                const size_t o = (size_t)j * m;
+                p1 = r1[k] - wv[k] * p1;
+                p2 = r2[k] - wv[k] * p2;
+                f1[o] = p1;
+                f2[o] = p2;
+            }
+        }
     }
 }
 

@@ -3,8 +3,10 @@ stereo_vision/stereo_vision.py:132-184 (compute_disparity) and :187-210 (project
 plus parse_config_file (disparity_calculation.py:75-128).  Same names, argument meaning and
 error behaviour; the cv2 calls inside are replaced by the CUDA engine.
 """
+import collections
 import configparser
 import os
+import threading
 
 import numpy as np
 import torch
@@ -105,18 +107,57 @@ def compute_disparity(gray_l, gray_r, disparity_settings, method="SGBM", return_
     `displ` and `dispr` are bit-exact with cv2 for these parameters; the ximgproc factories and the filter itself are
     UNPINNED (no cv2.ximgproc in this image, see wls.py).  With return_right=True `dispr` is returned as a third element.
     """
-    from . import wls
-    left_matcher = create_left_matcher(disparity_settings, method)
-    right_matcher = createRightMatcher(left_matcher)
-    wls_filter = wls.createDisparityWLSFilter(left_matcher)
-    wls_filter.setLambda(disparity_settings['lmbda'])
-    wls_filter.setSigmaColor(disparity_settings['sigma'])
+    left_matcher, right_matcher, wls_filter = _chain_objects(gray_l, disparity_settings, method)
     displ = left_matcher.compute(gray_l, gray_r)
     dispr = right_matcher.compute(gray_r, gray_l)
     filtered_img = wls_filter.filter(displ, gray_l, None, dispr)
     if return_right:
         return displ, filtered_img, dispr
     return displ, filtered_img
+
+
+# The reference builds two matchers and a filter on EVERY call.  Built from scratch, each of them allocates (and at the
+# end of the call frees) its device workspace, which costs more than the kernels for a single pair.  The objects carry no
+# state from one pair to the next, so the last few sets are kept per host thread (matcher objects are not re-entrant,
+# like cv2's) and per device, keyed by everything that defines them.  compute_disparity_cache_clear() drops them.
+_CHAIN_KEYS = ('window_size', 'min_disparity', 'num_disparities', 'block_size', 'disp12_max_diff', 'uniqueness_ratio',
+               'speckle_window_size', 'speckle_range', 'pre_filter_cap', 'lmbda', 'sigma', 'sgbm_mode')
+_CHAIN_CACHE_MAX = 2
+_tls = threading.local()
+
+
+def _chain_objects(gray_l, disparity_settings, method):
+    from . import wls
+    dev = gray_l.device.index if isinstance(gray_l, torch.Tensor) and gray_l.is_cuda else torch.cuda.current_device()
+    try:
+        key = (method, dev, tuple((k, disparity_settings.get(k)) for k in _CHAIN_KEYS))
+        hash(key)
+    except TypeError:
+        key = None
+    cache = getattr(_tls, "chain", None)
+    if cache is None:
+        cache = _tls.chain = collections.OrderedDict()
+    if key is not None and key in cache:
+        cache.move_to_end(key)
+        return cache[key]
+    left_matcher = create_left_matcher(disparity_settings, method)
+    right_matcher = createRightMatcher(left_matcher)
+    wls_filter = wls.createDisparityWLSFilter(left_matcher)
+    wls_filter.setLambda(disparity_settings['lmbda'])
+    wls_filter.setSigmaColor(disparity_settings['sigma'])
+    objs = (left_matcher, right_matcher, wls_filter)
+    if key is not None:
+        cache[key] = objs
+        while len(cache) > _CHAIN_CACHE_MAX:
+            cache.popitem(last=False)
+    return objs
+
+
+def compute_disparity_cache_clear():
+    """Drops the matchers / filters (and their device workspaces) that compute_disparity keeps for this host thread."""
+    cache = getattr(_tls, "chain", None)
+    if cache:
+        cache.clear()
 
 
 def project_points_3D(disparity, Q):
