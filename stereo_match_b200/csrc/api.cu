@@ -166,24 +166,59 @@ static SgbmLayout sgbm_layout(const SgbmEff& e, const SgbmEff& v, bool speckle, 
     return l;
 }
 
+// B2S_POISON=<byte value> | random (debug aid; compute-sanitizer's initcheck is not available on the GPU pool): the whole workspace
+// is filled with that byte before every compute, so that a kernel that reads memory nobody wrote gives a wrong result
+// every time instead of once in a thousand runs.  tests/test_gpu_poison.py runs the parity vectors under several patterns.
+static int poison_byte()       // -1: off; 0..255: that byte; 256: pseudo-random bytes (B2S_POISON=random)
+{
+    static int v = -2;
+    if (v == -2) {
+        const char* s = getenv("B2S_POISON");
+        v = !(s && *s) ? -1 : (!strcmp(s, "random") ? 256 : (atoi(s) & 0xff));
+    }
+    return v;
+}
+
+__global__ void k_poison_random(uint32_t* p, size_t n, uint32_t salt)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t x = (uint32_t)i * 2654435761u + salt;          // a cheap integer hash: unrelated values in neighbouring words
+    x ^= x >> 15; x *= 2246822519u; x ^= x >> 13; x *= 3266489917u; x ^= x >> 16;
+    p[i] = x;
+}
+
+int b2s_poison(void* ws, size_t bytes, cudaStream_t st)
+{
+    const int pb = poison_byte();
+    if (pb < 0 || !ws || !bytes) return B2S_OK;
+    if (pb < 256) { B2S_CUDA_CHECK(cudaMemsetAsync(ws, pb, bytes, st)); return B2S_OK; }
+    static uint32_t salt = 1;
+    const size_t n = bytes / 4;
+    k_poison_random<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((uint32_t*)ws, n, salt++ * 0x9e3779b9u);
+    B2S_CUDA_CHECK(cudaGetLastError());
+    return B2S_OK;
+}
+
 static int ensure_ws(b2s_matcher* h, size_t bytes, cudaStream_t st)
 {
     if (!h->flag) B2S_CUDA_CHECK(cudaMalloc(&h->flag, sizeof(int)));
-    if (bytes <= h->ws_bytes) return B2S_OK;
-    if (h->ws) {
-        B2S_CUDA_CHECK(cudaStreamSynchronize(st));
-        if (h->last_stream && h->last_stream != st) B2S_CUDA_CHECK(cudaStreamSynchronize(h->last_stream));
-        cudaFree(h->ws);
-        h->ws = nullptr; h->ws_bytes = 0;
+    if (bytes > h->ws_bytes) {
+        if (h->ws) {
+            B2S_CUDA_CHECK(cudaStreamSynchronize(st));
+            if (h->last_stream && h->last_stream != st) B2S_CUDA_CHECK(cudaStreamSynchronize(h->last_stream));
+            cudaFree(h->ws);
+            h->ws = nullptr; h->ws_bytes = 0;
+        }
+        cudaError_t err = cudaMalloc(&h->ws, bytes);
+        if (err != cudaSuccess) {
+            cudaGetLastError();
+            b2s_set_error("workspace allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(err));
+            return B2S_E_NOMEM;
+        }
+        h->ws_bytes = bytes;
     }
-    cudaError_t err = cudaMalloc(&h->ws, bytes);
-    if (err != cudaSuccess) {
-        cudaGetLastError();
-        b2s_set_error("workspace allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(err));
-        return B2S_E_NOMEM;
-    }
-    h->ws_bytes = bytes;
-    return B2S_OK;
+    return b2s_poison(h->ws, h->ws_bytes, st);
 }
 
 static int check_images(const char* who, const void* l, const void* r, const void* d, int H, int W, int batch)

@@ -92,6 +92,7 @@ __host__ __device__ inline int b2s_cell_pos(int d, int R, int G, int swz)
 
 void b2s_set_error(const char* fmt, ...);
 void b2s_count_launch(int n = 1);
+int b2s_poison(void* ws, size_t bytes, cudaStream_t st);   // debug aid: B2S_POISON (api.cu)
 
 #define B2S_CUDA_CHECK(expr)                                                          \
     do {                                                                              \

@@ -18,6 +18,7 @@
 // coefficients, so they go through the same sweep.
 #include "common.cuh"
 #include <cmath>
+#include <cstdlib>
 #include <new>
 #include <vector>
 
@@ -303,6 +304,7 @@ extern "C" int b2s_wls_filter(b2s_wls_handle h, const int16_t* disp_left, const 
         h->ws_bytes = need;
     }
     h->last_stream = st;
+    { int prc = b2s_poison(h->ws, h->ws_bytes, st); if (prc) return prc; }     // debug aid, see api.cu
     char* ws = (char*)h->ws;
     float* conf = (float*)(ws + 0 * plane); float* dright = (float*)(ws + 1 * plane);
     float* f1 = (float*)(ws + 2 * plane);   float* f2 = (float*)(ws + 3 * plane);
