@@ -430,7 +430,10 @@ ORC_API int orc_sgbm_compute_cn(const uint8_t* left, const uint8_t* right, int H
     size_t n = (size_t)H * W;
     /* cv2 4.13.0 (stereosgbm.cpp:511) raises cv2.error unless
        width - (minDisparity + numDisparities) > SADWindowSize/2 */
-    if (!(W - e.maxD > e.chkSW2)) return -2;
+    /* MODE_HH4 is separate code in cv2 and has no such test: it computes whatever width is left (probed: bit-exact with   */
+    /* this restatement down to width1 = 1, all INVALID below).  MODE_SGBM_3WAY only refuses W - maxD <= 0, but what it   */
+    /* returns for 0 < W - maxD <= blockSize/2 does not follow from the algorithm: kept as an error here.                  */
+    if (p->mode != 3 && !(W - e.maxD > e.chkSW2)) return -2;
     if (e.width1 <= 0) { for (size_t i = 0; i < n; i++) disp[i] = (int16_t)e.INVALID; return 0; }
     int16_t* tmp = (int16_t*)malloc(n * sizeof(int16_t));
     if (p->mode == 2) {

@@ -87,7 +87,10 @@ static int sgbm_effective(const b2s_sgbm_params& p, int H, int W, int batch, Sgb
     e.ndirs = p.mode == B2S_MODE_HH ? 8 : (p.mode == B2S_MODE_HH4 ? 4 : (p.mode == B2S_MODE_SGBM_3WAY ? 3 : 5));
     e.cn = 1; e.Hsrc = H; e.nst = 1; e.sz = e.ov = 0; e.uqle = 0; e.way3 = 0;
     // cv2 4.13.0 stereosgbm.cpp:511 raises cv2.error on this condition
-    if (!(W - maxD > chk_sw2)) {
+    // MODE_HH4 is separate code in cv2 and has no such test: it computes whatever width is left (bit-exact with the
+    // restatement down to one column; all INVALID when nothing is left).  MODE_SGBM_3WAY only refuses W - maxD <= 0, but
+    // its output for 0 < W - maxD <= blockSize/2 does not follow from the algorithm: refused here like in the other modes.
+    if (p.mode != B2S_MODE_HH4 && !(W - maxD > chk_sw2)) {
         b2s_set_error("StereoSGBM: Your input images are too small for your window size and max disparity "
                       "(expected: 'width - (params.minDisparity + params.numDisparities) > "
                       "params.calcSADWindowSize().width/2'), where %d must be greater than %d", W - maxD, chk_sw2);
@@ -465,7 +468,7 @@ extern "C" int b2s_bm_compute(b2s_handle h, const uint8_t* left, const uint8_t* 
     int rc = check_images("StereoBM", left, right, disp, H, W, batch);
     if (rc) return rc;
     if ((rc = bm_validate(h->bp))) return rc;
-    if (h->bp.blockSize > W || h->bp.blockSize > H) {
+    if (h->bp.blockSize >= W || h->bp.blockSize >= H) {          // cv2 4.13.0 refuses SADWindowSize >= min(width, height) (probed)
         b2s_set_error("StereoBM: SADWindowSize must be odd, be within 5..255 and be not larger than image width or height");
         return B2S_E_INVALID;
     }

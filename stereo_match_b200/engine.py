@@ -221,7 +221,8 @@ class StereoBM(_Matcher):
 
     def __init__(self, numDisparities=0, blockSize=21):
         super().__init__()
-        self._p = _lib.BmParams(numDisparities=int(numDisparities) if numDisparities else 64, blockSize=int(blockSize),
+        # cv2.StereoBM_create: any numDisparities <= 0 means 64 (probed: -16, -1, 0 all give getNumDisparities() == 64)
+        self._p = _lib.BmParams(numDisparities=int(numDisparities) if int(numDisparities) > 0 else 64, blockSize=int(blockSize),
                                 preFilterCap=31, textureThreshold=10, uniquenessRatio=15,
                                 speckleWindowSize=0, speckleRange=0, minDisparity=0, disp12MaxDiff=-1)
         _lib.check(_lib.load().b2s_bm_create(C.byref(self._p), C.byref(self._h)))

@@ -157,8 +157,13 @@ def filterSpeckles(img, newVal, maxSpeckleSize, maxDiff, buf=None):
     """cv2.filterSpeckles: in place for torch CUDA tensors; numpy arrays are updated in place too
     and returned (cv2 returns (img, buf))."""
     s, kind = _to_device(img, "img")
+    src8 = s if s.dtype == torch.uint8 else None
+    if src8 is not None:
+        # CV_8UC1 (cv2 accepts it too): the same labelling on an int16 copy; newVal goes through cv2's (uchar) cast
+        s = src8.to(torch.int16)
+        newVal = int(newVal) & 0xff
     if s.dtype != torch.int16:
-        raise error("filterSpeckles: only int16 images are supported", _lib.E_UNSUPPORTED)
+        raise error("filterSpeckles: img.type() == CV_8UC1 || img.type() == CV_16SC1", _lib.E_UNSUPPORTED)
     view = s[None] if s.dim() == 2 else s
     B, H, W = view.shape
     labels = torch.empty(B * H * W, dtype=torch.int32, device=s.device)
@@ -166,6 +171,8 @@ def filterSpeckles(img, newVal, maxSpeckleSize, maxDiff, buf=None):
     with torch.cuda.device(s.device):
         _lib.check(_lib.load().b2s_filter_speckles(_ptr(view), H, W, B, int(newVal), int(maxSpeckleSize), int(maxDiff),
                                                    _ptr(labels), _ptr(counts), _stream()))
+    if src8 is not None:
+        s = s.to(torch.uint8)
     if kind == "numpy":
         img[...] = s.cpu().numpy()
         return img, buf

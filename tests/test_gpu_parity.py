@@ -435,6 +435,41 @@ def test_point_cloud_batch_and_chain(cv2ref):
         assert np.array_equal(cols[offs[b]:offs[b + 1]].cpu().numpy(), wc)
 
 
+def test_boundary_rules_found_by_the_errors_soak(cv2ref):
+    """tools/soak_parity.py errors: cv2.StereoBM_create maps any numDisparities <= 0 to 64 and refuses a block that is not
+    SMALLER than the image; cv2.filterSpeckles also takes CV_8UC1; MODE_SGBM / MODE_HH refuse a too narrow image, MODE_HH4 does not."""
+    import cv2
+    rng = np.random.default_rng(3)
+    l = rng.integers(0, 256, (31, 100), dtype=np.uint8)
+    r = rng.integers(0, 256, (31, 100), dtype=np.uint8)
+    for nd in (-16, -1, 0):
+        m = sm.StereoBM_create(numDisparities=nd, blockSize=9)
+        assert m.getNumDisparities() == cv2.StereoBM_create(numDisparities=nd, blockSize=9).getNumDisparities() == 64
+        assert np.array_equal(m.compute(l, r), cv2.StereoBM_create(numDisparities=nd, blockSize=9).compute(l, r))
+    for bs, ok in ((29, True), (31, False), (33, False)):             # H = 31
+        if ok:
+            assert np.array_equal(sm.StereoBM_create(numDisparities=16, blockSize=bs).compute(l, r),
+                                  cv2.StereoBM_create(numDisparities=16, blockSize=bs).compute(l, r))
+        else:
+            with pytest.raises(cv2.error):
+                cv2.StereoBM_create(numDisparities=16, blockSize=bs).compute(l, r)
+            with pytest.raises(sm.error, match="not larger than image width or height"):
+                sm.StereoBM_create(numDisparities=16, blockSize=bs).compute(l, r)
+    for t in range(20):
+        img = (rng.integers(0, 6, (30, 40)) * int(rng.integers(1, 40))).astype(np.uint8)
+        nv, size, diff = int(rng.choice([0, 255, 7, -1, 300])), int(rng.integers(0, 30)), int(rng.integers(0, 50))
+        a, b = img.copy(), img.copy()
+        cv2.filterSpeckles(a, nv, size, diff)
+        out, _ = sm.filterSpeckles(b, nv, size, diff)
+        assert out is b and b.dtype == np.uint8 and np.array_equal(a, b)
+    narrow_l, narrow_r = np.ascontiguousarray(l[:, :34]), np.ascontiguousarray(r[:, :34])
+    for mode in (0, 1):
+        with pytest.raises(sm.error, match="too small"):
+            sm.StereoSGBM_create(numDisparities=32, blockSize=5, P1=100, P2=400, mode=mode).compute(narrow_l, narrow_r)
+    kw = dict(minDisparity=0, numDisparities=32, blockSize=5, P1=100, P2=400, mode=3)
+    assert np.array_equal(sm.StereoSGBM_create(**kw).compute(narrow_l, narrow_r), cv2.StereoSGBM_create(**kw).compute(narrow_l, narrow_r))
+
+
 @pytest.mark.parametrize("seed", range(80))
 def test_sgbm_random_sweep(seed):
     """Seeded random parameter / size / mode / channel combinations against live cv2 (tests/random_cases.py)."""

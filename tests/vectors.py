@@ -129,6 +129,11 @@ SGBM_SOAK_VECTORS = [
     ("synth", 782, 90, 37, 0, 24, 0, 0, 2, 7, 64, 0, 2, 0, -2),
     ("synth", 440, 108, 54, 0, 40, -3, 400, 2000, 0, 30, 33, 2, 0, 1),
     ("synth", 441, 108, 54, 0, 40, -3, 400, 2000, 0, 30, 33, 1, 0, 1),       # MODE_HH: the 5-pixel fallback
+    # MODE_HH4 has no "image too small" test in cv2: it computes whatever width is left, all INVALID when none is
+    ("synth", 60, 34, 30, 0, 32, 5, 100, 400, 1, 63, 5, 3, 0, 0),            # width1 = 2 <= blockSize / 2
+    ("synth", 61, 33, 30, 0, 32, 9, 100, 400, 1, 63, 5, 3, 20, 2),           # width1 = 1
+    ("synth", 62, 20, 12, 0, 32, 5, 100, 400, 1, 63, 5, 3, 0, 0),            # W < numDisparities: nothing computable
+    ("synth", 63, 32, 12, 0, 32, 5, 100, 400, 1, 63, 5, 3, 0, 0),            # width1 = 0
 ]
 
 

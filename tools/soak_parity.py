@@ -1,10 +1,10 @@
 """Randomised parity soak of the engine against live cv2: many more shapes / parameters than the test suite (numDisparities 128 /
 256, every mode, ratios up to 99, penalties up to the edge of the 16-bit domain, fully negative ranges, colour, batches).
-usage: python tools/soak_parity.py [n_cases] [seed0] [sgbm|wide|big|params|bm|ops|chain|misc]      (GPU box; prints failures, exits 1 on any)
+usage: python tools/soak_parity.py [n_cases] [seed0] [sgbm|wide|big|params|bm|ops|chain|misc|errors]      (GPU box; prints failures, exits 1 on any)
 sgbm: the numDisparities 128 / 256 kernels (soak_cases.gen); wide: every regime (gen_wide); big: numDisparities up to 1024,
 blocks up to 15 (gen_big); params: cv2's silent fallbacks and odd values (gen_params); bm: StereoBM (gen_bm); ops: remap, cvtColor,
 medianBlur, filterSpeckles, reprojectImageTo3D; chain: the fused per-pair chain (sm.pipeline) against the separate cv2 calls;
-misc: compute_disparity, project_points_3D, point_cloud, map2Dto3D.
+misc: compute_disparity, project_points_3D, point_cloud, map2Dto3D; errors: invalid calls (both sides must raise, or neither).
 
 Round 2: 600 cases found 25 mismatches, all three of them cv2 rules the restatement did not have (tests/vectors.py
 SGBM_SOAK_VECTORS); 0 of 600 after."""
@@ -96,7 +96,90 @@ def soak_misc(k):
     return fails
 
 
+def soak_errors(k):
+    """Invalid calls: cv2 raises cv2.error -- the engine must raise too (and must not raise where cv2 accepts).
+    -> descriptions of the disagreements"""
+    rng = np.random.default_rng(949400 + k)
+    out = []
+
+    def both(name, f_cv2, f_sm):
+        try:
+            f_cv2()
+            a = None
+        except (cv2.error, TypeError, ValueError, SystemError, OverflowError) as ex:
+            a = type(ex).__name__
+        try:
+            f_sm()
+            b = None
+        except (sm.error, TypeError, ValueError, OverflowError) as ex:
+            b = type(ex).__name__
+        if (a is None) != (b is None):
+            out.append("%s: cv2 %s, engine %s" % (name, a or "accepts", b or "accepts"))
+
+    h, w = int(rng.integers(20, 60)), int(rng.integers(80, 160))
+    l = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    r = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    D = 16 * int(rng.integers(1, 4))
+    bad_pairs = {
+        "height mismatch": (l, r[:-1]), "width mismatch": (l, np.ascontiguousarray(r[:, :-1])), "float32 images": (l.astype(np.float32), r.astype(np.float32)),
+        "uint16 images": (l.astype(np.uint16), r.astype(np.uint16)), "int8 images": (l.astype(np.int8), r.astype(np.int8)),
+        # (2- and 4-channel pairs are left out: cv2 4.13.0 accepts them and then corrupts its heap in MODE_HH4; the engine takes 1 or 3)
+        "gray vs colour": (l, np.stack([r] * 3, -1)), "empty": (l[:0], r[:0]), "one column": (l[:, :1], r[:, :1]),
+        "too narrow": (np.ascontiguousarray(l[:, :D]), np.ascontiguousarray(r[:, :D])), "colour pair": (np.stack([l] * 3, -1), np.stack([r] * 3, -1)),
+        "non-contiguous": (l[:, ::2], r[:, ::2]), "transposed view": (l.T, r.T), "different dtypes": (l, r.astype(np.float32)),
+    }
+    name = list(bad_pairs)[int(rng.integers(0, len(bad_pairs)))]
+    a, b = bad_pairs[name]
+    # (MODE_SGBM_3WAY is left out: cv2 only refuses W - maxD <= 0 there, the engine keeps the other modes' test, DESIGN.md 2)
+    kw = dict(minDisparity=0, numDisparities=D, blockSize=5, P1=100, P2=400, mode=int(rng.choice([0, 1, 3])))
+    both("SGBM " + name, lambda: cv2.StereoSGBM_create(**kw).compute(a, b), lambda: sm.StereoSGBM_create(**kw).compute(a, b))
+    both("BM " + name, lambda: cv2.StereoBM_create(numDisparities=D, blockSize=9).compute(a, b),
+         lambda: sm.StereoBM_create(numDisparities=D, blockSize=9).compute(a, b))
+    # matcher parameters
+    nd = int(rng.choice([0, -16, 8, 17, 24, 16, 48]))
+    bsz = int(rng.choice([0, 3, 4, 5, 6, 21, 255, 257, -5, h | 1, (h + 2) | 1, 2 * h + 1]))
+    both("BM numDisparities %d blockSize %d" % (nd, bsz), lambda: cv2.StereoBM_create(numDisparities=nd, blockSize=bsz).compute(l, r),
+         lambda: sm.StereoBM_create(numDisparities=nd, blockSize=bsz).compute(l, r))
+    nds = int(rng.choice([0, -16, 1, 7, 17, 16]))
+    both("SGBM numDisparities %d" % nds, lambda: cv2.StereoSGBM_create(minDisparity=0, numDisparities=nds, blockSize=5).compute(l, r),
+         lambda: sm.StereoSGBM_create(minDisparity=0, numDisparities=nds, blockSize=5).compute(l, r))
+    for setter, val in (("PreFilterCap", int(rng.choice([0, 1, 31, 63, 64, 100]))), ("TextureThreshold", int(rng.choice([-1, 0, 10]))),
+                        ("UniquenessRatio", int(rng.choice([-1, 0, 15, 101]))), ("PreFilterSize", int(rng.choice([3, 5, 9, 256, 4])))):
+        def mk(mod, setter=setter, val=val):
+            m = mod.StereoBM_create(numDisparities=32, blockSize=9)
+            getattr(m, "set" + setter)(val)
+            return m.compute(l, r)
+        if hasattr(sm.StereoBM_create(numDisparities=32, blockSize=9), "set" + setter):
+            both("BM set%s(%d)" % (setter, val), lambda: mk(cv2), lambda: mk(sm))
+    # the stage operators
+    d = rng.integers(-16, 500, (h, w)).astype(np.int16)
+    Q = np.eye(4)
+    badq = {"Q 3x4": Q[:3], "Q 4x3": Q[:, :3], "Q int": Q.astype(np.int32), "Q float32": Q.astype(np.float32), "Q 1-d": Q.ravel()}
+    qn = list(badq)[int(rng.integers(0, len(badq)))]
+    both("reproject " + qn, lambda: cv2.reprojectImageTo3D(d, badq[qn]), lambda: sm.reprojectImageTo3D(d, badq[qn]))
+    # (a 3-d disparity array is a batch for the engine; cv2 returns None for an empty one)
+    badd = {"float64 disparity": d.astype(np.float64), "uint16 disparity": d.astype(np.uint16), "int8 disparity": d.astype(np.int8)}
+    dn = list(badd)[int(rng.integers(0, len(badd)))]
+    both("reproject " + dn, lambda: cv2.reprojectImageTo3D(badd[dn], Q), lambda: sm.reprojectImageTo3D(badd[dn], Q))
+    mx = rng.random((h, w)).astype(np.float32) * w
+    my = rng.random((h, w)).astype(np.float32) * h
+    badm = {"float64 maps": (mx.astype(np.float64), my.astype(np.float64)), "map size mismatch": (mx, my[:-1]), "int maps": (mx.astype(np.int32), my.astype(np.int32)),
+            "smaller maps": (mx[:5, :7].copy(), my[:5, :7].copy())}
+    mn = list(badm)[int(rng.integers(0, len(badm)))]
+    both("remap " + mn, lambda: cv2.remap(l, badm[mn][0], badm[mn][1], cv2.INTER_LINEAR), lambda: sm.remap(l, badm[mn][0], badm[mn][1], sm.INTER_LINEAR))
+    both("medianBlur float", lambda: cv2.medianBlur(d.astype(np.float64), 3), lambda: sm.medianBlur(d.astype(np.float64), 3))
+    both("filterSpeckles uint8", lambda: cv2.filterSpeckles(l.copy(), 0, 10, 1), lambda: sm.filterSpeckles(l.copy(), 0, 10, 1))
+    return out
+
+
 for k in range(seed0, seed0 + n):
+    if which == "errors":
+        f = soak_errors(k)
+        ran += 1
+        if f:
+            bad += 1
+            print("FAIL errors case %d: %s" % (k, "; ".join(f)))
+        continue
     if which == "misc":
         f = soak_misc(k)
         ran += 1
