@@ -108,12 +108,36 @@ def compute_disparity(gray_l, gray_r, disparity_settings, method="SGBM", return_
     UNPINNED (no cv2.ximgproc in this image, see wls.py).  With return_right=True `dispr` is returned as a third element.
     """
     left_matcher, right_matcher, wls_filter = _chain_objects(gray_l, disparity_settings, method)
-    displ = left_matcher.compute(gray_l, gray_r)
-    dispr = right_matcher.compute(gray_r, gray_l)
-    filtered_img = wls_filter.filter(displ, gray_l, None, dispr)
+    # One upload, one download: the three calls run on device tensors, and the right-view matcher runs on a side stream
+    # next to the left one (a single pair keeps a dozen SMs busy, the two matchers share nothing but their read-only inputs).
+    gl, kind = engine._to_device(gray_l, "gray_l")
+    gr, _ = engine._to_device(gray_r, "gray_r")
+    with torch.cuda.device(gl.device):
+        cur = torch.cuda.current_stream()
+        side = _side_stream(gl.device)
+        side.wait_stream(cur)                       # the uploads above were queued on `cur`
+        displ = left_matcher.compute(gl, gr)
+        with torch.cuda.stream(side):
+            dispr = right_matcher.compute(gr, gl)
+        for t in (gl, gr, dispr):
+            t.record_stream(side)
+        cur.wait_stream(side)
+        dispr.record_stream(cur)
+        filtered_img = wls_filter.filter(displ, gl, None, dispr)
+    out = (engine._from_device(displ, kind), engine._from_device(filtered_img, kind))
     if return_right:
-        return displ, filtered_img, dispr
-    return displ, filtered_img
+        out += (engine._from_device(dispr, kind),)
+    return out
+
+
+def _side_stream(device):
+    streams = getattr(_tls, "side", None)
+    if streams is None:
+        streams = _tls.side = {}
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    if key not in streams:
+        streams[key] = torch.cuda.Stream(device=device)
+    return streams[key]
 
 
 # The reference builds two matchers and a filter on EVERY call.  Built from scratch, each of them allocates (and at the
