@@ -435,6 +435,51 @@ def test_point_cloud_batch_and_chain(cv2ref):
         assert np.array_equal(cols[offs[b]:offs[b + 1]].cpu().numpy(), wc)
 
 
+def test_concurrent_matchers_on_two_streams():
+    """One handle per (device, stream): two host threads, each with its own CUDA stream and its own matchers, compute
+    interleaved cases at the same time; nothing in the library is shared between them (thread-local error / counters,
+    per-handle workspaces), so every result equals cv2's."""
+    import threading
+    import cv2
+    from random_cases import random_case, random_bm_case
+    cases = [random_case(s) for s in (3, 12, 20, 33, 41, 57)]
+    want = [cv2.StereoSGBM_create(**kw).compute(l, r) for kw, l, r in cases]
+    D, bs, setters, bl, br = random_bm_case(4)
+    ref = cv2.StereoBM_create(numDisparities=D, blockSize=bs)
+    for name, val in setters.items():
+        getattr(ref, "set" + name[0].upper() + name[1:])(val)
+    bm_want = ref.compute(bl, br)
+    errs = []
+
+    def worker(tid):
+        try:
+            stream = torch.cuda.Stream()
+            with torch.cuda.stream(stream):
+                ms = [sm.StereoSGBM_create(**kw) for kw, _, _ in cases]
+                bm = sm.StereoBM_create(numDisparities=D, blockSize=bs)
+                for name, val in setters.items():
+                    getattr(bm, "set" + name[0].upper() + name[1:])(val)
+                dev = [(torch.from_numpy(l).cuda(), torch.from_numpy(r).cuda()) for _, l, r in cases]
+                BL, BR = torch.from_numpy(bl).cuda(), torch.from_numpy(br).cuda()
+                rng = np.random.default_rng(tid)
+                for rep in range(25):
+                    for j in rng.permutation(len(cases)):
+                        got = ms[j].compute(*dev[j]).cpu().numpy()
+                        if not np.array_equal(got, want[j]):
+                            errs.append("thread %d rep %d case %d: %d pixels differ" % (tid, rep, j, (got != want[j]).sum()))
+                    if not np.array_equal(bm.compute(BL, BR).cpu().numpy(), bm_want):
+                        errs.append("thread %d rep %d: StereoBM differs" % (tid, rep))
+        except Exception as ex:          # noqa: BLE001  (reported through the assertion below)
+            errs.append("thread %d: %r" % (tid, ex))
+
+    threads = [threading.Thread(target=worker, args=(t,)) for t in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errs, errs[:5]
+
+
 def test_boundary_rules_found_by_the_errors_soak(cv2ref):
     """tools/soak_parity.py errors: cv2.StereoBM_create maps any numDisparities <= 0 to 64 and refuses a block that is not
     SMALLER than the image; cv2.filterSpeckles also takes CV_8UC1; MODE_SGBM / MODE_HH refuse a too narrow image, MODE_HH4 does not."""
