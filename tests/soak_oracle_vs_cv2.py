@@ -55,20 +55,22 @@ def one_ops(k):
 
 
 def one(k):
-    """k >= 0: StereoSGBM case k // 3 of tools/soak_cases.gen_wide / gen_big / gen_params (k % 3) ; k < 0: StereoBM case -k-1"""
+    """k >= 0: StereoSGBM case k // 4 of tools/soak_cases.gen_wide / gen_big / gen_params / gen_struct (k % 4) ; k < 0: StereoBM case
+    (-k-1) // 2 of gen_bm / gen_bm_struct"""
     import cv2
     from oracle import port, cv2ref
     from soak_cases import gen_wide, gen_bm
     if k < 0:
-        D, bs, setters, l, r = gen_bm(-k - 1)
+        from soak_cases import gen_bm_struct
+        D, bs, setters, l, r = (gen_bm, gen_bm_struct)[(-k - 1) % 2]((-k - 1) // 2)
         want = cv2ref.bm_compute(l, r, D, bs, **setters)
         if "speckleWindowSize" in setters and not (want != (setters["minDisparity"] - 1) * 16).any():
             return None           # cv2 returns uninitialised memory when nothing is valid and a speckle window is set
         got = port.bm_compute(l, r, D, bs, **setters)
         n = int((got != want).sum())
         return (k, n, (D, bs, setters), l.shape) if n else None
-    from soak_cases import gen_big, gen_params
-    c = (gen_wide, gen_big, gen_params)[k % 3](k // 3)
+    from soak_cases import gen_big, gen_params, gen_struct
+    c = (gen_wide, gen_big, gen_params, gen_struct)[k % 4](k // 4)
     if c is None:
         return None
     kw, l, r = c

@@ -233,3 +233,63 @@ def gen_chain(k):
         Q[3, 3] = float(rng.normal(0, 0.5))
     return dict(kw=kw, left=raw(l), right=raw(r), maps_left=maps(), maps_right=maps(), Q=Q,
                 scale=float(rng.choice([1.0 / 16.0, 1.0])), hm=bool(rng.random() < 0.5), cn=cn)
+
+
+def structured_pair(rng, w, h, maxd):
+    """Image pairs full of exact ties: constant, step edges, checkerboards, stripes, binary noise, identical views, exact
+    shifts, half flat / half textured -- the opposite of the textured synthetic scenes."""
+    kind = int(rng.integers(0, 9))
+    yy, xx = np.mgrid[0:h, 0:w]
+    if kind == 0:
+        l = np.full((h, w), int(rng.integers(0, 256)), np.uint8)
+        r = np.full((h, w), int(rng.integers(0, 256)), np.uint8) if rng.random() < 0.5 else l.copy()
+    elif kind == 1:                                        # vertical step edges
+        p = int(rng.integers(2, 40))
+        l = (((xx // p) % 2) * int(rng.integers(1, 256))).astype(np.uint8)
+        r = np.roll(l, -int(rng.integers(0, max(maxd, 1))), 1)
+    elif kind == 2:                                        # checkerboard
+        p, q = int(rng.integers(1, 12)), int(rng.integers(1, 12))
+        l = ((((xx // p) + (yy // q)) % 2) * 255).astype(np.uint8)
+        r = np.roll(l, -int(rng.integers(0, max(maxd, 1))), 1)
+    elif kind == 3:                                        # horizontal stripes: every disparity looks the same
+        l = (((yy // int(rng.integers(1, 6))) % 2) * int(rng.integers(1, 256))).astype(np.uint8)
+        r = l.copy()
+    elif kind == 4:                                        # binary noise, exact shift
+        l = (rng.integers(0, 2, (h, w)) * 255).astype(np.uint8)
+        r = np.roll(l, -int(rng.integers(0, max(maxd, 1))), 1)
+    elif kind == 5:                                        # identical textured views (disparity 0 everywhere)
+        l = rng.integers(0, 256, (h, w), dtype=np.uint8)
+        r = l.copy()
+    elif kind == 6:                                        # few grey levels: plateaus
+        l = (rng.integers(0, 4, (h, w)) * 60).astype(np.uint8)
+        r = np.roll(l, -int(rng.integers(0, max(maxd, 1))), 1)
+        r[rng.random((h, w)) < 0.05] = 0
+    elif kind == 7:                                        # smooth ramp
+        l = ((xx * int(rng.integers(1, 5)) + yy) % 256).astype(np.uint8)
+        r = np.roll(l, -int(rng.integers(0, max(maxd, 1))), 1)
+    else:                                                  # left half flat, right half textured
+        l = rng.integers(0, 256, (h, w), dtype=np.uint8)
+        l[:, : w // 2] = 128
+        r = np.roll(l, -int(rng.integers(0, max(maxd, 1))), 1)
+    return np.ascontiguousarray(l), np.ascontiguousarray(r)
+
+
+def gen_struct(k):
+    """gen_wide's parameters on structured_pair images.  -> (kw, left, right) or None"""
+    c = gen_wide(k)
+    if c is None:
+        return None
+    kw, l, r = c
+    rng = np.random.default_rng(313100 + k)
+    h, w = l.shape[:2]
+    a, b = structured_pair(rng, w, h, max(kw["numDisparities"] + kw["minDisparity"], 1))
+    if l.ndim == 3:
+        a, b = np.stack([a, a // 2, 255 - a], -1), np.stack([b, b // 2, 255 - b], -1)
+    return kw, a, b
+
+
+def gen_bm_struct(k):
+    D, bs, setters, l, r = gen_bm(k)
+    rng = np.random.default_rng(313900 + k)
+    a, b = structured_pair(rng, l.shape[1], l.shape[0], max(D + setters["minDisparity"], 1))
+    return D, bs, setters, a, b

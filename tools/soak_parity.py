@@ -1,8 +1,9 @@
 """Randomised parity soak of the engine against live cv2: many more shapes / parameters than the test suite (numDisparities 128 /
 256, every mode, ratios up to 99, penalties up to the edge of the 16-bit domain, fully negative ranges, colour, batches).
-usage: python tools/soak_parity.py [n_cases] [seed0] [sgbm|wide|big|params|bm|ops|chain|misc|errors]      (GPU box; prints failures, exits 1 on any)
+usage: python tools/soak_parity.py [n_cases] [seed0] [sgbm|wide|big|params|struct|bm|bmstruct|ops|chain|misc|errors]      (GPU box; prints failures, exits 1 on any)
 sgbm: the numDisparities 128 / 256 kernels (soak_cases.gen); wide: every regime (gen_wide); big: numDisparities up to 1024,
-blocks up to 15 (gen_big); params: cv2's silent fallbacks and odd values (gen_params); bm: StereoBM (gen_bm); ops: remap, cvtColor,
+blocks up to 15 (gen_big); params: cv2's silent fallbacks and odd values (gen_params); struct / bmstruct: tie-heavy structured images
+(constant, edges, checkerboards, exact shifts); bm: StereoBM (gen_bm); ops: remap, cvtColor,
 medianBlur, filterSpeckles, reprojectImageTo3D; chain: the fused per-pair chain (sm.pipeline) against the separate cv2 calls;
 misc: compute_disparity, project_points_3D, point_cloud, map2Dto3D; errors: invalid calls (both sides must raise, or neither).
 
@@ -16,7 +17,7 @@ import cv2
 import numpy as np
 import torch
 
-from soak_cases import gen, gen_wide, gen_big, gen_params, gen_bm, gen_chain, ops_failures
+from soak_cases import gen, gen_wide, gen_big, gen_params, gen_struct, gen_bm, gen_bm_struct, gen_chain, ops_failures
 
 import stereo_match_b200 as sm
 from stereo_match_b200.synth import synth_pair
@@ -227,8 +228,8 @@ for k in range(seed0, seed0 + n):
             bad += 1
             print("FAIL chain case %d: %s, %r cn %d scale %g hm %d shape %r" % (k, ", ".join(f), c["kw"], c["cn"], c["scale"], c["hm"], c["left"].shape))
         continue
-    if which == "bm":
-        D, bs, setters, l, r = gen_bm(k)
+    if which in ("bm", "bmstruct"):
+        D, bs, setters, l, r = (gen_bm if which == "bm" else gen_bm_struct)(k)
         ref = cv2.StereoBM_create(numDisparities=D, blockSize=bs)
         m = sm.StereoBM_create(numDisparities=D, blockSize=bs)
         for name, val in setters.items():
@@ -243,7 +244,7 @@ for k in range(seed0, seed0 + n):
             bad += 1
             print("FAIL bm case %d: %d pixels differ, D %d bs %d %r shape %r" % (k, int((got != want).sum()), D, bs, setters, l.shape))
         continue
-    c = {"sgbm": gen, "wide": gen_wide, "big": gen_big, "params": gen_params}[which](k)
+    c = {"sgbm": gen, "wide": gen_wide, "big": gen_big, "params": gen_params, "struct": gen_struct}[which](k)
     if c is None:
         continue
     kw, l, r = c[:3]
