@@ -293,3 +293,29 @@ def gen_bm_struct(k):
     rng = np.random.default_rng(313900 + k)
     a, b = structured_pair(rng, l.shape[1], l.shape[0], max(D + setters["minDisparity"], 1))
     return D, bs, setters, a, b
+
+
+def gen_large(k):
+    """Realistic sizes (up to 1300 x 420) with random parameters and small batches: many bands in flight, the ticket order and
+    the progress publication of the band pipeline under different timings.  -> (kw, left, right, cn, batch)"""
+    rng = np.random.default_rng(474700 + k)
+    D = int(rng.choice([64, 96, 128, 128, 160, 256]))
+    bs = int(rng.choice([3, 5, 5, 7]))
+    cn = 3 if rng.random() < 0.1 else 1
+    cap = int(rng.choice([31, 63]))
+    cmax = bs * bs * (2 * (max(cap, 15) | 1) + 63) * cn
+    hi = (32767 - 2 * cmax) // 3
+    if hi < 100:                                           # colour with a large block leaves no overflow-free P2
+        cn, cmax = 1, cmax // 3
+        hi = (32767 - 2 * cmax) // 3
+    P2 = int(rng.integers(50, min(hi, 5000)))
+    P1 = int(rng.integers(1, P2))
+    minD = int(rng.choice([0, 0, 0, 16, -20]))
+    w = int(rng.integers(max(D + minD, 0) + 200, 1300))
+    h = int(rng.integers(60, 420))
+    kw = dict(minDisparity=minD, numDisparities=D, blockSize=bs, P1=P1, P2=P2, disp12MaxDiff=int(rng.choice([-1, 1, 2])),
+              preFilterCap=cap, uniquenessRatio=int(rng.choice([0, 5, 15])), speckleWindowSize=int(rng.choice([0, 100])),
+              speckleRange=int(rng.choice([1, 2])), mode=int(rng.choice([0, 1, 1, 2, 3])))
+    maxd = _scene_range(rng, D + minD)
+    l, r = synth_pair(w, h, maxd, seed=k) if cn == 1 else color_pair(w, h, maxd, k)
+    return kw, l, r, cn, int(rng.choice([1, 2, 3]))

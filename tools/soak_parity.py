@@ -1,8 +1,8 @@
 """Randomised parity soak of the engine against live cv2: many more shapes / parameters than the test suite (numDisparities 128 /
 256, every mode, ratios up to 99, penalties up to the edge of the 16-bit domain, fully negative ranges, colour, batches).
-usage: python tools/soak_parity.py [n_cases] [seed0] [sgbm|wide|big|params|struct|bm|bmstruct|ops|chain|misc|errors]      (GPU box; prints failures, exits 1 on any)
+usage: python tools/soak_parity.py [n_cases] [seed0] [sgbm|wide|big|params|struct|large|bm|bmstruct|ops|chain|misc|errors]      (GPU box; prints failures, exits 1 on any)
 sgbm: the numDisparities 128 / 256 kernels (soak_cases.gen); wide: every regime (gen_wide); big: numDisparities up to 1024,
-blocks up to 15 (gen_big); params: cv2's silent fallbacks and odd values (gen_params); struct / bmstruct: tie-heavy structured images
+blocks up to 15 (gen_big); params: cv2's silent fallbacks and odd values (gen_params); large: realistic sizes, small batches (gen_large); struct / bmstruct: tie-heavy structured images
 (constant, edges, checkerboards, exact shifts); bm: StereoBM (gen_bm); ops: remap, cvtColor,
 medianBlur, filterSpeckles, reprojectImageTo3D; chain: the fused per-pair chain (sm.pipeline) against the separate cv2 calls;
 misc: compute_disparity, project_points_3D, point_cloud, map2Dto3D; errors: invalid calls (both sides must raise, or neither).
@@ -17,7 +17,7 @@ import cv2
 import numpy as np
 import torch
 
-from soak_cases import gen, gen_wide, gen_big, gen_params, gen_struct, gen_bm, gen_bm_struct, gen_chain, ops_failures
+from soak_cases import gen, gen_wide, gen_big, gen_params, gen_struct, gen_large, gen_bm, gen_bm_struct, gen_chain, ops_failures
 
 import stereo_match_b200 as sm
 from stereo_match_b200.synth import synth_pair
@@ -244,11 +244,11 @@ for k in range(seed0, seed0 + n):
             bad += 1
             print("FAIL bm case %d: %d pixels differ, D %d bs %d %r shape %r" % (k, int((got != want).sum()), D, bs, setters, l.shape))
         continue
-    c = {"sgbm": gen, "wide": gen_wide, "big": gen_big, "params": gen_params, "struct": gen_struct}[which](k)
+    c = {"sgbm": gen, "wide": gen_wide, "big": gen_big, "params": gen_params, "struct": gen_struct, "large": gen_large}[which](k)
     if c is None:
         continue
     kw, l, r = c[:3]
-    cn, B = (c[3], c[4]) if which == "sgbm" else (l.ndim == 3 and 3 or 1, 1 + 2 * (k % 3 == 0))
+    cn, B = (c[3], c[4]) if which in ("sgbm", "large") else (l.ndim == 3 and 3 or 1, 1 + 2 * (k % 3 == 0))
     try:
         want = cv2.StereoSGBM_create(**kw).compute(l, r)
     except cv2.error:
